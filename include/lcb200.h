@@ -1,0 +1,170 @@
+/*
+ * lcb200.h — C ABI of the B200-native LightCompress/LLMC quantization hot path.
+ *
+ * Every entry point takes plain device pointers, sizes and a CUDA stream handle
+ * (passed as void* so that the header compiles without the CUDA toolkit). No
+ * torch types cross this boundary. Every function returns LCB_OK (0) or a negative
+ * LCB_E_* code; nothing allocates, nothing synchronises the host.
+ *
+ * The reference (zhangbilang/LightCompress, all-Python) has no FFI; each function
+ * below names the reference Python interface it replaces (file:line under
+ * /root/reference/llmc/compression/quantization/).
+ */
+#ifndef LCB200_H_
+#define LCB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LCB_ABI_VERSION 1
+
+/* status codes (the Python shim maps them onto the reference's exception types) */
+#define LCB_OK 0
+#define LCB_E_INVALID (-1)     /* bad argument combination      -> AssertionError   */
+#define LCB_E_SHAPE (-2)       /* non-divisible group etc.       -> ValueError       */
+#define LCB_E_UNSUPPORTED (-3) /* unknown format                 -> NotImplementedError */
+#define LCB_E_CUDA (-4)        /* launch failed                  -> RuntimeError     */
+#define LCB_E_ALIGN (-5)       /* pointer not aligned as stated  -> ValueError       */
+
+/* tensor storage dtypes */
+#define LCB_F32 0
+#define LCB_F16 1
+#define LCB_BF16 2
+
+/* quantization kind */
+#define LCB_KIND_INT 0      /* IntegerQuantizer           quant.py:661  */
+#define LCB_KIND_FP8_E4M3 1 /* FloatQuantizer bit='e4m3'  quant.py:963  */
+#define LCB_KIND_FP8_E5M2 2 /* FloatQuantizer bit='e5m2'                */
+
+/* what the kernel writes to `out` */
+#define LCB_OUT_FAKE 0   /* quant-dequant value, storage dtype (fake_quant_*)          */
+#define LCB_OUT_I8 1     /* integer code as int8   (real_quant, bit==8, qmin!=0)       */
+#define LCB_OUT_U8 2     /* integer code as uint8  (real_quant, bit==8, qmin==0)       */
+#define LCB_OUT_I32 3    /* integer code as int32  (real_quant, any other bit)         */
+#define LCB_OUT_FP8 4    /* fp8 byte (e4m3fn / e5m2) (FloatQuantizer.real_quant_*)     */
+#define LCB_OUT_NONE 5   /* nothing: qparams only  (get_tensor_qparams)                */
+#define LCB_OUT_CODE_T 6 /* integer code kept in the math dtype (IntegerQuantizer.quant) */
+
+/*
+ * Quantizer description. Mirrors the ctor kwargs of BaseQuantizer/IntegerQuantizer/
+ * FloatQuantizer (quant.py:47-101, 662-678, 964-1003).
+ *
+ * Arithmetic model (SURVEY.md §8a "exact arithmetic spec"): every torch op of the
+ * reference chain is "fp32 compute, round result to the math dtype". `math_dtype`
+ * is that dtype: the tensor dtype for per_tensor/per_channel/per_group/per_token
+ * dynamic quantization, LCB_F32 for per_block (quant.py:137-138 upcasts) and for
+ * static calls whose scales are fp32 (type promotion).
+ */
+typedef struct lcb_quant_spec {
+  int32_t dtype;       /* storage dtype of in / LCB_OUT_FAKE out                   */
+  int32_t math_dtype;  /* dtype every intermediate is rounded to                   */
+  int32_t qparam_dtype;/* storage dtype of the scales / zeros arrays               */
+  int32_t kind;        /* LCB_KIND_*                                                */
+  int32_t sym;         /* symmetric (zeros == 0)                                    */
+  int32_t round_zp;    /* quant.py:73, :556-558                                     */
+  int32_t out_mode;    /* LCB_OUT_*                                                 */
+  int32_t qp_math_plus1; /* 0: scales/zeros are computed in math_dtype. d+1: the divisions of get_qparams round to dtype d
+                            (per_tensor: 0-dim min/max divided by a 0-dim fp32 qmax promote to fp32, quant.py:552-556) */
+  float qmin;          /* quant.py:666-677 (int) / :979-1003 (float)                */
+  float qmax;
+  float output_scale_factor; /* quant.py:716 (dequant only), 1.0f if unused        */
+  float clip_ratio;    /* AutoClip v1 shrink: range *= clip_ratio before qparams (auto_clip.py:139-141,258-262); 1.0f = off */
+} lcb_quant_spec;
+
+/*
+ * Grouped quant-dequant, the single-pass kernel.
+ * The tensor is a row-major [rows, cols] matrix with leading dimension `cols`
+ * (contiguous). A quantization unit is a `unit_rows x unit_cols` tile:
+ *   per_group   : 1 x group_size        per_channel / per_token : 1 x cols
+ *   per_tensor  : rows x cols            per_block               : bs x bs (ragged edges = zero padded)
+ * dynamic != 0 : min/max/absmax -> qparams -> round -> clamp -> dequant in one pass;
+ *                scales/zeros (may be NULL) receive the qparams, one per unit, row-major over the
+ *                unit grid [ceil(rows/unit_rows), ceil(cols/unit_cols)].
+ * dynamic == 0 : scales (and zeros unless sym) are inputs.
+ * workspace    : >= lcb_fakequant_workspace_bytes() bytes, only used by per_tensor dynamic.
+ *
+ * Replaces IntegerQuantizer.get_tensor_qparams + quant_dequant / quant (quant.py:690-717),
+ * fake_quant_{weight,act}_{dynamic,static} (quant.py:719-869), real_quant_weight_{dynamic,static}
+ * (quant.py:871-953), FloatQuantizer equivalents (quant.py:1043-1221) and
+ * weight_cast_to_fp8 (quant.py:34-43, kernel.py:56-83).
+ */
+int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t rows, int64_t cols,
+                  int64_t unit_rows, int64_t unit_cols, const lcb_quant_spec* spec, int dynamic,
+                  void* workspace, void* stream);
+
+int64_t lcb_fakequant_workspace_bytes(void);
+
+/*
+ * Block-wise FP8 dequantisation y = x_fp8 * s[block] -> bf16/f16/f32
+ * Replaces weight_cast_to_bf16 (quant.py:18-31, kernel.py:86-138).
+ */
+int lcb_fp8_block_dequant(const void* codes, const float* scales, void* out, int64_t rows,
+                          int64_t cols, int64_t block, int32_t kind, int32_t out_dtype,
+                          void* stream);
+
+/*
+ * GPTQ Hessian accumulation  H <- H * n/(n+b) ; n += b ; H += (2/n) X^T X
+ * X is the layer input flattened to [tokens, C] row-major (the reference transposes a view,
+ * gptq.py:265-267), H is fp32 [C, C] row-major. n_before / n_batch are the reference's
+ * `nsamples` and `tmp` (gptq.py:283-290; they count batches, not tokens).
+ * The contraction runs on tcgen05 tensor cores with a bf16 3-way split of the fp32 operand
+ * (error ~2^-22 relative, i.e. fp32-class) and fp32 accumulation in TMEM.
+ * workspace: lcb_hessian_workspace_bytes(tokens, C) bytes of device scratch.
+ * Replaces GPTQ.add_batch (gptq.py:254-295) minus the per-batch all-reduce.
+ */
+int lcb_hessian_accum(float* H, const void* X, int64_t tokens, int64_t C, int32_t x_dtype,
+                      double n_before, double n_batch, void* workspace, void* stream);
+int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C);
+
+/*
+ * GPTQ blocked column update (gptq.py:199-244).
+ * W [R, C] fp32 row-major is updated in place (the reference mutates W too), Hinv [C, C] fp32 is the
+ * upper Cholesky factor of the inverse damped Hessian (gptq.py:172-174).
+ * Out (`tmp`, gptq.py:237) receives the error-compensated float columns, Losses the per-element
+ * loss (gptq.py:238). For per_group dynamic (static_groups == 0) group qparams are searched on the
+ * outer W at every group boundary (gptq.py:215-223) and written to gscales / gzeros, laid out
+ * [C/group, R] fp32. For static_groups / per_channel the same arrays are inputs
+ * (group index per column from `col_group`, int32 [C], may be NULL = col / group).
+ * workspace: lcb_gptq_workspace_bytes(R, C, blocksize).
+ * Replaces GPTQ.weight_transform + search_column_qparams (gptq.py:199-244, 359-366).
+ */
+int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out, float* Losses, float* gscales,
+                              float* gzeros, const int32_t* col_group, int64_t R, int64_t C,
+                              int64_t n_nonout, int32_t blocksize, int32_t group_size,
+                              int32_t static_groups, const lcb_quant_spec* spec, void* workspace,
+                              void* stream);
+int64_t lcb_gptq_workspace_bytes(int64_t R, int64_t C, int32_t blocksize);
+
+/*
+ * AWQ scale-search candidate, one fused pass per candidate ratio (awq.py:202-248):
+ *   Wq = fake_quant(W * s[None, :])          (awq.py:147-164, weight scaled in place then fake-quantised)
+ *   out = (x / s) @ Wq^T                      (base_bq.py:877-889 scaling_input + F.linear)
+ *   loss[cand] += sum((out - org_out)^2)      (awq.py:134-145; caller divides by numel)
+ * W [R, C] and x [T, C] and org_out [T, R] are bf16/f16 row-major; cand_scales [n_cand, C] in the same
+ * dtype (awq.py:100-107 computes them in the activation dtype). loss is fp32 [n_cand] (sum of squared
+ * error, accumulated; zero it first). The scaled + fake-quantised weight tile is produced in shared
+ * memory and fed to tcgen05 directly — it never round-trips HBM.
+ */
+int lcb_awq_candidates(const void* W, const void* x, const void* org_out, const void* cand_scales,
+                       float* loss, int64_t T, int64_t R, int64_t C, int32_t n_cand,
+                       int32_t group_size, const lcb_quant_spec* spec, void* workspace, void* stream);
+int64_t lcb_awq_workspace_bytes(int64_t T, int64_t R, int64_t C, int32_t n_cand);
+
+/* column absmax of a [rows, cols] matrix -> fp32 [cols] (running max: out = max(out, colmax)).
+ * Replaces SmoothQuant.get_act_scale / get_weight_scale (smoothquant.py:27-51) and the |x| reductions
+ * of Awq.get_act_scale (awq.py:74-85) when mean != 0 (then it is a column |x| sum). */
+int lcb_col_absstat(const void* x, float* out, int64_t rows, int64_t cols, int32_t dtype, int32_t mean,
+                    void* stream);
+
+/* version / capability probe; returns LCB_ABI_VERSION */
+int lcb_abi_version(void);
+/* name of the last failing CUDA call of this thread ("" if none) */
+const char* lcb_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LCB200_H_ */

@@ -1,0 +1,180 @@
+// fakequant_host.cuh — host-side dispatch of lcb_fakequant (included by fakequant.cu)
+#pragma once
+#include <math.h>
+
+namespace lcb {
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static SpecD make_specd(const lcb_quant_spec* s) {
+  SpecD d;
+  d.dtype = s->dtype;
+  d.math_dtype = s->math_dtype;
+  d.qparam_dtype = s->qparam_dtype;
+  d.kind = s->kind;
+  d.sym = s->sym;
+  d.round_zp = s->round_zp;
+  d.out_mode = s->out_mode;
+  d.qmin = s->qmin;
+  d.qmax = s->qmax;
+  d.osf = s->output_scale_factor;
+  d.clip = s->clip_ratio;
+  d.qp_math = s->qp_math_plus1 > 0 ? s->qp_math_plus1 - 1 : s->math_dtype;
+  bool ints = (floorf(d.qmin) == d.qmin) && (floorf(d.qmax) == d.qmax) && fabsf(d.qmin) <= 256.f &&
+              fabsf(d.qmax) <= 256.f;
+  d.fast_ok = (d.kind == LCB_KIND_INT) ? (d.round_zp && ints) : 1;
+  return d;
+}
+
+static int grid_for(int64_t work_ctas, int ctas_per_sm) {
+  int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
+  return (int)(work_ctas < cap ? (work_ctas < 1 ? 1 : work_ctas) : cap);
+}
+
+#define LCB_NV_SWITCH(NVV, ...)                   \
+  switch (NVV) {                                  \
+    case 1: { constexpr int NV = 1; __VA_ARGS__; } break; \
+    case 2: { constexpr int NV = 2; __VA_ARGS__; } break; \
+    case 4: { constexpr int NV = 4; __VA_ARGS__; } break; \
+    default: { constexpr int NV = 8; __VA_ARGS__; } break; \
+  }
+
+template <typename T, int KINDC>
+static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, int64_t n_units, int64_t unit_len,
+                             const SpecD& sp, cudaStream_t st) {
+  constexpr int VEC = TI<T>::VEC;
+  const int64_t nvec = unit_len / VEC;
+  if (nvec <= 256) {
+    int lanes = 1;
+    while (lanes < nvec && lanes < 32) lanes <<= 1;
+    if (lanes < 4) lanes = 4;
+    int nv = (int)((nvec + lanes - 1) / lanes);
+    int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
+    const int64_t subs_per_cta = 256 / lanes;
+    LCB_NV_SWITCH(nvt, {
+      constexpr int UNR = NV >= 4 ? 1 : (4 / NV);
+      int64_t ctas = (n_units + subs_per_cta * UNR - 1) / (subs_per_cta * UNR);
+      int grid = grid_for(ctas, 8);
+      fq_subwarp_kernel<T, NV, UNR, KINDC><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, lanes, sp);
+    });
+  } else if (nvec <= 4096) {
+    int threads = nvec <= 2048 ? 256 : 512;
+    int nv = (int)((nvec + threads - 1) / threads);
+    int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
+    int grid = grid_for(n_units, threads == 256 ? 6 : 3);
+    LCB_NV_SWITCH(nvt, { fq_row_kernel<T, NV, KINDC><<<grid, threads, 0, st>>>(in, out, scales, zeros, n_units, unit_len, sp); });
+  } else {
+    int grid = grid_for(n_units, 4);
+    fq_row_stream_kernel<T, KINDC><<<grid, 512, 0, st>>>(in, out, scales, zeros, n_units, unit_len, sp);
+  }
+  LCB_CUDA_CHECK_LAUNCH("fq_dynamic_1d");
+  return LCB_OK;
+}
+
+template <typename T, int KINDC>
+static int launch_static(const T* in, void* out, const void* scales, const void* zeros, int64_t rows, int64_t cols,
+                         int64_t ur, int64_t uc, const SpecD& sp, cudaStream_t st) {
+  constexpr int VEC = TI<T>::VEC;
+  int64_t total = rows * (cols / VEC);
+  int grid = grid_for((total + 1023) / 1024, 8);
+  if (sp.math_dtype == LCB_F32)
+    fq_static_kernel<T, float, KINDC><<<grid, 256, 0, st>>>(in, out, scales, zeros, rows, cols, ur, uc, sp);
+  else
+    fq_static_kernel<T, T, KINDC><<<grid, 256, 0, st>>>(in, out, scales, zeros, rows, cols, ur, uc, sp);
+  LCB_CUDA_CHECK_LAUNCH("fq_static");
+  return LCB_OK;
+}
+
+constexpr int kMaxParts = kNumSMs * 8;
+
+template <typename T>
+static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros, int64_t rows, int64_t cols,
+                           int64_t ur, int64_t uc, SpecD sp, int dynamic, void* workspace, cudaStream_t st) {
+  constexpr int VEC = TI<T>::VEC;
+  const T* in = reinterpret_cast<const T*>(in_);
+  const int kindc = sp.kind == LCB_KIND_INT ? 0 : 1;
+  if (ur > rows) ur = rows;
+  if (uc > cols) uc = cols;
+  const bool vec_ok = aligned16(in) && (out == nullptr || aligned16(out)) && (cols % VEC == 0) && (uc % VEC == 0);
+  const bool whole = (ur == rows && uc == cols);
+  const bool math_is_T = sp.math_dtype == sp.dtype;
+#define LCB_KIND_SWITCH(...)                                  \
+  if (kindc == 0) { constexpr int KINDC = 0; __VA_ARGS__; }   \
+  else { constexpr int KINDC = 1; __VA_ARGS__; }
+
+  if (!dynamic) {
+    if (!scales) return LCB_E_INVALID;
+    if (vec_ok && (math_is_T || sp.math_dtype == LCB_F32)) {
+      LCB_KIND_SWITCH(return launch_static<T, KINDC>(in, out, scales, zeros, rows, cols, ur, uc, sp, st));
+    }
+    int64_t units = ((rows + ur - 1) / ur) * ((cols + uc - 1) / uc);
+    fq_generic_kernel<T><<<grid_for((units + 7) / 8, 8), 256, 0, st>>>(in, out, scales, zeros, rows, cols, ur, uc, 0, 0, sp);
+    LCB_CUDA_CHECK_LAUNCH("fq_generic_static");
+    return LCB_OK;
+  }
+  // dynamic
+  if (vec_ok && math_is_T && !whole && (ur == 1 || rows == 1) && cols % uc == 0) {
+    LCB_KIND_SWITCH(return launch_dynamic_1d<T, KINDC>(in, out, scales, zeros, rows * (cols / uc), uc, sp, st));
+  }
+  if (vec_ok && math_is_T && whole && rows * cols >= 4096) {
+    if (!workspace) return LCB_E_INVALID;
+    float* ws = reinterpret_cast<float*>(workspace);
+    int64_t numel = rows * cols;
+    int parts = grid_for((numel / VEC + 1023) / 1024, 8);
+    minmax_partial_kernel<T><<<parts, 256, 0, st>>>(in, numel, ws);
+    minmax_finalize_kernel<<<1, 256, 0, st>>>(ws, parts, scales, zeros, sp);
+    LCB_CUDA_CHECK_LAUNCH("fq_minmax");
+    if (sp.out_mode == LCB_OUT_NONE) return LCB_OK;
+    SpecD sp2 = sp;
+    sp2.qparam_dtype = LCB_F32;
+    float* q = ws + 2 * parts;
+    LCB_KIND_SWITCH(return launch_static<T, KINDC>(in, out, q, sp.sym ? nullptr : q + 1, rows, cols, rows, cols, sp2, st));
+  }
+  if (vec_ok && sp.math_dtype == LCB_F32 && ur == 128 && uc == 128 && sp.sym) {
+    int64_t tiles = ((rows + 127) / 128) * ((cols + 127) / 128);
+    if (tiles > 0x7fffffff) return LCB_E_SHAPE;
+    LCB_KIND_SWITCH(fq_block2d_kernel<T, KINDC><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp));
+    LCB_CUDA_CHECK_LAUNCH("fq_block2d");
+    return LCB_OK;
+  }
+  {
+    int64_t units = ((rows + ur - 1) / ur) * ((cols + uc - 1) / uc);
+    int abs_range = (ur > 1 && !whole) ? 1 : 0;  // per_block: range of |x| (quant.py:137-138)
+    fq_generic_kernel<T><<<grid_for((units + 7) / 8, 8), 256, 0, st>>>(in, out, scales, zeros, rows, cols, ur, uc, 1, abs_range, sp);
+    LCB_CUDA_CHECK_LAUNCH("fq_generic_dynamic");
+    return LCB_OK;
+  }
+#undef LCB_KIND_SWITCH
+}
+
+}  // namespace lcb
+
+extern "C" int64_t lcb_fakequant_workspace_bytes(void) { return (int64_t)(2 * lcb::kMaxParts + 8) * sizeof(float); }
+
+extern "C" int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t rows, int64_t cols,
+                             int64_t unit_rows, int64_t unit_cols, const lcb_quant_spec* spec, int dynamic,
+                             void* workspace, void* stream) {
+  using namespace lcb;
+  if (!in || !spec || rows < 0 || cols < 0 || unit_rows < 1 || unit_cols < 1) return LCB_E_INVALID;
+  if (spec->out_mode != LCB_OUT_NONE && !out) return LCB_E_INVALID;
+  if (spec->kind < LCB_KIND_INT || spec->kind > LCB_KIND_FP8_E5M2) return LCB_E_UNSUPPORTED;
+  if (spec->dtype < LCB_F32 || spec->dtype > LCB_BF16 || spec->math_dtype < LCB_F32 || spec->math_dtype > LCB_BF16 ||
+      spec->qparam_dtype < LCB_F32 || spec->qparam_dtype > LCB_BF16)
+    return LCB_E_UNSUPPORTED;
+  if (spec->out_mode < LCB_OUT_FAKE || spec->out_mode > LCB_OUT_CODE_T) return LCB_E_UNSUPPORTED;
+  if (spec->kind != LCB_KIND_INT && !(spec->out_mode == LCB_OUT_FAKE || spec->out_mode == LCB_OUT_FP8 ||
+                                      spec->out_mode == LCB_OUT_NONE || spec->out_mode == LCB_OUT_CODE_T))
+    return LCB_E_INVALID;
+  if (spec->kind == LCB_KIND_INT && spec->out_mode == LCB_OUT_FP8) return LCB_E_INVALID;
+  if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  if (rows == 0 || cols == 0) return LCB_OK;
+  // ragged units are only defined for per_block (zero padding); 1-D groups must divide (quant.py:627-630)
+  if (unit_rows == 1 && unit_cols < cols && cols % unit_cols != 0) return LCB_E_SHAPE;
+  SpecD sp = make_specd(spec);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (spec->dtype) {
+    case LCB_F32: return fakequant_typed<float>(in, out, scales, zeros, rows, cols, unit_rows, unit_cols, sp, dynamic, workspace, st);
+    case LCB_F16: return fakequant_typed<__half>(in, out, scales, zeros, rows, cols, unit_rows, unit_cols, sp, dynamic, workspace, st);
+    default: return fakequant_typed<__nv_bfloat16>(in, out, scales, zeros, rows, cols, unit_rows, unit_cols, sp, dynamic, workspace, st);
+  }
+}

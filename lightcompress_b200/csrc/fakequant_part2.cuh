@@ -1,0 +1,221 @@
+// fakequant_part2.cuh — per_block, static, generic and per_tensor kernels (included by fakequant.cu)
+#pragma once
+
+namespace lcb {
+
+// ------------------------------------------------------------------------------------------------
+// per_block 128x128 (quant.py:137-138: |x| upcast to fp32 -> fp32 scales, fp32 math)
+// ------------------------------------------------------------------------------------------------
+template <typename T, int KINDC>
+__global__ void __launch_bounds__(256)
+    fq_block2d_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, int64_t rows,
+                      int64_t cols, SpecD sp) {
+  constexpr int VEC = TI<T>::VEC;
+  constexpr int BS = 128;
+  constexpr int VPR = BS / VEC;        // vectors per tile row
+  constexpr int RPP = 256 / VPR;       // rows per pass
+  constexpr int NP = BS / RPP;         // passes
+  __shared__ float red[64];
+  const int64_t ncb = (cols + BS - 1) / BS;
+  const int64_t bi = blockIdx.x / ncb, bj = blockIdx.x % ncb;
+  const int vr = threadIdx.x / VPR, vc = threadIdx.x % VPR;
+  const int64_t col = bj * BS + vc * VEC;
+  uint4 raw[NP];
+  bool ok[NP];
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    const int64_t row = bi * BS + p * RPP + vr;
+    ok[p] = (row < rows) && (col < cols);
+    if (ok[p]) raw[p] = ld_stream(in + row * cols + col);
+  }
+  float mx = 0.f;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    if (ok[p]) {
+      float f[VEC];
+      TI<T>::unpack(raw[p], f);
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) mx = max_nan(mx, fabsf(f[i]));
+    }
+  }
+  float mn = mx;
+  block_minmax(mx, mn, red);
+  UnitQ u;
+  qparams_from_range(mx, mx, sp, u);
+  finish_unit(sp, u);
+  if (!finite_f(mx)) u.exact = 1;
+  if (threadIdx.x == 0 && scales) store_rt(scales, blockIdx.x, u.s_out, sp.qparam_dtype);
+  if (sp.out_mode == LCB_OUT_NONE) return;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    if (ok[p]) {
+      const int64_t row = bi * BS + p * RPP + vr;
+      float f[VEC];
+      TI<T>::unpack(raw[p], f);
+      quant_store_vec<T, float, KINDC>(f, u, sp, out, row * cols + col);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// static qparams: elementwise
+// ------------------------------------------------------------------------------------------------
+template <typename T, typename M, int KINDC>
+__global__ void __launch_bounds__(256)
+    fq_static_kernel(const T* __restrict__ in, void* __restrict__ out, const void* __restrict__ scales,
+                     const void* __restrict__ zeros, int64_t rows, int64_t cols, int64_t ur, int64_t uc,
+                     SpecD sp) {
+  constexpr int VEC = TI<T>::VEC;
+  const int64_t vpr = cols / VEC;
+  const int64_t total = rows * vpr;
+  const int64_t ncu = (cols + uc - 1) / uc;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t v0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < total; v0 += 4 * stride) {
+    uint4 raw[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t v = v0 + k * stride;
+      if (v < total) raw[k] = ld_stream(in + v * VEC);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int64_t v = v0 + k * stride;
+      if (v >= total) continue;
+      const int64_t row = v / vpr, col = (v % vpr) * VEC;
+      const int64_t unit = (row / ur) * ncu + col / uc;
+      UnitQ u;
+      u.s = load_rt(scales, unit, sp.qparam_dtype);
+      u.z = (zeros && !sp.sym && sp.kind == LCB_KIND_INT) ? load_rt(zeros, unit, sp.qparam_dtype) : 0.f;
+      if (sp.kind != LCB_KIND_INT && u.s == 0.f) u.s = 1.f;
+      finish_unit(sp, u);
+      float f[VEC];
+      TI<T>::unpack(raw[k], f);
+      float am = 0.f;
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) am = max_nan(am, fabsf(f[i]));
+      if (!(__fmul_rn(am, u.r) < 1e30f)) u.exact = 1;
+      quant_store_vec<T, M, KINDC>(f, u, sp, out, v * VEC);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic: warp per 2-D unit, scalar accesses, literal arithmetic. Any shape, any alignment, any spec.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void store_scalar(void* out, int64_t e, float val, float code, const SpecD& sp) {
+  switch (sp.out_mode) {
+    case LCB_OUT_FAKE: TI<T>::store1(reinterpret_cast<T*>(out) + e, val); break;
+    case LCB_OUT_CODE_T: TI<T>::store1(reinterpret_cast<T*>(out) + e, code); break;
+    case LCB_OUT_I8: reinterpret_cast<int8_t*>(out)[e] = (int8_t)(int)code; break;
+    case LCB_OUT_U8: reinterpret_cast<uint8_t*>(out)[e] = (uint8_t)(int)code; break;
+    case LCB_OUT_I32: reinterpret_cast<int32_t*>(out)[e] = (int)code; break;
+    case LCB_OUT_FP8: reinterpret_cast<uint8_t*>(out)[e] = f32_to_fp8_byte(code, sp.kind); break;
+    default: break;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    fq_generic_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
+                      void* __restrict__ zeros, int64_t rows, int64_t cols, int64_t ur, int64_t uc, int dynamic,
+                      int abs_range, SpecD sp) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t nru = (rows + ur - 1) / ur, ncu = (cols + uc - 1) / uc;
+  sp.fast_ok = 0;
+  for (int64_t unit = warp; unit < nru * ncu; unit += nwarps) {
+    const int64_t r0 = (unit / ncu) * ur, c0 = (unit % ncu) * uc;
+    const int64_t nr = min(ur, rows - r0), nc = min(uc, cols - c0);
+    const int64_t n = nr * nc;
+    UnitQ u;
+    if (dynamic) {
+      float mx = -INFINITY, mn = INFINITY;
+      for (int64_t i = lane; i < n; i += 32) {
+        float x = TI<T>::load1(in + (r0 + i / nc) * cols + c0 + i % nc);
+        if (abs_range) x = fabsf(x);
+        mx = max_nan(mx, x);
+        mn = min_nan(mn, x);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      }
+      if (abs_range && (nr < ur || nc < uc)) mn = min_nan(mn, 0.f);  // zero padding (quant.py:637-638)
+      qparams_from_range(mn, mx, sp, u);
+      finish_unit(sp, u);
+      if (lane == 0) write_qparams(scales, zeros, unit, u, sp);
+    } else {
+      u.s = load_rt(scales, unit, sp.qparam_dtype);
+      u.z = (zeros && !sp.sym && sp.kind == LCB_KIND_INT) ? load_rt(zeros, unit, sp.qparam_dtype) : 0.f;
+      if (sp.kind != LCB_KIND_INT && u.s == 0.f) u.s = 1.f;
+      finish_unit(sp, u);
+    }
+    if (sp.out_mode == LCB_OUT_NONE) continue;
+    for (int64_t i = lane; i < n; i += 32) {
+      const int64_t e = (r0 + i / nc) * cols + c0 + i % nc;
+      float2 vc = fq_elem_literal(TI<T>::load1(in + e), u, sp);
+      store_scalar<T>(out, e, vc.x, vc.y, sp);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// per_tensor: phase 1 = grid min/max, finalize = qparams; phase 2 = fq_static_kernel
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) minmax_partial_kernel(const T* __restrict__ in, int64_t numel, float* ws) {
+  constexpr int VEC = TI<T>::VEC;
+  __shared__ float red[64];
+  const int64_t nvec = numel / VEC;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float mx = -INFINITY, mn = INFINITY;
+  for (int64_t v0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v0 < nvec; v0 += 4 * stride) {
+    uint4 raw[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (v0 + k * stride < nvec) raw[k] = *reinterpret_cast<const uint4*>(in + (v0 + k * stride) * VEC);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (v0 + k * stride < nvec) {
+        float f[VEC];
+        TI<T>::unpack(raw[k], f);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+          mx = max_nan(mx, f[i]);
+          mn = min_nan(mn, f[i]);
+        }
+      }
+  }
+  block_minmax(mx, mn, red);
+  if (threadIdx.x == 0) {
+    ws[2 * blockIdx.x] = mx;
+    ws[2 * blockIdx.x + 1] = mn;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    minmax_finalize_kernel(float* ws, int nparts, void* scales, void* zeros, SpecD sp) {
+  __shared__ float red[64];
+  float mx = -INFINITY, mn = INFINITY;
+  for (int i = threadIdx.x; i < nparts; i += blockDim.x) {
+    mx = max_nan(mx, ws[2 * i]);
+    mn = min_nan(mn, ws[2 * i + 1]);
+  }
+  block_minmax(mx, mn, red);
+  if (threadIdx.x == 0) {
+    UnitQ u;
+    qparams_from_range(mn, mx, sp, u);
+    finish_unit(sp, u);
+    float* q = ws + 2 * nparts;  // phase-2 qparams, fp32 (values already rounded to the math dtype)
+    q[0] = u.s;
+    q[1] = u.z;
+    sp.osf = 1.0f;  // user-visible scale is the un-factored one; phase 2 applies osf itself
+    write_qparams(scales, zeros, 0, u, sp);
+  }
+}
+
+}  // namespace lcb
+#include "fakequant_host.cuh"

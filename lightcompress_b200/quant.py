@@ -1,0 +1,495 @@
+"""Drop-in mirror of `llmc.compression.quantization.quant` for the B200 hot path.
+
+`IntegerQuantizer` / `FloatQuantizer` keep the reference's constructor kwargs, method names, argument
+meaning, return conventions and error behaviour (quant.py:46-1221) but every tensor pass runs in the
+hand-written sm_100a kernels behind the C ABI (include/lcb200.h). PyTorch is only used for device
+memory, views and the stream handle. There is no CPU / eager fallback: tensors must live on a CUDA
+device and the extension must be built.
+"""
+import torch
+
+from . import _cabi
+
+_DT = {torch.float32: _cabi.LCB_F32, torch.float16: _cabi.LCB_F16, torch.bfloat16: _cabi.LCB_BF16}
+_RANK = {torch.bfloat16: 0, torch.float16: 0, torch.float32: 1}
+
+
+def _promote(*dtypes):
+    """torch type promotion restricted to {bf16, f16, f32} for tensors with dim >= 1."""
+    kinds = set(dtypes)
+    if len(kinds) == 1:
+        return dtypes[0]
+    return torch.float32  # any f32 operand, or a bf16/f16 mix, promotes to f32
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(t, what):
+    if not t.is_cuda:
+        raise RuntimeError(f'{what}: tensor is on {t.device}; lightcompress_b200 has no CPU path '
+                           '(the sm_100a extension is the only implementation)')
+    if t.dtype not in _DT:
+        raise TypeError(f'{what}: unsupported dtype {t.dtype}')
+
+
+class _Units:
+    """How a tensor maps onto the [rows, cols] / unit_rows x unit_cols grid of lcb_fakequant."""
+    __slots__ = ('rows', 'cols', 'ur', 'uc', 'n_units', 'qshape')
+
+
+class BaseQuantizer(object):
+    """Mirror of quant.py:46-658 (ctor kwargs = the YAML `quant.weight|act` schema)."""
+
+    def __init__(self, bit, symmetric, granularity, **kwargs):
+        self.bit = bit
+        self.sym = symmetric
+        self.granularity = granularity
+        self.kwargs = kwargs
+        self.calib_algo = kwargs.get('calib_algo', 'minmax')
+        if granularity == 'per_group':
+            self.group_size = kwargs['group_size']
+        elif granularity == 'per_head':
+            self.head_num = kwargs['head_num']
+        elif granularity == 'per_block':
+            assert self.calib_algo == 'minmax' and self.sym
+            self.block_size = kwargs['block_size']
+        if kwargs.get('ste', False) or kwargs.get('ste_all', False):
+            raise NotImplementedError('straight-through estimators need autograd; not on the CUDA hot path')
+        self.round_func = torch.round
+        self.ste_all = False
+        self.round_zp = kwargs.get('round_zp', True)
+        self.mse_b_num = kwargs.get('mse_b_num', 1)
+        self.maxshrink = kwargs.get('maxshrink', 0.8)
+        self.mse_grid = kwargs.get('mse_grid', 100)
+        self.bins = kwargs.get('bins', 2048)
+
+    # ---- layout ---------------------------------------------------------------------------------
+    def _units(self, tensor):
+        u = _Units()
+        g = self.granularity
+        shape = tuple(tensor.shape)
+        numel = tensor.numel()
+        last = shape[-1] if len(shape) else 1
+        if g == 'per_group' and last >= self.group_size:
+            if last % self.group_size != 0:
+                raise ValueError(f'Dimension {last} not divisible by group size {self.group_size}')
+            u.rows, u.cols, u.ur, u.uc = numel // last, last, 1, self.group_size
+            u.qshape = (numel // self.group_size, 1)
+        elif g == 'per_head':
+            u.rows, u.cols = self.head_num, numel // self.head_num
+            u.ur, u.uc = 1, u.cols
+            u.qshape = (self.head_num, 1)
+        elif g == 'per_block':
+            assert len(shape) == 2, 'per_block expects a 2-D weight'
+            bs = self.block_size
+            u.rows, u.cols, u.ur, u.uc = shape[0], shape[1], bs, bs
+            u.qshape = (-(-shape[0] // bs), 1, -(-shape[1] // bs), 1)
+        elif g == 'per_tensor':
+            u.rows, u.cols = (numel // last, last) if numel else (0, 0)
+            u.ur, u.uc = max(u.rows, 1), max(u.cols, 1)
+            u.qshape = ()
+        else:  # per_channel / per_token / short per_group rows: one unit per last-dim row
+            u.rows, u.cols, u.ur, u.uc = (numel // last if last else 0), last, 1, max(last, 1)
+            u.qshape = shape[:-1] + (1,)
+        u.n_units = 1
+        for d in u.qshape:
+            u.n_units *= d
+        return u
+
+    def reshape_tensor(self, tensor, allow_padding=False):
+        """quant.py:612-642 (views only; per_block pads like the reference)."""
+        g = self.granularity
+        if g == 'per_group':
+            if tensor.shape[-1] >= self.group_size:
+                if tensor.shape[-1] % self.group_size != 0:
+                    raise ValueError(f'Dimension {tensor.shape[-1]} not divisible by group size {self.group_size}')
+                return tensor.reshape(-1, self.group_size)
+            return tensor
+        if g == 'per_head':
+            return tensor.reshape(self.head_num, -1)
+        if g == 'per_block':
+            bs = self.block_size
+            m, n = tensor.shape
+            mp, np_ = -(-m // bs) * bs, -(-n // bs) * bs
+            if (mp, np_) != (m, n):
+                t = tensor.new_zeros((mp, np_))
+                t[:m, :n] = tensor
+            else:
+                t = tensor
+            return t.view(-1, bs, np_ // bs, bs)
+        return tensor
+
+    def restore_tensor(self, tensor, shape):
+        """quant.py:644-658."""
+        if tensor.shape == shape:
+            return tensor
+        if self.granularity == 'per_block':
+            return tensor.reshape(-1, tensor.shape[2] * tensor.shape[3])[:shape[0], :shape[1]]
+        return tensor.reshape(shape)
+
+    # ---- the one kernel call ------------------------------------------------------------------------
+    def _spec(self, dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf=1.0, clip=1.0):
+        s = _cabi.QuantSpec()
+        s.dtype, s.math_dtype, s.qparam_dtype = _DT[dtype], _DT[math_dtype], _DT[qparam_dtype]
+        s.kind = self._kind()
+        s.sym = 1 if self.sym else 0
+        s.round_zp = 1 if self.round_zp else 0
+        s.out_mode = out_mode
+        s.qmin, s.qmax = float(qmin), float(qmax)
+        s.output_scale_factor = float(osf)
+        s.clip_ratio = float(clip)
+        return s
+
+    def _run(self, x, rows, cols, ur, uc, spec, dynamic, out=None, scales=None, zeros=None):
+        lib = _cabi.load()
+        ws = None
+        if dynamic and ur >= rows and uc >= cols:
+            ws = torch.empty(int(lib.lcb_fakequant_workspace_bytes()), dtype=torch.uint8, device=x.device)
+        st = lib.lcb_fakequant(
+            x.data_ptr(), out.data_ptr() if out is not None else None,
+            scales.data_ptr() if scales is not None else None,
+            zeros.data_ptr() if zeros is not None else None,
+            rows, cols, ur, uc, spec, 1 if dynamic else 0, ws.data_ptr() if ws is not None else None, _stream())
+        _cabi.check(st, 'lcb_fakequant')
+
+    def _math_dtype_dynamic(self, dtype):
+        return torch.float32 if self.granularity == 'per_block' else dtype
+
+    def _qrange(self):
+        return float(self.qmin), float(self.qmax)
+
+    def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0):
+        """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
+        _require_cuda(tensor, 'dynamic quant')
+        if self.calib_algo not in ('minmax',):
+            raise NotImplementedError(f'calib_algo={self.calib_algo!r} is not on the CUDA hot path (minmax only)')
+        x = tensor.contiguous()
+        u = self._units(x)
+        md = self._math_dtype_dynamic(x.dtype)
+        qmin, qmax = self._qrange()
+        spec = self._spec(x.dtype, md, md, out_mode, qmin, qmax, osf, clip)
+        out = torch.empty(x.shape, dtype=out_dtype, device=x.device) if out_mode != _cabi.OUT_NONE else None
+        scales = zeros = None
+        if want_qparams:
+            scales = torch.empty(u.qshape, dtype=md, device=x.device)
+            if not self.sym and self._kind() == _cabi.KIND_INT:
+                zeros = torch.empty(u.qshape, dtype=md, device=x.device)
+        with torch.cuda.device(x.device):
+            self._run(x, u.rows, u.cols, u.ur, u.uc, spec, True, out, scales, zeros)
+        return out, scales, zeros
+
+    def _static(self, tensor, scales, zeros, qmax, qmin, out_mode, out_dtype, osf=1.0, units=None):
+        _require_cuda(tensor, 'static quant')
+        x = tensor.contiguous()
+        u = units or self._units(x)
+        dts = [x.dtype]
+        if torch.is_tensor(scales) and scales.dim() > 0:
+            dts.append(scales.dtype)
+        zt = torch.is_tensor(zeros) and zeros.numel() > 1
+        if zt:
+            dts.append(zeros.dtype)
+        md = _promote(*dts)
+        scales = torch.as_tensor(scales, device=x.device)
+        if scales.numel() == 1 and u.n_units != 1:
+            u = _Units()
+            last = x.shape[-1]
+            u.rows, u.cols = x.numel() // last, last
+            u.ur, u.uc, u.n_units = u.rows, u.cols, 1
+        if scales.numel() != u.n_units:
+            raise ValueError(f'static qparams hold {scales.numel()} values, tensor has {u.n_units} units')
+        sc = scales.to(device=x.device, dtype=md).contiguous()
+        zp = None
+        if not self.sym and self._kind() == _cabi.KIND_INT and zeros is not None:
+            zp = torch.as_tensor(zeros, device=x.device).to(dtype=md)
+            if zp.numel() == 1 and u.n_units != 1:
+                zp = zp.expand(u.n_units)
+            zp = zp.contiguous()
+        qmin_f = float(qmin) if qmin is not None else float(self.qmin)
+        qmax_f = float(qmax) if qmax is not None else float(self.qmax)
+        spec = self._spec(x.dtype, md, md, out_mode, qmin_f, qmax_f, osf)
+        out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            self._run(x, u.rows, u.cols, u.ur, u.uc, spec, False, out, sc, zp)
+        return out
+
+    # ---- reference API ------------------------------------------------------------------------------
+    def get_tensor_qparams(self, tensor, args={}):
+        """quant.py:690-697 / :1043-1059 → (reshaped_tensor, scales, zeros, qmax, qmin)."""
+        _, scales, zeros, = self._dynamic(tensor, _cabi.OUT_NONE, None, True)
+        if zeros is None:
+            zeros = torch.tensor(0.0)
+        dev = tensor.device
+        return self.reshape_tensor(tensor), scales, zeros, self.qmax.to(dev), self.qmin.to(dev)
+
+    def get_minmax_range(self, tensor):
+        raise NotImplementedError('use get_tensor_qparams (range + qparams are fused in one kernel)')
+
+    def _bcast_units(self, tensor, scales):
+        """units for direct quant()/dequant()/quant_dequant() calls on already reshaped tensors."""
+        u = _Units()
+        n = scales.numel() if torch.is_tensor(scales) else 1
+        if tensor.dim() == 4 and torch.is_tensor(scales) and scales.dim() == 4:
+            rb, bs, cb, bs2 = tensor.shape
+            raise NotImplementedError('4-D per_block views: call the fake_quant_* / real_quant_* entry points')
+        last = tensor.shape[-1]
+        u.rows, u.cols = tensor.numel() // last, last
+        if n == 1:
+            u.ur, u.uc, u.n_units = u.rows, u.cols, 1
+        elif n == u.rows:
+            u.ur, u.uc, u.n_units = 1, u.cols, u.rows
+        else:
+            raise ValueError(f'cannot broadcast {n} qparams over tensor of shape {tuple(tensor.shape)}')
+        return u
+
+    def quant_dequant(self, tensor, scales, zeros, qmax, qmin, output_scale_factor=1):
+        """quant.py:714-717 on a reshaped [units, unit_len] tensor with [units, 1] (or scalar) qparams."""
+        md = _promote(tensor.dtype, *( [scales.dtype] if torch.is_tensor(scales) and scales.dim() > 0 else []))
+        x = tensor if md == tensor.dtype else tensor.to(md)
+        return self._static(x, scales, zeros, qmax, qmin, _cabi.OUT_FAKE, x.dtype, output_scale_factor,
+                            units=self._bcast_units(x, scales))
+
+    def quant(self, tensor, scales, zeros, qmax, qmin):
+        """quant.py:699-708: integer codes kept in the (promoted) floating dtype."""
+        md = _promote(tensor.dtype, *( [scales.dtype] if torch.is_tensor(scales) and scales.dim() > 0 else []))
+        x = tensor if md == tensor.dtype else tensor.to(md)
+        return self._static(x, scales, zeros, qmax, qmin, _cabi.OUT_CODE_T, x.dtype,
+                            units=self._bcast_units(x, scales))
+
+    # fake quant --------------------------------------------------------------------------------------
+    def _split_mixed(self, t, args, dim):
+        if 'int_indices' in args:
+            if self.granularity == 'per_group':
+                assert len(args['int_indices']) % self.group_size == 0
+            return t.index_select(dim, torch.as_tensor(args['int_indices'], device=t.device))
+        return None
+
+    def _fake_dynamic(self, tensor, args, is_weight):
+        org_bit = None
+        if 'current_bit' in args:
+            org_bit, self.bit = self.bit, args['current_bit']
+            self._set_int_range()
+        try:
+            dim = 1 if is_weight else 2
+            sub = self._split_mixed(tensor, args, dim)
+            if sub is not None:
+                q, _, _ = self._dynamic(sub, _cabi.OUT_FAKE, sub.dtype, False)
+                mix = tensor.clone()
+                mix.index_copy_(dim, torch.as_tensor(args['int_indices'], device=tensor.device), q)
+                return mix
+            if is_weight and 'dim' in args and 'ic' in args['dim']:
+                q, _, _ = self._dynamic(tensor.T, _cabi.OUT_FAKE, tensor.dtype, False)
+                return q.T
+            q, _, _ = self._dynamic(tensor, _cabi.OUT_FAKE, tensor.dtype, False)
+            return q
+        finally:
+            if org_bit is not None:
+                self.bit = org_bit
+                self._set_int_range()
+
+    def _fake_static(self, tensor, args, is_weight):
+        if 'rounding' in args:
+            raise NotImplementedError("args['rounding'] (AdaRound-style floor+offset) is not on the CUDA hot path")
+        osf = args.get('output_scale_factor', 1) if is_weight else 1
+        dim = 1 if is_weight else 2
+        sub = self._split_mixed(tensor, args, dim)
+        if sub is not None:
+            q = self._static(sub, args['scales'], args['zeros'], args['qmax'], args['qmin'], _cabi.OUT_FAKE,
+                             sub.dtype, osf)
+            mix = tensor.clone()
+            mix.index_copy_(dim, torch.as_tensor(args['int_indices'], device=tensor.device), q)
+            return mix
+        if is_weight and 'dim' in args and 'ic' in args['dim']:
+            return self._static(tensor.T, args['scales'], args['zeros'], args['qmax'], args['qmin'],
+                                _cabi.OUT_FAKE, tensor.dtype, osf).T
+        return self._static(tensor, args['scales'], args['zeros'], args['qmax'], args['qmin'], _cabi.OUT_FAKE,
+                            tensor.dtype, osf)
+
+    def fake_quant_weight_dynamic(self, weight, args={}):
+        """quant.py:833-869 / :1142-1159."""
+        return self._fake_dynamic(weight, args, True)
+
+    def fake_quant_act_dynamic(self, act, args={}):
+        """quant.py:754-783 / :1100-1109."""
+        return self._fake_dynamic(act, args, False)
+
+    def fake_quant_weight_static(self, weight, args):
+        """quant.py:785-831 / :1111-1140."""
+        return self._fake_static(weight, args, True)
+
+    def fake_quant_act_static(self, act, args={}):
+        """quant.py:719-752 / :1083-1098."""
+        return self._fake_static(act, args, False)
+
+    def _set_int_range(self):
+        pass
+
+    def _qparams_view(self, scales, zeros, weight):
+        if self.granularity == 'per_tensor':
+            shape = (1,)
+        elif self.granularity == 'per_block':
+            shape = (scales.shape[0], scales.shape[2])
+        else:
+            shape = (weight.shape[0], -1)
+        return scales.view(shape), (zeros.view(shape) if zeros is not None else None)
+
+
+class IntegerQuantizer(BaseQuantizer):
+    """Mirror of quant.py:661-960."""
+
+    def __init__(self, bit, symmetric, granularity, **kwargs):
+        super().__init__(bit, symmetric, granularity, **kwargs)
+        self.quant_type = 'int-quant'
+        self._set_int_range()
+        self.dst_nbins = 2 ** bit
+
+    def _kind(self):
+        return _cabi.KIND_INT
+
+    def _set_int_range(self):
+        # quant.py:665-677 — note the asymmetric qmin is the *float* 0.0, qmax an int (kept for drop-in parity)
+        if 'int_range' in self.kwargs:
+            lo, hi = self.kwargs['int_range'][0], self.kwargs['int_range'][1]
+        elif self.sym:
+            lo, hi = -(2 ** (self.bit - 1)), 2 ** (self.bit - 1) - 1
+        else:
+            lo, hi = 0.0, 2 ** self.bit - 1
+        self.qmin = torch.tensor(lo)
+        self.qmax = torch.tensor(hi)
+
+    def dequant(self, tensor, scales, zeros):
+        raise NotImplementedError('dequant alone is not a hot-path entry; use quant_dequant / fake_quant_*')
+
+    def _code_dtype(self):
+        # quant.py:929-936: bit 8 -> int8 (uint8 when qmin == 0); anything else -> unpacked int32
+        if self.bit == 8:
+            return (torch.int8, _cabi.OUT_I8) if self.qmin != 0 else (torch.uint8, _cabi.OUT_U8)
+        return torch.int32, _cabi.OUT_I32
+
+    def real_quant_weight_dynamic(self, weight, args={}):
+        """quant.py:916-953 → (codes, scales, zeros|None)."""
+        osf = 1
+        if 'output_scale_factor' in args:
+            osf = args['output_scale_factor']
+            del args['output_scale_factor']
+        dtype, mode = self._code_dtype()
+        codes, scales, zeros = self._dynamic(weight, mode, dtype, True, osf=osf)
+        if not self.sym and self.round_zp:
+            zeros = zeros.to(dtype)
+        elif self.sym:
+            zeros = None
+        scales, zeros = self._qparams_view(scales, zeros, codes)
+        return codes, scales, zeros
+
+    def real_quant_weight_static(self, weight, args):
+        """quant.py:871-914."""
+        osf = 1
+        if 'output_scale_factor' in args:
+            osf = args['output_scale_factor']
+            del args['output_scale_factor']
+        dtype, mode = self._code_dtype()
+        scales, zeros = args['scales'], args['zeros']
+        codes = self._static(weight, scales, zeros, args['qmax'], args['qmin'], mode, dtype)
+        scales = scales * osf
+        if not self.sym and self.round_zp:
+            zeros = zeros.to(dtype)
+        elif self.sym:
+            zeros = None
+        scales, zeros = self._qparams_view(scales, zeros, codes)
+        return codes, scales, zeros
+
+    def __repr__(self):
+        return (f'IntegerQuantizer(bit={self.bit}, sym={self.sym},granularity={self.granularity},'
+                f'kwargs={self.kwargs}, qmin={self.qmin}, qmax={self.qmax})')
+
+
+class FloatQuantizer(BaseQuantizer):
+    """Mirror of quant.py:963-1229 for the scale-based (`use_qtorch: True`) FP8 formats.
+
+    Rounding is fp32 -> fp8 round-to-nearest-even (the rounding of `Tensor.to(torch.float8_*)`, which ends
+    every reference real-quant call, quant.py:1183/1211, and of the reference's own Triton path,
+    kernel.py:8-83). qtorch itself is an un-vendored dependency: parity unpinned for its tie rule, see
+    DESIGN.md.
+    """
+
+    def __init__(self, bit, symmetric, granularity, **kwargs):
+        super().__init__(bit, symmetric, granularity, **kwargs)
+        self.sym = True
+        self.quant_type = 'float-quant'
+        self.e_bits = int(self.bit[1])
+        self.m_bits = int(self.bit[-1])
+        self.sign_bits = 1
+        self.num_bits = self.e_bits + self.m_bits + self.sign_bits
+        self.default_bias = 2 ** (self.e_bits - 1)
+        self.dst_nbins = 2 ** self.num_bits
+        self.use_qtorch = kwargs.get('use_qtorch')
+        if self.bit not in ('e4m3', 'e5m2'):
+            raise NotImplementedError('Only FP8 E4M3 / E5M2 are on the CUDA hot path')
+        if not self.use_qtorch:
+            raise NotImplementedError('per-element power-of-two float scales (use_qtorch unset, '
+                                      'quant.py:1005-1027) are not on the CUDA hot path')
+        if 'float_range' in kwargs:
+            self.qmin, self.qmax = kwargs['float_range']
+        else:
+            finfo = torch.finfo(torch.float8_e4m3fn if self.e_bits == 4 else torch.float8_e5m2)
+            self.qmin, self.qmax = finfo.min, finfo.max
+        self.qmax = torch.tensor(self.qmax)
+        self.qmin = torch.tensor(self.qmin)
+
+    def _kind(self):
+        return _cabi.KIND_FP8_E4M3 if self.e_bits == 4 else _cabi.KIND_FP8_E5M2
+
+    def _fp8_dtype(self):
+        return torch.float8_e4m3fn if self.e_bits == 4 else torch.float8_e5m2
+
+    def quant_dequant(self, tensor, scales, zeros, qmax, qmin):
+        return super().quant_dequant(tensor, scales, zeros, qmax, qmin)
+
+    def real_quant_weight_dynamic(self, weight, args={}):
+        """quant.py:1195-1221 → (fp8 codes, scales, None)."""
+        assert self.bit in ['e4m3', 'e5m2'], 'Only FP8 E4M3 and E5M2 support real quant'
+        osf = 1
+        if 'output_scale_factor' in args:
+            osf = args['output_scale_factor']
+            del args['output_scale_factor']
+        codes, scales, _ = self._dynamic(weight, _cabi.OUT_FP8, torch.uint8, True, osf=osf)
+        scales, _ = self._qparams_view(scales, None, codes)
+        return codes.view(self._fp8_dtype()), scales, None
+
+    def real_quant_weight_static(self, weight, args):
+        """quant.py:1161-1193."""
+        assert self.bit in ['e4m3', 'e5m2'], 'Only FP8 E4M3 and E5M2 support real quant'
+        osf = 1
+        if 'output_scale_factor' in args:
+            osf = args['output_scale_factor']
+            del args['output_scale_factor']
+        scales = args['scales']
+        codes = self._static(weight, scales, None, args['qmax'], args['qmin'], _cabi.OUT_FP8, torch.uint8)
+        scales, _ = self._qparams_view(scales * osf, None, codes)
+        return codes.view(self._fp8_dtype()), scales, None
+
+    def __repr__(self):
+        return (f'FloatQuantizer(bit={self.bit},e_bits={self.e_bits}, m_bits={self.m_bits},'
+                f'granularity={self.granularity},kwargs={self.kwargs}, qmin={self.qmin}, qmax={self.qmax})')
+
+
+def weight_cast_to_fp8(weight, block_size):
+    """quant.py:34-43 / kernel.py:73-83: per-block e4m3 codes + fp32 scales [ceil(R/bs), ceil(C/bs)]."""
+    q = FloatQuantizer(bit='e4m3', symmetric=True, granularity='per_block', block_size=block_size, use_qtorch=True)
+    codes, scales, _ = q.real_quant_weight_dynamic(weight)
+    return codes, scales
+
+
+def weight_cast_to_bf16(weight, scale, block_size):
+    """quant.py:18-31 / kernel.py:115-138: y = fp8 * s[block] -> bf16."""
+    _require_cuda(scale, 'weight_cast_to_bf16')
+    lib = _cabi.load()
+    w = weight.contiguous()
+    out = torch.empty(w.shape, dtype=torch.bfloat16, device=w.device)
+    kind = _cabi.KIND_FP8_E4M3 if w.dtype == torch.float8_e4m3fn else _cabi.KIND_FP8_E5M2
+    with torch.cuda.device(w.device):
+        st = lib.lcb_fp8_block_dequant(w.data_ptr(), scale.float().contiguous().data_ptr(), out.data_ptr(),
+                                       w.shape[0], w.shape[1], block_size, kind, _cabi.LCB_BF16, _stream())
+    _cabi.check(st, 'lcb_fp8_block_dequant')
+    return out

@@ -1,0 +1,5 @@
+"""CPU oracle of the LLMC quantization hot path — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+package. The product (lightcompress_b200/) never does.
+"""
