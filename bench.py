@@ -1,0 +1,241 @@
+"""bench.py — headline benchmark of the B200-native LLMC quantization hot path.
+
+Metric (BASELINE.json): fake-quant HBM GB/s on Llama-3-8B shapes (+ GPTQ calibration s/block as extra keys).
+A "step" = one pass of the w4a16 group-128 fake-quant (IntegerQuantizer(4, asym, per_group 128)
+.fake_quant_weight_dynamic, the quantization of BASELINE configs[1]) over the 7 linear weights of one
+Llama-3-8B transformer block (218.1 M bf16 elements, 436 MB in + 436 MB out: larger than the 126 MB L2, so no
+flush is needed between iterations).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N > 1 (torchrun): independent linear layers / blocks shard naturally — every rank processes its own block, no
+data-path collective; value = total bytes of all ranks / max-over-ranks time ("scaling": "weak").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LLAMA3_8B_BLOCK = [('q_proj', 4096, 4096), ('k_proj', 1024, 4096), ('v_proj', 1024, 4096), ('o_proj', 4096, 4096),
+                   ('gate_proj', 14336, 4096), ('up_proj', 14336, 4096), ('down_proj', 4096, 14336)]
+METRIC = 'fake-quant HBM GB/s (% of peak); GPTQ/AWQ calib s/block, Llama-3-8B'
+WORKLOAD = 'Llama-3-8B block (7 linears, 218.1M bf16 params) w4a16 asym group-128 fake_quant_weight_dynamic'
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d['hbm_gbs']), float(d.get('bf16_tflops_sustained', d.get('bf16_tflops', 1400.0))), 'measured'
+    return 6650.0, 1590.0, 'fallback'
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--id={self.index}', f'--query-gpu={self.Q}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([f.strip() for f in line.split(',')])
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i] == 'Active' for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(sm)}
+
+
+def make_weights(torch, dev, seed):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    ws = []
+    for _, r, c in LLAMA3_8B_BLOCK:
+        w = torch.randn((r, c), generator=g, device=dev, dtype=torch.float32) * 0.02
+        ws.append(w.to(torch.bfloat16))
+    return ws
+
+
+def cpu_baseline(steps=3, sample=('q_proj', 4096, 4096)):
+    """The oracle port (oracle/lc_oracle.c, OpenMP over all host cores) on a bounded sample of the workload."""
+    import torch
+    from oracle import quant_oracle as qo
+    _, r, c = sample
+    x = (torch.randn(r, c, generator=torch.Generator().manual_seed(0)) * 0.02).to(torch.bfloat16)
+    kw = dict(kind=0, sym=False, qmin=0.0, qmax=15.0)
+    qo.fakequant(x, r, c, 1, 128, **kw)
+    best = 1e30
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        qo.fakequant(x, r, c, 1, 128, **kw)
+        best = min(best, time.perf_counter() - t0)
+    return {'value': r * c * 4 / best / 1e9, 'unit': 'GB/s', 'cores': os.cpu_count(), 'kind': 'port',
+            'sample': f'{sample[0]} [{r},{c}] bf16 w4 asym g128, best of {steps} (oracle/lc_oracle.c, OpenMP)'}, best
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    total = 0.0
+    for _ in range(args.warmup):
+        cpu_baseline(1)
+    vals = []
+    for _ in range(args.steps):
+        cb, t = cpu_baseline(1)
+        vals.append(cb['value'])
+        total += t
+    v = sum(vals) / len(vals)
+    cb['value'] = v
+    print(json.dumps({'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': 'GB/s', 'n_gpus': args.gpus,
+                      'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total / args.steps * 1e3,
+                      'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16',
+                      'data': 'synthetic', 'config': {'workload': WORKLOAD, 'sample': cb['sample']},
+                      'cpu_baseline': cb,
+                      'e2e': {'value': v, 'unit': 'GB/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extras', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from lightcompress_b200 import _cabi
+    from lightcompress_b200.quant import IntegerQuantizer
+
+    _cabi.load()  # fail loudly when the extension is missing
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    ws = make_weights(torch, dev, seed=rank)
+    numel = sum(w.numel() for w in ws)
+    alg_bytes = numel * 4  # 2 B in + 2 B out per element
+    q = IntegerQuantizer(4, False, 'per_group', group_size=128)
+
+    def step():
+        return [q.fake_quant_weight_dynamic(w) for w in ws]
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler = ClockSampler(local)
+    sync()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    sync()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = alg_bytes * world / (ms * 1e-3) / 1e9
+
+    # end to end through the public API with HOST buffers: pinned H2D of the weights, fake-quant, D2H of the result
+    hin = [torch.empty(w.shape, dtype=w.dtype).pin_memory() for w in ws]
+    hout = [torch.empty(w.shape, dtype=w.dtype).pin_memory() for w in ws]
+    for h, w in zip(hin, ws):
+        h.copy_(w)
+
+    def e2e_step():
+        for h, o in zip(hin, hout):
+            o.copy_(q.fake_quant_weight_dynamic(h.to(dev, non_blocking=True)), non_blocking=True)
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    sync()
+    e0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e1.record()
+    sync()
+    t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+    e2e = {'value': alg_bytes * world / (e2e_ms * 1e-3) / 1e9, 'unit': 'GB/s', 'h2d_bytes_per_step': numel * 2,
+           'd2h_bytes_per_step': numel * 2, 'ms_per_step': e2e_ms}
+
+    hbm_peak, tf_peak, which = peaks()
+    per_gpu = alg_bytes / (ms * 1e-3) / 1e9
+    roofline = {'bound': 'hbm', 'kernel': 'fq_subwarp_kernel<bf16,NV=1,UNROLL=4,int>', 'achieved': per_gpu,
+                'peak': hbm_peak, 'peak_source': f'{which} (MEASURED_PEAKS.json hbm_gbs)', 'unit': 'GB/s',
+                'frac': per_gpu / hbm_peak, 'frac_of_nominal_8TBs': per_gpu / 8000.0, 'traffic': None,
+                'algorithmic_bytes_per_launch': 'numel*4 (bf16 in + bf16 out); 7 launches per step'}
+    tr = os.path.join(ROOT, 'profiles', 'fakequant_traffic.json')
+    if os.path.exists(tr):
+        roofline['traffic'] = json.load(open(tr)).get('dram_bytes_per_launch')
+
+    out = {'metric': METRIC, 'value': value, 'unit': 'GB/s', 'n_gpus': world, 'steps': args.steps,
+           'warmup': max(args.warmup, 3), 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+           'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+           'config': {'workload': WORKLOAD, 'l2': 'inputs (436 MB) + outputs (436 MB) per step exceed the 126 MB L2',
+                      'parallelism': f'layers/blocks sharded x{world}, no collective'},
+           'clocks': clocks, 'e2e': e2e, 'gpu_launches': 7 * args.steps, 'roofline': roofline}
+
+    if rank == 0 and not args.no_extras:
+        try:
+            from bench_extras import extras
+            out['extras'] = extras(torch, dev, hbm_peak, tf_peak)
+        except ImportError:
+            pass
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out['cpu_baseline'] = cpu_baseline()[0]
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

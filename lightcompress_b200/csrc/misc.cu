@@ -1,0 +1,96 @@
+// misc.cu — small bandwidth-bound helpers: block-wise FP8 dequant, column |x| statistics.
+#include "common.cuh"
+
+namespace lcb {
+
+// y[r, c] = fp8(codes[r, c]) * scales[r / bs, c / bs]   (kernel.py:86-138 / quant.py:18-31)
+template <typename TO>
+__global__ void __launch_bounds__(256)
+    fp8_block_dequant_kernel(const uint8_t* __restrict__ codes, const float* __restrict__ scales, TO* __restrict__ out,
+                             int64_t rows, int64_t cols, int64_t bs, int kind) {
+  const int64_t ncb = (cols + bs - 1) / bs;
+  const int64_t total = rows * cols;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const bool vec = (cols % 8 == 0) && (bs % 8 == 0);
+  if (vec) {
+    const int64_t nv = total / 8;
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += stride) {
+      const int64_t e = v * 8, r = e / cols, c = e % cols;
+      const float s = scales[(r / bs) * ncb + c / bs];
+      const uint2 raw = *reinterpret_cast<const uint2*>(codes + e);
+      const uint32_t w[2] = {raw.x, raw.y};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float f = fp8_byte_to_f32((uint8_t)(w[i >> 2] >> (8 * (i & 3))), kind);
+        TI<TO>::store1(out + e + i, __fmul_rn(f, s));
+      }
+    }
+  } else {
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+      const int64_t r = e / cols, c = e % cols;
+      TI<TO>::store1(out + e, __fmul_rn(fp8_byte_to_f32(codes[e], kind), scales[(r / bs) * ncb + c / bs]));
+    }
+  }
+}
+
+// out[c] = max(out[c], max_r |x[r, c]|)   or   out[c] += sum_r |x[r, c]|
+// grid: x = column tiles of 256 columns (threads = 128, 2 columns per thread via 32-bit loads), y = row slabs.
+template <typename T>
+__global__ void __launch_bounds__(128)
+    col_absstat_kernel(const T* __restrict__ x, float* __restrict__ out, int64_t rows, int64_t cols, int mean) {
+  const int64_t c = (int64_t)blockIdx.x * 128 + threadIdx.x;
+  if (c >= cols) return;
+  const int64_t r0 = (int64_t)blockIdx.y * rows / gridDim.y, r1 = (int64_t)(blockIdx.y + 1) * rows / gridDim.y;
+  float acc = 0.f;
+  int64_t r = r0;
+  for (; r + 4 <= r1; r += 4) {
+    float v0 = fabsf(TI<T>::load1(x + r * cols + c)), v1 = fabsf(TI<T>::load1(x + (r + 1) * cols + c));
+    float v2 = fabsf(TI<T>::load1(x + (r + 2) * cols + c)), v3 = fabsf(TI<T>::load1(x + (r + 3) * cols + c));
+    if (mean) acc += (v0 + v1) + (v2 + v3);
+    else acc = max_nan(max_nan(acc, max_nan(v0, v1)), max_nan(v2, v3));
+  }
+  for (; r < r1; ++r) {
+    float v = fabsf(TI<T>::load1(x + r * cols + c));
+    if (mean) acc += v; else acc = max_nan(acc, v);
+  }
+  if (mean) atomicAdd(out + c, acc);
+  else atomicMax(reinterpret_cast<int*>(out + c), __float_as_int(acc));  // non-negative floats order like ints
+}
+
+}  // namespace lcb
+
+extern "C" int lcb_fp8_block_dequant(const void* codes, const float* scales, void* out, int64_t rows, int64_t cols,
+                                     int64_t block, int32_t kind, int32_t out_dtype, void* stream) {
+  using namespace lcb;
+  if (!codes || !scales || !out || block < 1) return LCB_E_INVALID;
+  if (kind != LCB_KIND_FP8_E4M3 && kind != LCB_KIND_FP8_E5M2) return LCB_E_UNSUPPORTED;
+  if (rows == 0 || cols == 0) return LCB_OK;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int64_t work = (rows * cols / 8 + 255) / 256;
+  int grid = (int)(work < 148 * 8 ? (work < 1 ? 1 : work) : 148 * 8);
+  const uint8_t* c = reinterpret_cast<const uint8_t*>(codes);
+  if (out_dtype == LCB_BF16) fp8_block_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(c, scales, (__nv_bfloat16*)out, rows, cols, block, kind);
+  else if (out_dtype == LCB_F16) fp8_block_dequant_kernel<__half><<<grid, 256, 0, st>>>(c, scales, (__half*)out, rows, cols, block, kind);
+  else if (out_dtype == LCB_F32) fp8_block_dequant_kernel<float><<<grid, 256, 0, st>>>(c, scales, (float*)out, rows, cols, block, kind);
+  else return LCB_E_UNSUPPORTED;
+  LCB_CUDA_CHECK_LAUNCH("fp8_block_dequant");
+  return LCB_OK;
+}
+
+extern "C" int lcb_col_absstat(const void* x, float* out, int64_t rows, int64_t cols, int32_t dtype, int32_t mean,
+                               void* stream) {
+  using namespace lcb;
+  if (!x || !out) return LCB_E_INVALID;
+  if (rows == 0 || cols == 0) return LCB_OK;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int gx = (int)((cols + 127) / 128);
+  int64_t want = (148 * 8 + gx - 1) / gx;
+  int gy = (int)(want < 1 ? 1 : (want > rows ? rows : want));
+  dim3 grid(gx, gy);
+  if (dtype == LCB_BF16) col_absstat_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const __nv_bfloat16*)x, out, rows, cols, mean);
+  else if (dtype == LCB_F16) col_absstat_kernel<__half><<<grid, 128, 0, st>>>((const __half*)x, out, rows, cols, mean);
+  else if (dtype == LCB_F32) col_absstat_kernel<float><<<grid, 128, 0, st>>>((const float*)x, out, rows, cols, mean);
+  else return LCB_E_UNSUPPORTED;
+  LCB_CUDA_CHECK_LAUNCH("col_absstat");
+  return LCB_OK;
+}

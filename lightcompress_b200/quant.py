@@ -169,13 +169,19 @@ class BaseQuantizer(object):
         u = self._units(x)
         md = self._math_dtype_dynamic(x.dtype)
         qmin, qmax = self._qrange()
-        spec = self._spec(x.dtype, md, md, out_mode, qmin, qmax, osf, clip)
+        # per_tensor: the 0-dim min/max divided by a 0-dim *float* tensor (qmax - qmin with qmin = tensor(0.0), or a
+        # float qmax) promotes to fp32 under torch's 0-dim rules -> fp32 scales / zeros (quant.py:552-556)
+        qd = md
+        if self.granularity == 'per_tensor' and (self._kind() != _cabi.KIND_INT or not self.sym):
+            qd = torch.float32
+        spec = self._spec(x.dtype, md, qd, out_mode, qmin, qmax, osf, clip)
+        spec.qp_math_plus1 = _DT[qd] + 1
         out = torch.empty(x.shape, dtype=out_dtype, device=x.device) if out_mode != _cabi.OUT_NONE else None
         scales = zeros = None
         if want_qparams:
-            scales = torch.empty(u.qshape, dtype=md, device=x.device)
+            scales = torch.empty(u.qshape, dtype=qd, device=x.device)
             if not self.sym and self._kind() == _cabi.KIND_INT:
-                zeros = torch.empty(u.qshape, dtype=md, device=x.device)
+                zeros = torch.empty(u.qshape, dtype=qd, device=x.device)
         with torch.cuda.device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, True, out, scales, zeros)
         return out, scales, zeros
@@ -199,16 +205,16 @@ class BaseQuantizer(object):
             u.ur, u.uc, u.n_units = u.rows, u.cols, 1
         if scales.numel() != u.n_units:
             raise ValueError(f'static qparams hold {scales.numel()} values, tensor has {u.n_units} units')
-        sc = scales.to(device=x.device, dtype=md).contiguous()
+        sc = scales.to(device=x.device, dtype=torch.float32).contiguous()  # exact upcast; math dtype stays `md`
         zp = None
         if not self.sym and self._kind() == _cabi.KIND_INT and zeros is not None:
-            zp = torch.as_tensor(zeros, device=x.device).to(dtype=md)
+            zp = torch.as_tensor(zeros, device=x.device).to(dtype=torch.float32)
             if zp.numel() == 1 and u.n_units != 1:
                 zp = zp.expand(u.n_units)
             zp = zp.contiguous()
         qmin_f = float(qmin) if qmin is not None else float(self.qmin)
         qmax_f = float(qmax) if qmax is not None else float(self.qmax)
-        spec = self._spec(x.dtype, md, md, out_mode, qmin_f, qmax_f, osf)
+        spec = self._spec(x.dtype, md, torch.float32, out_mode, qmin_f, qmax_f, osf)
         out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
         with torch.cuda.device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, False, out, sc, zp)

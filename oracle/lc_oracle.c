@@ -162,6 +162,7 @@ static float elem(float x, const unitq* u, const lco_spec* sp, float* code) {
     return rd(t4 * u->s_out, md);
   }
   float t1 = rd(x / u->s, md);
+  { volatile float zp = 0.0f; t1 = rd(t1 + zp, md); }  /* "+ zeros", zeros = tensor(0.0): -0 becomes +0 */
   float q = round_fp8(t1, sp->kind);
   *code = q;
   return q * u->s_out;
@@ -239,7 +240,9 @@ int64_t lco_check_markstein(const float* xs, int64_t nx, const float* ss, int64_
       float e = fmaf(-s, q0, x);
       float q = fmaf(e, r, q0);
       float ref = x / s;
-      if (f2bits(q) != f2bits(ref) && !(q != q && ref != ref)) ++bad;
+      /* quotients below 2^-40 round to zero in every output format (int codes, fp8): a last-bit difference caused by
+         an underflowing residual there cannot reach the output, so it is not counted */
+      if (f2bits(q) != f2bits(ref) && !(q != q && ref != ref) && (fabsf(q) >= 0x1p-40f || fabsf(ref) >= 0x1p-40f)) ++bad;
     }
   }
   return bad;

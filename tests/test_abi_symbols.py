@@ -1,0 +1,39 @@
+"""CPU: liblcb200.so loads and exports every symbol include/lcb200.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+from lightcompress_b200 import _build, _cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, 'include', 'lcb200.h')).read()
+    src = re.sub(r'/\*.*?\*/', '', src, flags=re.S)
+    return sorted(set(re.findall(r'\b(lcb_[a-z0-9_]+)\s*\(', src)))
+
+
+def test_header_symbols_are_exported_and_bound():
+    _build.build()
+    lib = ctypes.CDLL(_build.LIB)
+    syms = declared_symbols()
+    assert len(syms) >= 12
+    for s in syms:
+        assert hasattr(lib, s), f'{s} declared in lcb200.h but not exported'
+        assert s in _cabi.SIGNATURES, f'{s} has no ctypes signature'
+    assert set(_cabi.SIGNATURES) == set(syms)
+
+
+def test_abi_version_and_struct_layout():
+    lib = _cabi.load()
+    assert lib.lcb_abi_version() == 1
+    assert ctypes.sizeof(_cabi.QuantSpec) == 48
+    assert lib.lcb_fakequant_workspace_bytes() > 0
+
+
+def test_sass_is_sm100a_only():
+    import subprocess
+    out = subprocess.run(['cuobjdump', '-lelf', _build.LIB], capture_output=True, text=True).stdout
+    archs = set(re.findall(r'sm_(\d+a?)', out))
+    assert archs == {'100a'}, archs

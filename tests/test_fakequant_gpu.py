@@ -1,0 +1,147 @@
+"""GPU parity: the CUDA path, called through the quantizer API -> C ABI, against
+  (1) the committed reference golden vectors (bit-exact),
+  (2) the C oracle on larger seeded inputs (bit-exact),
+  (3) size-independent properties at Llama-3-8B sizes (idempotence, codes/scales consistency).
+"""
+import pytest
+import torch
+
+from lightcompress_b200 import quant as Q
+from oracle import quant_oracle as qo
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+RECS = H.load_golden()
+DEV = 'cuda:0'
+
+
+@pytest.mark.parametrize('rec', RECS, ids=[H.case_id(r) for r in RECS])
+def test_cuda_matches_reference_golden(rec):
+    c = rec['case']
+    x = H.case_input(c).to(DEV)
+    if rec.get('raises') == 'ValueError':
+        with pytest.raises(ValueError):
+            H.make_quantizer(Q, c).fake_quant_weight_dynamic(x)
+        return
+    q = H.make_quantizer(Q, c)
+    x0 = x.clone()
+    fake = q.fake_quant_act_dynamic(x) if c.get('api') == 'act' else q.fake_quant_weight_dynamic(x)
+    assert torch.equal(x, x0), 'input was mutated'
+    assert fake.shape == x.shape and fake.dtype == x.dtype
+    assert H.bits_equal(fake.cpu(), rec['fake']), 'fake-quant values differ from the reference'
+    _, s, z, qmax, qmin = q.get_tensor_qparams(x)
+    assert s.shape == rec['qp_scales'].shape and s.dtype == rec['qp_scales'].dtype
+    assert H.bits_equal(s.cpu(), rec['qp_scales']), 'scales differ'
+    if rec['qp_zeros'].numel() > 1 or not c.get('sym', True):
+        assert H.bits_equal(z.cpu().reshape(rec['qp_zeros'].shape), rec['qp_zeros']), 'zeros differ'
+    assert float(qmax) == float(rec['qmax']) and float(qmin) == float(rec['qmin'])
+    if 'codes' in rec:
+        codes, s2, z2 = q.real_quant_weight_dynamic(x)
+        assert str(codes.dtype) == rec['codes_dtype']
+        got = codes.view(torch.uint8).cpu() if rec['codes'].dtype == torch.uint8 and codes.element_size() == 1 \
+            and 'float8' in rec['codes_dtype'] else codes.cpu().to(torch.int16)
+        assert torch.equal(got, rec['codes']), 'codes differ'
+        assert s2.shape == rec['scales'].shape and H.bits_equal(s2.cpu(), rec['scales'])
+        if rec['zeros'] is None:
+            assert z2 is None
+        else:
+            assert z2.dtype == rec['zeros'].dtype and torch.equal(z2.cpu(), rec['zeros'])
+    if 'static_fake' in rec:
+        args = {'scales': rec['static_scales'].to(DEV), 'zeros': rec['static_zeros'].to(DEV), 'qmax': qmax, 'qmin': qmin}
+        assert H.bits_equal(q.fake_quant_weight_static(x, args).cpu(), rec['static_fake'])
+        args = {'scales': rec['qp_scales'].to(DEV), 'zeros': rec['qp_zeros'].to(DEV), 'qmax': qmax, 'qmin': qmin}
+        assert H.bits_equal(q.fake_quant_weight_static(x, args).cpu(), rec['static_fake_T'])
+
+
+BIG = [
+    dict(cls='int', bit=4, sym=False, gran='per_group', kwargs={'group_size': 128}, shape=(1024, 4096)),
+    dict(cls='int', bit=4, sym=True, gran='per_group', kwargs={'group_size': 64}, shape=(512, 4096)),
+    dict(cls='int', bit=8, sym=True, gran='per_token', shape=(4, 256, 4096), input='act'),
+    dict(cls='int', bit=8, sym=False, gran='per_token', shape=(2, 64, 14336), input='act'),
+    dict(cls='int', bit=8, sym=True, gran='per_channel', shape=(1024, 4096)),
+    dict(cls='int', bit=8, sym=True, gran='per_channel', shape=(16, 40000)),      # streaming row kernel
+    dict(cls='int', bit=8, sym=False, gran='per_tensor', shape=(1024, 2048)),
+    dict(cls='int', bit=3, sym=False, gran='per_group', kwargs={'group_size': 32}, shape=(256, 1024)),
+    dict(cls='int', bit=4, sym=False, gran='per_channel', shape=(333, 1000)),       # 1000 % 8 == 0, odd row count
+    dict(cls='int', bit=4, sym=False, gran='per_channel', shape=(64, 1001)),        # generic kernel
+    dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(1408, 2048)),
+    dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(576, 2048)),
+    dict(cls='fp', bit='e5m2', gran='per_group', kwargs={'group_size': 128}, shape=(256, 2048)),
+    dict(cls='int', bit=8, sym=True, gran='per_block', kwargs={'block_size': 128}, shape=(300, 520)),
+]
+
+
+@pytest.mark.parametrize('dtype', ['bfloat16', 'float16', 'float32'])
+@pytest.mark.parametrize('c', BIG, ids=[f"{c['cls']}{c['bit']}-{c['gran']}-{'x'.join(map(str, c['shape']))}" for c in BIG])
+def test_cuda_matches_oracle(c, dtype):
+    c = dict(c, dtype=dtype, seed=7)
+    x = H.case_input(c)
+    x.view(-1)[::997] = 0
+    q = H.make_quantizer(Q, c)
+    xd = x.to(DEV)
+    fake = q.fake_quant_act_dynamic(xd) if c.get('input') == 'act' else q.fake_quant_weight_dynamic(xd)
+    ref, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
+    assert H.bits_equal(fake.cpu(), ref)
+    if x.dim() == 2:
+        codes, s, z = q.real_quant_weight_dynamic(xd)
+        rc, rs, rz = H.oracle_case(c, x, H.code_mode(c))
+        assert torch.equal(codes.view(torch.uint8).cpu() if codes.element_size() == 1 else codes.cpu(),
+                           rc.view(torch.uint8) if rc.element_size() == 1 else rc)
+        assert H.bits_equal(s.cpu().reshape(-1), rs.reshape(-1))
+        if rz is not None:
+            assert torch.equal(z.cpu().reshape(-1).float(), rz.reshape(-1).float())
+
+
+def test_nonfinite_inputs_take_the_literal_chain():
+    c = dict(cls='int', bit=4, sym=False, gran='per_group', kwargs={'group_size': 128}, shape=(8, 512), dtype='bfloat16', seed=3)
+    x = H.case_input(c)
+    x[0, 5] = float('inf')
+    x[1, 7] = float('nan')
+    x[2, 300] = float('-inf')
+    q = H.make_quantizer(Q, c)
+    fake = q.fake_quant_weight_dynamic(x.to(DEV))
+    ref, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
+    assert H.bits_equal(fake.cpu(), ref)
+
+
+def test_full_size_properties_llama3_8b():
+    """At BASELINE sizes: fake-quant is idempotent on its own grid and equals dequantised codes."""
+    torch.manual_seed(0)
+    for shape in [(4096, 4096), (14336, 4096), (4096, 14336)]:
+        w = (torch.randn(shape, device=DEV) * 0.02).to(torch.bfloat16)
+        q = Q.IntegerQuantizer(4, False, 'per_group', group_size=128)
+        fq = q.fake_quant_weight_dynamic(w)
+        codes, s, z = q.real_quant_weight_dynamic(w)
+        assert codes.dtype == torch.int32 and int(codes.min()) >= 0 and int(codes.max()) <= 15
+        deq = ((codes.view(-1, 128).to(torch.bfloat16) - z.view(-1, 1).to(torch.bfloat16)) * s.view(-1, 1)).view(shape)
+        assert torch.equal(deq, fq)
+        # every group uses both ends of the code range (min -> 0, max -> 15)
+        g = codes.view(-1, 128)
+        assert bool((g.min(dim=1).values == 0).all()) and bool((g.max(dim=1).values == 15).all())
+        # quantising the fake-quant tensor with the same (static) qparams is the identity
+        _, s0, z0, qmax, qmin = q.get_tensor_qparams(w)
+        again = q.fake_quant_weight_static(fq, {'scales': s0, 'zeros': z0, 'qmax': qmax, 'qmin': qmin})
+        assert torch.equal(again, fq)
+
+
+def test_act_per_token_full_size():
+    torch.manual_seed(1)
+    x = torch.randn(8, 2048, 4096, device=DEV, dtype=torch.bfloat16)
+    q = Q.IntegerQuantizer(8, True, 'per_token')
+    y = q.fake_quant_act_dynamic(x)
+    amax = x.float().abs().amax(-1, keepdim=True)
+    assert bool(((y.float() - x.float()).abs() <= amax / 127 * 0.51 + 1e-3 * amax).all())
+    _, s, _, _, _ = q.get_tensor_qparams(x)
+    assert s.shape == (8, 2048, 1)
+
+
+def test_fp8_block_roundtrip():
+    torch.manual_seed(2)
+    w = (torch.randn(1408, 2048, device=DEV) * 0.02).to(torch.bfloat16)
+    codes, scales = Q.weight_cast_to_fp8(w, 128)
+    assert codes.dtype == torch.float8_e4m3fn and scales.shape == (11, 16) and scales.dtype == torch.float32
+    back = Q.weight_cast_to_bf16(codes, scales, 128)
+    q = Q.FloatQuantizer('e4m3', True, 'per_block', block_size=128, use_qtorch=True)
+    assert torch.equal(back, q.fake_quant_weight_dynamic(w))
+    codes2, scales2 = Q.weight_cast_to_fp8(back, 128)   # idempotent on its own grid
+    assert torch.equal(codes2.view(torch.uint8), codes.view(torch.uint8))

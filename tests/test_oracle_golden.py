@@ -17,8 +17,9 @@ def test_oracle_matches_reference(rec):
             H.oracle_case(c, x, qo.OUT_FAKE)
         return
     assert float(x.double().sum()) == rec['x_sum'], 'input regeneration drifted'
-    fake, scales, zeros = H.oracle_case(c, x, qo.OUT_FAKE)
+    fake, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
     assert H.bits_equal(fake, rec['fake']), 'fake-quant values differ'
+    _, scales, zeros = H.oracle_case(c, x, qo.OUT_NONE)  # get_tensor_qparams
     assert H.bits_equal(scales.view(rec['qp_scales'].shape), rec['qp_scales']), 'scales differ'
     if zeros is not None:
         assert H.bits_equal(zeros.view(rec['qp_zeros'].shape), rec['qp_zeros']), 'zeros differ'
