@@ -1,8 +1,9 @@
 // fakequant.cu — single-pass grouped quant-dequant (subsystem 1 of the north star).
 //
 // One HBM read + one HBM write per element. Kernels:
-//   fq_subwarp_kernel : units of <= 32 lanes x 8 x 16 B; a sub-warp of 4..32 lanes owns a unit, 128-bit
-//                       coalesced loads, xor-shuffle min/max, qparams + round + clamp + dequant in registers.
+//   fq_group_kernel   : (fq_group.cuh) units of <= 32 lanes x 8 x 16 B; a sub-warp of 4..32 lanes owns U units per
+//                       iteration, 128-bit coalesced loads, transposing xor-shuffle min/max, one qparam computation
+//                       per unit, round + clamp + dequant in registers.
 //   fq_row_kernel     : long units (per_channel / per_token rows): one CTA per row, row cached in registers,
 //                       warp-shuffle + smem block reduce.
 //   fq_block2d_kernel : per_block 128x128 tiles (fp32 math), CTA per tile, ragged edges zero-padded.
@@ -105,69 +106,9 @@ __device__ __forceinline__ void write_qparams(void* scales, void* zeros, int64_t
   if (zeros && !sp.sym && sp.kind == LCB_KIND_INT) store_rt(zeros, unit, u.z, sp.qparam_dtype);
 }
 
-// ------------------------------------------------------------------------------------------------
-// sub-warp kernel: unit = LANES lanes x NV vectors
-// ------------------------------------------------------------------------------------------------
-template <typename T, int NV, int UNROLL, int KINDC>
-__global__ void __launch_bounds__(256)
-    fq_subwarp_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
-                      void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp) {
-  constexpr int VEC = TI<T>::VEC;
-  const int nvec = unit_len / VEC;
-  const int lane_in = threadIdx.x & (lanes - 1);
-  const int64_t sub_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / lanes;
-  const int64_t n_sub = ((int64_t)gridDim.x * blockDim.x) / lanes;
-  const int64_t iters = (n_units + n_sub * UNROLL - 1) / (n_sub * UNROLL);
-
-  for (int64_t it = 0; it < iters; ++it) {
-    uint4 raw[UNROLL][NV];
-    int64_t unit[UNROLL];
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      unit[k] = (it * UNROLL + k) * n_sub + sub_id;
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        if (unit[k] < n_units && v < nvec)
-          raw[k][j] = ld_stream(in + unit[k] * unit_len + (int64_t)v * VEC);
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      const bool valid = unit[k] < n_units;
-      float mx = -INFINITY, mn = INFINITY;
-      float f[NV][VEC];
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        if (valid && v < nvec) {
-          TI<T>::unpack(raw[k][j], f[j]);
-#pragma unroll
-          for (int i = 0; i < VEC; ++i) {
-            mx = max_nan(mx, f[j][i]);
-            mn = min_nan(mn, f[j][i]);
-          }
-        }
-      }
-      for (int o = lanes >> 1; o > 0; o >>= 1) {
-        mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-      }
-      if (!valid) continue;
-      UnitQ u;
-      qparams_from_range(mn, mx, sp, u);
-      finish_unit(sp, u);
-      if (!(finite_f(mx) && finite_f(mn))) u.exact = 1;
-      if (lane_in == 0) write_qparams(scales, zeros, unit[k], u, sp);
-      if (sp.out_mode == LCB_OUT_NONE) continue;
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        if (v < nvec) quant_store_vec<T, T, KINDC>(f[j], u, sp, out, unit[k] * unit_len + (int64_t)v * VEC);
-      }
-    }
-  }
-}
+}  // namespace lcb
+#include "fq_group.cuh"
+namespace lcb {
 
 // ------------------------------------------------------------------------------------------------
 // row kernel: one CTA per unit, row cached in registers (NV vectors per thread)

@@ -45,18 +45,33 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
   constexpr int VEC = TI<T>::VEC;
   const int64_t nvec = unit_len / VEC;
   if (nvec <= 256) {
-    int lanes = 1;
+    int lanes = 4;
     while (lanes < nvec && lanes < 32) lanes <<= 1;
-    if (lanes < 4) lanes = 4;
-    int nv = (int)((nvec + lanes - 1) / lanes);
-    int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
+    const int nv = (int)((nvec + lanes - 1) / lanes);
+    const int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
+    int u = 16 / nvt;             // U * NV <= 16 vectors in flight per lane
+    if (u > lanes) u = lanes;     // the transposing butterfly needs U <= lanes
+    FastSpec fs;
+    fs.qmin = sp.qmin;
+    fs.qmax = sp.qmax;
+    fs.div = (sp.sym || sp.kind != LCB_KIND_INT) ? sp.qmax : sp.qmax - sp.qmin;
+    fs.rdiv = 1.0f / fs.div;
+    fs.eps = TI<T>::ID == LCB_BF16 ? __bfloat162float(__float2bfloat16_rn(1e-5f))
+             : TI<T>::ID == LCB_F16 ? __half2float(__float2half_rn(1e-5f)) : 1e-5f;
     const int64_t subs_per_cta = 256 / lanes;
-    LCB_NV_SWITCH(nvt, {
-      constexpr int UNR = NV >= 4 ? 1 : (4 / NV);
-      int64_t ctas = (n_units + subs_per_cta * UNR - 1) / (subs_per_cta * UNR);
-      int grid = grid_for(ctas, 8);
-      fq_subwarp_kernel<T, NV, UNR, KINDC><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, lanes, sp);
-    });
+#define LCB_LAUNCH_GROUP(NVc, Uc)                                                                      \
+  {                                                                                                    \
+    int64_t ctas = (n_units + subs_per_cta * Uc - 1) / (subs_per_cta * Uc);                            \
+    fq_group_kernel<T, NVc, Uc, KINDC><<<grid_for(ctas, 16), 256, 0, st>>>(in, out, scales, zeros, n_units, \
+                                                                          (int)unit_len, lanes, sp, fs); \
+  }
+    if (nvt == 1 && u == 16) LCB_LAUNCH_GROUP(1, 16)
+    else if (nvt == 1 && u == 8) LCB_LAUNCH_GROUP(1, 8)
+    else if (nvt == 1) LCB_LAUNCH_GROUP(1, 4)
+    else if (nvt == 2) LCB_LAUNCH_GROUP(2, 8)
+    else if (nvt == 4) LCB_LAUNCH_GROUP(4, 4)
+    else LCB_LAUNCH_GROUP(8, 2)
+#undef LCB_LAUNCH_GROUP
   } else if (nvec <= 4096) {
     int threads = nvec <= 2048 ? 256 : 512;
     int nv = (int)((nvec + threads - 1) / threads);

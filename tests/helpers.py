@@ -83,6 +83,17 @@ def bits_equal(a, b):
     return torch.equal(a, b)
 
 
+def equal_nan_aware(a, b):
+    """bit-exact on every non-NaN element, NaN exactly where the other has NaN (payload bits are unspecified)."""
+    if a.shape != b.shape or a.dtype != b.dtype:
+        return False
+    na, nb = torch.isnan(a), torch.isnan(b)
+    if not torch.equal(na, nb):
+        return False
+    z = torch.zeros((), dtype=a.dtype)
+    return bits_equal(torch.where(na, z, a), torch.where(nb, z, b))
+
+
 def make_quantizer(mod, c):
     """Instantiate the product (or reference) quantizer class of module `mod` for a golden case."""
     kw = dict(c.get('kwargs', {}))

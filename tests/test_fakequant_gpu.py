@@ -101,7 +101,8 @@ def test_nonfinite_inputs_take_the_literal_chain():
     q = H.make_quantizer(Q, c)
     fake = q.fake_quant_weight_dynamic(x.to(DEV))
     ref, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
-    assert H.bits_equal(fake.cpu(), ref)
+    assert H.equal_nan_aware(fake.cpu(), ref)
+    assert int(torch.isnan(ref).sum()) >= 256  # the inf / nan groups really are poisoned in the reference model
 
 
 def test_full_size_properties_llama3_8b():
