@@ -97,7 +97,9 @@ struct TI<__nv_bfloat16> {
     return make_uint4(w[0], w[1], w[2], w[3]);
   }
   __device__ __forceinline__ static float rd(float x) {
-    return __bfloat162float(__float2bfloat16_rn(x));
+    uint32_t d;  // F2FP.BF16.F32.PACK_AB (full-rate) instead of the conversion-pipe F2F
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(0.0f), "f"(x));
+    return __uint_as_float(d << 16);
   }
   __device__ __forceinline__ static float load1(const __nv_bfloat16* p) {
     return __bfloat162float(*p);

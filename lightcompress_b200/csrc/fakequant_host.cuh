@@ -39,38 +39,77 @@ static int grid_for(int64_t work_ctas, int ctas_per_sm) {
     default: { constexpr int NV = 8; __VA_ARGS__; } break; \
   }
 
+static inline float host_rd(float x, int dt) {
+  if (dt == LCB_BF16) return __bfloat162float(__float2bfloat16_rn(x));
+  if (dt == LCB_F16) return __half2float(__float2half_rn(x));
+  return x;
+}
+
+// constants + chain selection of the group kernel (fq_group.cuh / fq_packed.cuh)
+template <typename T>
+static FastSpec make_fastspec(const SpecD& sp) {
+  FastSpec fs;
+  fs.qmin = sp.qmin;
+  fs.qmax = sp.qmax;
+  fs.div = (sp.sym || sp.kind != LCB_KIND_INT) ? sp.qmax : sp.qmax - sp.qmin;
+  fs.rdiv = 1.0f / fs.div;
+  fs.eps = host_rd(1e-5f, TI<T>::ID);
+  const float span = sp.qmax - sp.qmin;
+  fs.chain = CHAIN_F32;
+  if (sp.kind == LCB_KIND_INT && sp.fast_ok) {
+    if (TI<T>::ID == LCB_BF16) fs.chain = span <= 63.f ? CHAIN_BF16_SMALL : span <= 255.f ? CHAIN_BF16_WIDE : CHAIN_F32;
+    if (TI<T>::ID == LCB_F16 && span <= 511.f) fs.chain = CHAIN_F16;
+  }
+  // bf16 qparams by FMUL: div must be an integer whose odd part is small (fq_packed.cuh)
+  fs.cheap_qp = 0;
+  if (TI<T>::ID == LCB_BF16 && sp.fast_ok && fs.div >= 1.f && fs.div <= 1e6f && floorf(fs.div) == fs.div) {
+    long d = (long)fs.div;
+    while ((d & 1) == 0) d >>= 1;
+    fs.cheap_qp = d <= 1024 ? 1 : 0;
+  }
+  return fs;
+}
+
 template <typename T, int KINDC>
 static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, int64_t n_units, int64_t unit_len,
                              const SpecD& sp, cudaStream_t st) {
   constexpr int VEC = TI<T>::VEC;
   const int64_t nvec = unit_len / VEC;
-  if (nvec <= 256) {
+  if (nvec <= 512) {
+    // sub-warp per unit: lanes = pow2 >= nvec / 2 in [4, 32], NV vectors per lane
     int lanes = 4;
-    while (lanes < nvec && lanes < 32) lanes <<= 1;
+    while (lanes * 2 < nvec && lanes < 32) lanes <<= 1;
     const int nv = (int)((nvec + lanes - 1) / lanes);
-    const int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
-    int u = 16 / nvt;             // U * NV <= 16 vectors in flight per lane
-    if (u > lanes) u = lanes;     // the transposing butterfly needs U <= lanes
-    FastSpec fs;
-    fs.qmin = sp.qmin;
-    fs.qmax = sp.qmax;
-    fs.div = (sp.sym || sp.kind != LCB_KIND_INT) ? sp.qmax : sp.qmax - sp.qmin;
-    fs.rdiv = 1.0f / fs.div;
-    fs.eps = TI<T>::ID == LCB_BF16 ? __bfloat162float(__float2bfloat16_rn(1e-5f))
-             : TI<T>::ID == LCB_F16 ? __half2float(__float2half_rn(1e-5f)) : 1e-5f;
-    const int64_t subs_per_cta = 256 / lanes;
-#define LCB_LAUNCH_GROUP(NVc, Uc)                                                                      \
-  {                                                                                                    \
-    int64_t ctas = (n_units + subs_per_cta * Uc - 1) / (subs_per_cta * Uc);                            \
-    fq_group_kernel<T, NVc, Uc, KINDC><<<grid_for(ctas, 16), 256, 0, st>>>(in, out, scales, zeros, n_units, \
-                                                                          (int)unit_len, lanes, sp, fs); \
+    const int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : nv <= 8 ? 8 : 16;
+    const int u = nvt >= 8 ? 1 : 8 / nvt;
+    const FastSpec fs = make_fastspec<T>(sp);
+    const int64_t units_per_cta = (int64_t)8 * u * (32 / lanes);
+    const int grid = grid_for((n_units + units_per_cta - 1) / units_per_cta, 16);
+    // chain compiled into the kernel: the packed 16-bit chains and the inline fp32 chain serve LCB_OUT_FAKE only
+    int chain = CHAIN_ANY_OUT;
+    if (sp.out_mode == LCB_OUT_FAKE) chain = (KINDC == 0) ? fs.chain : CHAIN_F32;
+#define LCB_LAUNCH_GROUP_C(NVc, CH)                                                                             \
+  fq_group_kernel<T, NVc, KINDC, CH><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, lanes, sp, fs)
+#define LCB_LAUNCH_GROUP(NVc)                                                                                   \
+  {                                                                                                             \
+    if (chain == CHAIN_ANY_OUT) LCB_LAUNCH_GROUP_C(NVc, CHAIN_ANY_OUT);                                         \
+    else if (chain == CHAIN_F32) LCB_LAUNCH_GROUP_C(NVc, CHAIN_F32);                                            \
+    else if (TI<T>::ID == LCB_BF16 && KINDC == 0 && chain == CHAIN_BF16_SMALL) {                                \
+      if constexpr (TI<T>::ID == LCB_BF16 && KINDC == 0) LCB_LAUNCH_GROUP_C(NVc, CHAIN_BF16_SMALL);             \
+    } else if (TI<T>::ID == LCB_BF16 && KINDC == 0 && chain == CHAIN_BF16_WIDE) {                               \
+      if constexpr (TI<T>::ID == LCB_BF16 && KINDC == 0) LCB_LAUNCH_GROUP_C(NVc, CHAIN_BF16_WIDE);              \
+    } else if (TI<T>::ID == LCB_F16 && KINDC == 0 && chain == CHAIN_F16) {                                      \
+      if constexpr (TI<T>::ID == LCB_F16 && KINDC == 0) LCB_LAUNCH_GROUP_C(NVc, CHAIN_F16);                     \
+    } else LCB_LAUNCH_GROUP_C(NVc, CHAIN_ANY_OUT);                                                              \
   }
-    if (nvt == 1 && u == 16) LCB_LAUNCH_GROUP(1, 16)
-    else if (nvt == 1 && u == 8) LCB_LAUNCH_GROUP(1, 8)
-    else if (nvt == 1) LCB_LAUNCH_GROUP(1, 4)
-    else if (nvt == 2) LCB_LAUNCH_GROUP(2, 8)
-    else if (nvt == 4) LCB_LAUNCH_GROUP(4, 4)
-    else LCB_LAUNCH_GROUP(8, 2)
+    switch (nvt) {
+      case 1: LCB_LAUNCH_GROUP(1) break;
+      case 2: LCB_LAUNCH_GROUP(2) break;
+      case 4: LCB_LAUNCH_GROUP(4) break;
+      case 8: LCB_LAUNCH_GROUP(8) break;
+      default: LCB_LAUNCH_GROUP(16) break;
+    }
+#undef LCB_LAUNCH_GROUP_C
 #undef LCB_LAUNCH_GROUP
   } else if (nvec <= 4096) {
     int threads = nvec <= 2048 ? 256 : 512;

@@ -1,12 +1,14 @@
-// fq_group.cuh — the per_group / short-row kernel (units of <= 2048 16-bit or 1024 fp32 elements).
+// fq_group.cuh — the per_group / per_token / per_channel kernel for units of up to 32 lanes x 16 x 128-bit.
 //
-// A sub-warp of L lanes (4..32) owns U units per iteration (U*NV <= 16 x 128-bit vectors per lane, all loads issued
-// before any use). Per unit every lane reduces its 8*NV elements to a packed (max, -min) pair; a TRANSPOSING xor
-// butterfly then leaves lane i with the range of unit i (U-1 shuffles for U units instead of U*log2 L), lane i
-// computes that unit's qparams ONCE (division-free: Markstein steps on host-rounded reciprocals), and the four
-// per-unit constants are broadcast back with sub-warp shuffles. Element work is the fast chain of fq_math.cuh.
+// A sub-warp of L lanes (4..32) owns one unit; every lane holds NV 128-bit vectors of it. A warp works on
+// U * (32 / L) consecutive units per iteration (U * NV = 8..16 vectors per lane, all loads issued before any use, one
+// contiguous span per warp). Per unit: packed (max, -min) reduce in registers, log2(L) xor-shuffles, the qparams
+// (computed redundantly by every lane: cheaper than broadcasting them), then round + clamp + dequant on packed 16-bit
+// pairs (fq_packed.cuh) and one 128-bit streaming store per vector. The loop body is a few hundred instructions:
+// the previous revision unrolled 16 units x 3 code paths into 180 KB of straight-line SASS and ran at the speed of
+// the instruction cache (profiles/r1_fakequant.md).
 #pragma once
-#include "fq_math.cuh"
+#include "fq_packed.cuh"
 
 namespace lcb {
 
@@ -29,7 +31,6 @@ struct Range<float> {
   __device__ __forceinline__ static P shfl_xor(P a, int o) {
     return {__shfl_xor_sync(0xffffffffu, a.mx, o), __shfl_xor_sync(0xffffffffu, a.nmn, o)};
   }
-  __device__ __forceinline__ static P select(bool c, P a, P b) { return {c ? a.mx : b.mx, c ? a.nmn : b.nmn}; }
   __device__ __forceinline__ static float mx(P a) { return a.mx; }
   __device__ __forceinline__ static float mn(P a) { return -a.nmn; }
 };
@@ -42,10 +43,7 @@ __device__ __forceinline__ uint32_t as_u32(H2 h) { return *reinterpret_cast<uint
 template <typename T, typename H2>
 struct Range16 {
   using P = uint32_t;  // low half: max, high half: -min
-  __device__ __forceinline__ static P init() { return T16_NEG_INF2(); }
-  __device__ __forceinline__ static uint32_t T16_NEG_INF2() {
-    return sizeof(T) == 2 && TI<T>::ID == LCB_BF16 ? 0xff80ff80u : 0xfc00fc00u;
-  }
+  __device__ __forceinline__ static P init() { return TI<T>::ID == LCB_BF16 ? 0xff80ff80u : 0xfc00fc00u; }
   __device__ __forceinline__ static P from_vec(const uint4& v) {
     H2 a = __hmax2_nan(__hmax2_nan(as_h2<H2>(v.x), as_h2<H2>(v.y)), __hmax2_nan(as_h2<H2>(v.z), as_h2<H2>(v.w)));
     H2 b = __hmin2_nan(__hmin2_nan(as_h2<H2>(v.x), as_h2<H2>(v.y)), __hmin2_nan(as_h2<H2>(v.z), as_h2<H2>(v.w)));
@@ -55,7 +53,6 @@ struct Range16 {
   }
   __device__ __forceinline__ static P join(P a, P b) { return as_u32(__hmax2_nan(as_h2<H2>(a), as_h2<H2>(b))); }
   __device__ __forceinline__ static P shfl_xor(P a, int o) { return __shfl_xor_sync(0xffffffffu, a, o); }
-  __device__ __forceinline__ static P select(bool c, P a, P b) { return c ? a : b; }
   __device__ __forceinline__ static float mx(P a) {
     uint16_t h = (uint16_t)(a & 0xffffu);
     return TI<T>::load1(reinterpret_cast<const T*>(&h));
@@ -70,7 +67,6 @@ struct Range<__half> : Range16<__half, __half2> {};
 template <>
 struct Range<__nv_bfloat16> : Range16<__nv_bfloat16, __nv_bfloat162> {};
 
-// ---- division-free qparams (math dtype == storage dtype T) -------------------------------------------------
 // Markstein step: RN(a / b) from r = RN(1 / b)
 __device__ __forceinline__ float div_mk(float a, float b, float r) {
   float q0 = __fmul_rn(a, r);
@@ -78,124 +74,193 @@ __device__ __forceinline__ float div_mk(float a, float b, float r) {
   return __fmaf_rn(e, r, q0);
 }
 
-struct FastSpec {   // host-precomputed constants of the fast chain
+struct FastSpec {   // host-precomputed constants of the fast chains
   float qmin, qmax, div, rdiv;  // div = qmax (sym / fp8) or qmax - qmin (asym); rdiv = RN(1 / div)
   float eps;                    // rd_T(1e-5f)
+  int chain;                    // CHAIN_*: element chain of the LCB_OUT_FAKE path
+  int cheap_qp;                 // 1: bf16 qparams by FMUL + MUFU.RCP (fq_packed.cuh), 0: Markstein / IEEE reciprocal
 };
 
+// qparams of one unit from its range; math dtype == storage dtype T (quant.py:545-559)
 template <typename T>
-__device__ __forceinline__ void qparams_fast(float mn, float mx, const SpecD& sp, const FastSpec& fs, UnitQ& u) {
+__device__ __forceinline__ void qparams_unit(float mn, float mx, const SpecD& sp, const FastSpec& fs, UnitQ& u) {
   if (sp.clip != 1.0f) {
     mx = TI<T>::rd(__fmul_rn(mx, sp.clip));
     mn = TI<T>::rd(__fmul_rn(mn, sp.clip));
   }
-  float s, z = 0.f;
-  if (sp.sym || sp.kind != LCB_KIND_INT) {
-    float a = max_nan(max_nan(fabsf(mx), fabsf(mn)), fs.eps);  // rd(max(a, 1e-5f)) == max(a, rd(1e-5f)) for a in T
+  float s, z = 0.f, r;
+  const bool symlike = sp.sym || sp.kind != LCB_KIND_INT;
+  // rd(max(a, 1e-5f)) == max(a, rd(1e-5f)) for a already in T
+  const float a = symlike ? max_nan(max_nan(fabsf(mx), fabsf(mn)), fs.eps) : max_nan(TI<T>::rd(__fsub_rn(mx, mn)), fs.eps);
+  if (fs.cheap_qp) {
+    s = TI<T>::rd(__fmul_rn(a, fs.rdiv));
+    if (sp.kind != LCB_KIND_INT && s == 0.f && sp.out_mode != LCB_OUT_NONE) s = 1.f;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s));  // s >= rd(1e-5)/div: never subnormal
+    if (!symlike) {
+      const float t = TI<T>::rd(__fmul_rn(mn, r));
+      z = clamp_nan(TI<T>::rd(__fsub_rn(fs.qmin, rintf(t))), fs.qmin, fs.qmax);
+    }
+  } else {
     s = TI<T>::rd(div_mk(a, fs.div, fs.rdiv));
     if (sp.kind != LCB_KIND_INT && s == 0.f && sp.out_mode != LCB_OUT_NONE) s = 1.f;
-    u.r = __frcp_rn(s);
-  } else {
-    float d = max_nan(TI<T>::rd(__fsub_rn(mx, mn)), fs.eps);
-    s = TI<T>::rd(div_mk(d, fs.div, fs.rdiv));
-    u.r = __frcp_rn(s);
-    float t = TI<T>::rd(div_mk(mn, s, u.r));
-    z = clamp_nan(TI<T>::rd(__fsub_rn(fs.qmin, rintf(t))), fs.qmin, fs.qmax);
+    r = __frcp_rn(s);
+    if (!symlike) {
+      const float t = TI<T>::rd(div_mk(mn, s, r));
+      z = clamp_nan(TI<T>::rd(__fsub_rn(fs.qmin, rintf(t))), fs.qmin, fs.qmax);
+    }
   }
   u.s = s;
+  u.r = r;
   u.z = z;
   u.s_out = (sp.osf != 1.0f) ? TI<T>::rd(__fmul_rn(s, sp.osf)) : s;
   u.lo = __fsub_rn(fs.qmin, z);
   u.hi = __fsub_rn(fs.qmax, z);
-  // window in which every Markstein step above and in the element chain is exact (tests/test_fq_math_identity.py)
-  const bool ok = sp.fast_ok && (s >= 1e-20f) && (s <= 1e20f) && finite_f(mx) && finite_f(mn);
+  // window in which every step above and in the element chains is exact (tests/test_fq_math_identity.py)
+  const bool ok = sp.fast_ok && (s >= 1e-20f) && (s <= 1e20f) && finite_f(mx) && finite_f(mn) &&
+                  (__fmul_rn(max_nan(fabsf(mx), fabsf(mn)), r) < 1e30f);
   u.exact = ok ? 0 : 1;
 }
 
-template <typename T, int NV, int U, int KINDC>
+// ---- out-of-line rare paths (kept out of the loop body so that the hot code stays a few KB) -------------------------
+// literal arithmetic for a whole vector (non-finite ranges, round_zp=False, exotic specs)
+template <typename T>
+__device__ __noinline__ void quant_store_vec_literal(uint4 raw, float mn, float mx, SpecD sp, void* out, int64_t e0) {
+  constexpr int VEC = TI<T>::VEC;
+  UnitQ u;
+  qparams_from_range(mn, mx, sp, u);
+  finish_unit(sp, u);
+  float f[VEC], val[VEC], code[VEC];
+  TI<T>::unpack(raw, f);
+#pragma unroll 1
+  for (int i = 0; i < VEC; ++i) {
+    float2 vc = fq_elem_literal(f[i], u, sp);
+    val[i] = vc.x;
+    code[i] = vc.y;
+  }
+  store_vec<T>(out, e0, val, code, sp);
+}
+__device__ __noinline__ void write_qparams_literal(float mn, float mx, SpecD sp, void* scales, void* zeros, int64_t unit) {
+  UnitQ u;
+  qparams_from_range(mn, mx, sp, u);
+  finish_unit(sp, u);
+  write_qparams(scales, zeros, unit, u, sp);
+}
+// fp32 fast chain + runtime out_mode store (codes / fp8 / wide integer ranges)
+template <typename T, int KINDC>
+__device__ __noinline__ void quant_store_vec_generic(uint4 raw, UnitQ u, SpecD sp, void* out, int64_t e0) {
+  float f[TI<T>::VEC];
+  TI<T>::unpack(raw, f);
+  quant_store_vec<T, T, KINDC>(f, u, sp, out, e0);
+}
+
+// fp32 fast chain, LCB_OUT_FAKE only, inline (fp32 tensors; fp8 fake-quant)
+template <typename T, int KINDC>
+__device__ __forceinline__ uint4 quant_vec_fast_f32(const uint4& raw, const UnitQ& u, int kind) {
+  constexpr int VEC = TI<T>::VEC;
+  float f[VEC], val[VEC], code;
+  TI<T>::unpack(raw, f);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i)
+    val[i] = KINDC == 0 ? fq_elem_fast_int<T>(f[i], u, &code) : fq_elem_fast_fp8<T>(f[i], u, kind, &code);
+  return TI<T>::pack(val);
+}
+
+enum { CHAIN_ANY_OUT = -1 };  // template value: runtime out_mode, out-of-line generic chain
+
+// CHAIN: element chain compiled in. CHAIN_ANY_OUT serves every out_mode through quant_store_vec_generic; the others
+// are LCB_OUT_FAKE only (the host guarantees it).
+template <typename T, int NV, int KINDC, int CHAIN>
 __global__ void __launch_bounds__(256)
     fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
                     void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
   constexpr int VEC = TI<T>::VEC;
+  constexpr int U = NV >= 8 ? 1 : 8 / NV;
   using R = Range<T>;
   const int nvec = unit_len / VEC;
   const int lane = threadIdx.x & 31;
   const int lane_in = lane & (lanes - 1);
-  const unsigned sub_mask = (lanes == 32 ? 0xffffffffu : ((1u << lanes) - 1u)) << (lane & ~(lanes - 1));
-  const int64_t sub_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / lanes;
-  const int64_t n_sub = ((int64_t)gridDim.x * blockDim.x) / lanes;
-  const int64_t iters = (n_units + n_sub * U - 1) / (n_sub * U);
+  const int spw = 32 / lanes;          // sub-warps (units) per warp per k
+  const int sub_in_warp = lane / lanes;
+  const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t upw = (int64_t)U * spw;  // units per warp per iteration
+  const int64_t iters = (n_units + n_warps * upw - 1) / (n_warps * upw);
 
   for (int64_t it = 0; it < iters; ++it) {
-    // consecutive sub-warps take consecutive blocks of U units: a warp reads one contiguous span per k
-    const int64_t unit0 = (it * n_sub + sub_id) * U;
+    const int64_t unit0 = (it * n_warps + warp_id) * upw + sub_in_warp;  // unit of k: unit0 + k * spw
     uint4 raw[U][NV];
 #pragma unroll
     for (int k = 0; k < U; ++k) {
+      const int64_t unit = unit0 + (int64_t)k * spw;
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
         const int v = j * lanes + lane_in;
-        if (unit0 + k < n_units && v < nvec) raw[k][j] = ld_stream(in + (unit0 + k) * unit_len + (int64_t)v * VEC);
+        raw[k][j] = (unit < n_units && v < nvec) ? ld_stream(in + unit * unit_len + (int64_t)v * VEC)
+                                                 : make_uint4(0u, 0u, 0u, 0u);
       }
     }
-    typename R::P rg[U];
 #pragma unroll
     for (int k = 0; k < U; ++k) {
-      rg[k] = R::init();
+      const int64_t unit = unit0 + (int64_t)k * spw;
+      typename R::P rg = R::init();
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
         const int v = j * lanes + lane_in;
-        if (unit0 + k < n_units && v < nvec) rg[k] = R::join(rg[k], R::from_vec(raw[k][j]));
+        if (v < nvec) rg = R::join(rg, R::from_vec(raw[k][j]));
       }
-    }
-    // plain butterfly while more lanes than units, then the transposing butterfly
-    for (int o = lanes >> 1; o >= U; o >>= 1) {
-#pragma unroll
-      for (int k = 0; k < U; ++k) rg[k] = R::join(rg[k], R::shfl_xor(rg[k], o));
-    }
-#pragma unroll
-    for (int o = U / 2; o >= 1; o >>= 1) {
-      const bool upper = (lane_in & o) != 0;
-#pragma unroll
-      for (int i = 0; i < o; ++i) {
-        typename R::P send = R::select(upper, rg[i], rg[i + o]);
-        typename R::P keep = R::select(upper, rg[i + o], rg[i]);
-        rg[i] = R::join(keep, R::shfl_xor(send, o));
-      }
-    }
-    // lane_in (mod U) now owns unit (lane_in mod U)
-    const int own = lane_in & (U - 1);
-    UnitQ mine;
-    qparams_fast<T>(R::mn(rg[0]), R::mx(rg[0]), sp, fs, mine);
-    if (lane_in < U && unit0 + own < n_units) write_qparams(scales, zeros, unit0 + own, mine, sp);
-    if (sp.out_mode == LCB_OUT_NONE) continue;
-    const float r_flag = mine.exact ? -1.0f : mine.r;
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
+      for (int o = lanes >> 1; o > 0; o >>= 1) rg = R::join(rg, R::shfl_xor(rg, o));
+      const float mx = R::mx(rg), mn = R::mn(rg);
       UnitQ u;
-      u.s = __shfl_sync(0xffffffffu, mine.s, k, lanes);
-      u.r = __shfl_sync(0xffffffffu, r_flag, k, lanes);
-      u.lo = __shfl_sync(0xffffffffu, mine.lo, k, lanes);
-      u.hi = __shfl_sync(0xffffffffu, mine.hi, k, lanes);
-      u.s_out = (sp.osf != 1.0f) ? __shfl_sync(0xffffffffu, mine.s_out, k, lanes) : u.s;
-      u.z = __fsub_rn(fs.qmin, u.lo);
-      u.exact = 0;
-      if (unit0 + k >= n_units) continue;  // sub-warp uniform
-      if (u.r < 0.f) {                     // sub-warp uniform: literal chain for this unit
-        const float mx = __shfl_sync(sub_mask, R::mx(rg[0]), k, lanes);
-        const float mn = __shfl_sync(sub_mask, R::mn(rg[0]), k, lanes);
-        qparams_from_range(mn, mx, sp, u);
-        finish_unit(sp, u);
-        u.exact = 1;
+      qparams_unit<T>(mn, mx, sp, fs, u);
+      if (unit >= n_units) continue;  // sub-warp uniform; no shuffles below
+      const int64_t e0 = unit * unit_len + (int64_t)lane_in * VEC;
+      if (u.exact) {  // sub-warp uniform, rare: literal chain, qparams recomputed literally as well
+        if (lane_in == 0) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
+        if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+          for (int j = 0; j < NV; ++j)
+            if (j * lanes + lane_in < nvec)
+              quant_store_vec_literal<T>(raw[k][j], mn, mx, sp, out, e0 + (int64_t)j * lanes * VEC);
+        }
+        continue;
+      }
+      if (lane_in == 0) write_qparams(scales, zeros, unit, u, sp);
+      if (CHAIN == CHAIN_ANY_OUT) {
+        if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+          for (int j = 0; j < NV; ++j)
+            if (j * lanes + lane_in < nvec)
+              quant_store_vec_generic<T, KINDC>(raw[k][j], u, sp, out, e0 + (int64_t)j * lanes * VEC);
+        }
+        continue;
+      }
+      T* o = reinterpret_cast<T*>(out) + e0;
+      UnitP p;
+      if (CHAIN == CHAIN_BF16_SMALL || CHAIN == CHAIN_BF16_WIDE) {
+        p.lo2 = pack_bf16x2(u.lo, u.lo);
+        p.hi2 = pack_bf16x2(u.hi, u.hi);
+        p.s2 = pack_bf16x2(u.s_out, u.s_out);
+      } else if (CHAIN == CHAIN_F16) {
+        p.lo2 = pack_f16x2(u.lo, u.lo);
+        p.hi2 = pack_f16x2(u.hi, u.hi);
+        p.s2 = pack_f16x2(u.s_out, u.s_out);
       }
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        if (v < nvec) {
-          float f[VEC];
-          TI<T>::unpack(raw[k][j], f);
-          quant_store_vec<T, T, KINDC>(f, u, sp, out, (unit0 + k) * unit_len + (int64_t)v * VEC);
-        }
+        const uint4 w = raw[k][j];
+        uint4 r4;
+        if (CHAIN == CHAIN_BF16_SMALL)
+          r4 = make_uint4(fq2_bf16_small(w.x, u.r, p), fq2_bf16_small(w.y, u.r, p), fq2_bf16_small(w.z, u.r, p),
+                          fq2_bf16_small(w.w, u.r, p));
+        else if (CHAIN == CHAIN_BF16_WIDE)
+          r4 = make_uint4(fq2_bf16_wide(w.x, u.r, p, u.s_out), fq2_bf16_wide(w.y, u.r, p, u.s_out),
+                          fq2_bf16_wide(w.z, u.r, p, u.s_out), fq2_bf16_wide(w.w, u.r, p, u.s_out));
+        else if (CHAIN == CHAIN_F16)
+          r4 = make_uint4(fq2_f16(w.x, u.s, u.r, p), fq2_f16(w.y, u.s, u.r, p), fq2_f16(w.z, u.s, u.r, p),
+                          fq2_f16(w.w, u.s, u.r, p));
+        else
+          r4 = quant_vec_fast_f32<T, KINDC>(w, u, sp.kind);
+        if (j * lanes + lane_in < nvec) st_stream(o + (int64_t)j * lanes * VEC, r4);
       }
     }
   }

