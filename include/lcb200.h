@@ -106,18 +106,25 @@ int lcb_fp8_block_dequant(const void* codes, const float* scales, void* out, int
                           void* stream);
 
 /*
- * GPTQ Hessian accumulation  H <- H * n/(n+b) ; n += b ; H += (2/n) X^T X
- * X is the layer input flattened to [tokens, C] row-major (the reference transposes a view,
- * gptq.py:265-267), H is fp32 [C, C] row-major. n_before / n_batch are the reference's
- * `nsamples` and `tmp` (gptq.py:283-290; they count batches, not tokens).
- * The contraction runs on tcgen05 tensor cores with a bf16 3-way split of the fp32 operand
- * (error ~2^-22 relative, i.e. fp32-class) and fp32 accumulation in TMEM.
- * workspace: lcb_hessian_workspace_bytes(tokens, C) bytes of device scratch.
- * Replaces GPTQ.add_batch (gptq.py:254-295) minus the per-batch all-reduce.
+ * GPTQ Hessian accumulation  S += X^T X   (upper 128x128 blocks of S only; SYRK)
+ * X is the layer input flattened to [tokens, C] row-major (the reference transposes a view of it, gptq.py:265-267),
+ * f32 / f16 / bf16. S is fp32 [C, C] row-major, zero-initialised by the caller, and holds the UN-NORMALISED running
+ * sum: the reference's H after k batches equals (2/k) * sum_{j<=k} X_j^T X_j (gptq.py:283-290: H *= n/(n+b);
+ * H += (2/n) X^T X), so the scale is applied once by lcb_hessian_finalize instead of once per batch. Any number
+ * of tokens may be passed per call (several calibration batches at once). Only 128x128 blocks (i, j >= i) of S are
+ * written; lcb_hessian_finalize mirrors them.
+ * The contraction runs on tcgen05 tensor cores, fp32 accumulation in TMEM: 16-bit inputs multiply exactly; f32 input
+ * is split into bf16 hi + lo (|x - hi - lo| <= 2^-17 |x|) and accumulated as hi*hi + hi*lo + lo*hi.
+ * workspace: lcb_hessian_workspace_bytes(tokens, C, x_dtype) bytes of device scratch (0 for 16-bit inputs).
+ * Multi-GPU: every rank accumulates its own token shard into its own S; ONE all-reduce(SUM) of S per linear, then
+ * finalize with scale = 2 / (total batches) — replaces the per-batch all-reduce of gptq.py:292-295.
+ * Replaces GPTQ.add_batch (gptq.py:254-295).
  */
-int lcb_hessian_accum(float* H, const void* X, int64_t tokens, int64_t C, int32_t x_dtype,
-                      double n_before, double n_batch, void* workspace, void* stream);
-int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C);
+int lcb_hessian_accum(float* S, const void* X, int64_t tokens, int64_t C, int32_t x_dtype, void* workspace,
+                      void* stream);
+int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C, int32_t x_dtype);
+/* H = scale * sym(S) in place: scales the upper blocks and mirrors them into the lower ones. scale = 2 / nsamples. */
+int lcb_hessian_finalize(float* S, int64_t C, double scale, void* stream);
 
 /*
  * GPTQ blocked column update (gptq.py:199-244).

@@ -31,9 +31,9 @@ SIGNATURES = {
                                      ctypes.POINTER(QuantSpec), ctypes.c_int, _c_vp, _c_vp]),
     'lcb_fakequant_workspace_bytes': (_c_i64, []),
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
-    'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, ctypes.c_double,
-                                         ctypes.c_double, _c_vp, _c_vp]),
-    'lcb_hessian_workspace_bytes': (_c_i64, [_c_i64, _c_i64]),
+    'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp, _c_vp]),
+    'lcb_hessian_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i32]),
+    'lcb_hessian_finalize': (ctypes.c_int, [_c_vp, _c_i64, ctypes.c_double, _c_vp]),
     'lcb_gptq_weight_transform': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64,
                                                  _c_i64, _c_i64, _c_i32, _c_i32, _c_i32,
                                                  ctypes.POINTER(QuantSpec), _c_vp, _c_vp]),

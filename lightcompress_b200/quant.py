@@ -22,8 +22,32 @@ def _promote(*dtypes):
     return torch.float32  # any f32 operand, or a bf16/f16 mix, promotes to f32
 
 
-def _stream():
-    return torch.cuda.current_stream().cuda_stream
+_raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+
+
+def _stream(index=None):
+    """cudaStream_t of torch's current stream on device `index` (raw handle: no Stream object is built)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device() if index is None else index)
+    return torch.cuda.current_stream(index).cuda_stream
+
+
+class _NoCtx(object):
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NOCTX = _NoCtx()
+
+
+def _on_device(dev):
+    """Context that makes `dev` the current CUDA device; free when it already is."""
+    if dev.index is None or dev.index == torch.cuda.current_device():
+        return _NOCTX
+    return torch.cuda.device(dev)
 
 
 def _require_cuda(t, what):
@@ -67,9 +91,20 @@ class BaseQuantizer(object):
 
     # ---- layout ---------------------------------------------------------------------------------
     def _units(self, tensor):
+        shape = tuple(tensor.shape)
+        d = self.__dict__
+        key = (shape, self.granularity, d.get('group_size'), d.get('block_size'), d.get('head_num'))
+        cache = d.setdefault('_units_cache', {})
+        u = cache.get(key)
+        if u is None:
+            if len(cache) > 256:
+                cache.clear()
+            u = cache[key] = self._units_uncached(tensor, shape)
+        return u
+
+    def _units_uncached(self, tensor, shape):
         u = _Units()
         g = self.granularity
-        shape = tuple(tensor.shape)
         numel = tensor.numel()
         last = shape[-1] if len(shape) else 1
         if g == 'per_group' and last >= self.group_size:
@@ -130,7 +165,18 @@ class BaseQuantizer(object):
         return tensor.reshape(shape)
 
     # ---- the one kernel call ------------------------------------------------------------------------
-    def _spec(self, dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf=1.0, clip=1.0):
+    def _spec(self, dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf=1.0, clip=1.0, qp_plus1=0):
+        key = (dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf, clip, qp_plus1, self.sym, self.round_zp)
+        cache = self.__dict__.setdefault('_spec_cache', {})
+        s = cache.get(key)
+        if s is None:
+            if len(cache) > 256:
+                cache.clear()
+            s = cache[key] = self._spec_uncached(dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf, clip)
+            s.qp_math_plus1 = qp_plus1
+        return s
+
+    def _spec_uncached(self, dtype, math_dtype, qparam_dtype, out_mode, qmin, qmax, osf=1.0, clip=1.0):
         s = _cabi.QuantSpec()
         s.dtype, s.math_dtype, s.qparam_dtype = _DT[dtype], _DT[math_dtype], _DT[qparam_dtype]
         s.kind = self._kind()
@@ -143,7 +189,7 @@ class BaseQuantizer(object):
         return s
 
     def _run(self, x, rows, cols, ur, uc, spec, dynamic, out=None, scales=None, zeros=None):
-        lib = _cabi.load()
+        lib = _cabi._lib or _cabi.load()
         ws = None
         if dynamic and ur >= rows and uc >= cols:
             ws = torch.empty(int(lib.lcb_fakequant_workspace_bytes()), dtype=torch.uint8, device=x.device)
@@ -151,14 +197,20 @@ class BaseQuantizer(object):
             x.data_ptr(), out.data_ptr() if out is not None else None,
             scales.data_ptr() if scales is not None else None,
             zeros.data_ptr() if zeros is not None else None,
-            rows, cols, ur, uc, spec, 1 if dynamic else 0, ws.data_ptr() if ws is not None else None, _stream())
-        _cabi.check(st, 'lcb_fakequant')
+            rows, cols, ur, uc, spec, 1 if dynamic else 0, ws.data_ptr() if ws is not None else None,
+            _stream(x.device.index))
+        if st:
+            _cabi.check(st, 'lcb_fakequant')
 
     def _math_dtype_dynamic(self, dtype):
         return torch.float32 if self.granularity == 'per_block' else dtype
 
     def _qrange(self):
-        return float(self.qmin), float(self.qmax)
+        # float(0-dim tensor) costs ~1 us each: cache until qmin / qmax are re-assigned
+        c = self.__dict__.get('_qrange_cache')
+        if c is None or c[0] is not self.qmin or c[1] is not self.qmax:
+            c = self.__dict__['_qrange_cache'] = (self.qmin, self.qmax, float(self.qmin), float(self.qmax))
+        return c[2], c[3]
 
     def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0):
         """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
@@ -174,15 +226,19 @@ class BaseQuantizer(object):
         qd = md
         if self.granularity == 'per_tensor' and (self._kind() != _cabi.KIND_INT or not self.sym):
             qd = torch.float32
-        spec = self._spec(x.dtype, md, qd, out_mode, qmin, qmax, osf, clip)
-        spec.qp_math_plus1 = _DT[qd] + 1
-        out = torch.empty(x.shape, dtype=out_dtype, device=x.device) if out_mode != _cabi.OUT_NONE else None
+        spec = self._spec(x.dtype, md, qd, out_mode, qmin, qmax, osf, clip, _DT[qd] + 1)
+        if out_mode == _cabi.OUT_NONE:
+            out = None
+        elif out_dtype == x.dtype:
+            out = torch.empty_like(x)
+        else:
+            out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
         scales = zeros = None
         if want_qparams:
             scales = torch.empty(u.qshape, dtype=qd, device=x.device)
             if not self.sym and self._kind() == _cabi.KIND_INT:
                 zeros = torch.empty(u.qshape, dtype=qd, device=x.device)
-        with torch.cuda.device(x.device):
+        with _on_device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, True, out, scales, zeros)
         return out, scales, zeros
 
@@ -216,7 +272,7 @@ class BaseQuantizer(object):
         qmax_f = float(qmax) if qmax is not None else float(self.qmax)
         spec = self._spec(x.dtype, md, torch.float32, out_mode, qmin_f, qmax_f, osf)
         out = torch.empty(x.shape, dtype=out_dtype, device=x.device)
-        with torch.cuda.device(x.device):
+        with _on_device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, False, out, sc, zp)
         return out
 
@@ -494,8 +550,10 @@ def weight_cast_to_bf16(weight, scale, block_size):
     w = weight.contiguous()
     out = torch.empty(w.shape, dtype=torch.bfloat16, device=w.device)
     kind = _cabi.KIND_FP8_E4M3 if w.dtype == torch.float8_e4m3fn else _cabi.KIND_FP8_E5M2
-    with torch.cuda.device(w.device):
-        st = lib.lcb_fp8_block_dequant(w.data_ptr(), scale.float().contiguous().data_ptr(), out.data_ptr(),
-                                       w.shape[0], w.shape[1], block_size, kind, _cabi.LCB_BF16, _stream())
+    sc = scale.float().contiguous()
+    with _on_device(w.device):
+        st = lib.lcb_fp8_block_dequant(w.data_ptr(), sc.data_ptr(), out.data_ptr(),
+                                       w.shape[0], w.shape[1], block_size, kind, _cabi.LCB_BF16,
+                                       _stream(w.device.index))
     _cabi.check(st, 'lcb_fp8_block_dequant')
     return out
