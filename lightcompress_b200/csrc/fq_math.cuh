@@ -80,7 +80,7 @@ __device__ __forceinline__ void finish_unit(const SpecD& sp, UnitQ& u) {
 
 // ---- LITERAL element chain -----------------------------------------------------------------------
 // returns (.x) the fake-quant value, already rounded to the math dtype, and (.y) the integer / fp8 code value
-__device__ __noinline__ float2 fq_elem_literal(float x, const UnitQ& u, const SpecD& sp) {
+static __device__ __noinline__ float2 fq_elem_literal(float x, const UnitQ& u, const SpecD& sp) {
   const int md = sp.math_dtype;
   if (sp.kind == LCB_KIND_INT) {
     float q;

@@ -1,3 +1,260 @@
-#include "common.cuh"
-extern "C" int lcb_gptq_weight_transform(float*, const float*, float*, float*, float*, float*, const int32_t*, int64_t, int64_t, int64_t, int32_t, int32_t, int32_t, const lcb_quant_spec*, void*, void*) { return LCB_E_UNSUPPORTED; }
-extern "C" int64_t lcb_gptq_workspace_bytes(int64_t, int64_t, int32_t) { return 0; }
+// gptq.cu — GPTQ blocked column update (gptq.py:199-244) as three kernels per column block:
+//
+//   gptq_group_qparams_kernel : per-row (min, max) -> (scale, zero) of every quantization group that STARTS inside the
+//       block, searched on the outer W exactly where the reference does (gptq.py:215-223: `W[:, i1+i : i1+i+gs]`, i.e.
+//       columns that have received every earlier block's lazy update but none of this block's in-block updates).
+//   gptq_block_kernel : the serial part. 8 lanes own one weight row; lane l keeps columns l, l+8, ... of the 128-column
+//       block in registers. Step i: broadcast w = W1[:, i] inside the 8-lane group, quant-dequant it (fp32, the literal
+//       reference chain), err = (w - q) / d, then every lane updates its remaining columns
+//       W1[:, j] -= err * Hinv1[i, j] (separate multiply and subtract, as the reference's outer-product + sub).
+//       With identical inputs this kernel is bit-identical to the reference's in-block loop. Err leaves as bf16 hi + lo.
+//   lazy-batch updates on tensor cores (tc_gemm.cuh, D -= A * B with bf16 hi/lo splits of Err and Hinv):
+//       level 1, after each block : W[:, i2 : s2] -= Err[:, i1:i2] * Hinv[i1:i2, i2:s2]     (inside a 1024-wide super-block)
+//       level 2, after each super-block : W[:, s2 : C] -= Err[:, s1:s2] * Hinv[s1:s2, s2:C]  (K = 1024)
+//   The reference applies every block to ALL trailing columns (R*C^2/256*8 bytes of W traffic, 26 GB for Llama-3-8B
+//   down_proj); the two-level schedule is the same sum with K = 1024 for the far part (5 GB).
+#include <algorithm>
+#include "fq_math.cuh"
+#include "tc_gemm.cuh"
+
+namespace lcb {
+namespace {
+
+struct GSpec {
+  float qmin, qmax;
+  int sym, round_zp;
+};
+
+// ---- per-row group qparams (fp32 literal chain: quant.py:132-143, 545-559) --------------------------------------------
+// one warp per (row, group); groups g0 .. g0+ng-1 start at column g * gs and span min(gs, n_nonout - g*gs) columns
+__global__ void __launch_bounds__(256)
+    gptq_group_qparams_kernel(const float* __restrict__ W, float* __restrict__ gscales, float* __restrict__ gzeros,
+                              int64_t R, int64_t C, int64_t n_nonout, int gs, int g0, int ng, SpecD sp) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (warp >= R * ng) return;
+  const int64_t row = warp / ng;
+  const int g = g0 + (int)(warp % ng);
+  const int64_t c0 = (int64_t)g * gs;
+  const int64_t span = min((int64_t)gs, n_nonout - c0);
+  float mx = -INFINITY, mn = INFINITY;
+  for (int64_t c = lane; c < span; c += 32) {
+    const float x = W[row * C + c0 + c];
+    mx = max_nan(mx, x);
+    mn = min_nan(mn, x);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if (lane == 0) {
+    UnitQ u;
+    qparams_from_range(mn, mx, sp, u);
+    gscales[(int64_t)g * R + row] = u.s;
+    if (gzeros) gzeros[(int64_t)g * R + row] = u.z;
+  }
+}
+
+// ---- IntegerQuantizer.quant_dequant of one fp32 value (quant.py:699-717), math dtype fp32 ------------------------------
+__device__ __forceinline__ float qdq_f32(float x, float s, float z, const GSpec& g) {
+  float q;
+  if (g.round_zp) {
+    q = clamp_nan(__fadd_rn(rintf(__fdiv_rn(x, s)), z), g.qmin, g.qmax);
+  } else {
+    const float sc = max_nan(s, 1e-9f);
+    q = clamp_nan(rintf(__fadd_rn(__fdiv_rn(x, sc), z)), g.qmin, g.qmax);
+  }
+  return __fmul_rn(__fsub_rn(q, z), s);
+}
+
+constexpr int LPR = 8;    // lanes per weight row
+constexpr int NK = 16;    // columns per lane (block of up to 128 columns)
+constexpr int BSMAX = LPR * NK;
+
+// grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BSMAX * BSMAX floats (Hinv1)
+__global__ void __launch_bounds__(256)
+    gptq_block_kernel(const float* __restrict__ W, const float* __restrict__ Hinv, float* __restrict__ Out,
+                      float* __restrict__ Losses, __nv_bfloat16* __restrict__ err_hi, __nv_bfloat16* __restrict__ err_lo,
+                      const float* __restrict__ gscales, const float* __restrict__ gzeros,
+                      const int32_t* __restrict__ col_group, int64_t R, int64_t C, int i1, int count, int err_col0,
+                      int err_ld, int group_size, GSpec gsp) {
+  extern __shared__ float Hs[];  // [BSMAX][BSMAX], rows/cols >= count are zero
+  for (int idx = threadIdx.x; idx < BSMAX * BSMAX; idx += blockDim.x) {
+    const int r = idx / BSMAX, c = idx % BSMAX;
+    Hs[idx] = (r < count && c < count) ? Hinv[(int64_t)(i1 + r) * C + i1 + c] : 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int l = lane & (LPR - 1);
+  const int64_t row_raw = (int64_t)blockIdx.x * 32 + (threadIdx.x / LPR);
+  const bool row_ok = row_raw < R;
+  const int64_t row = row_ok ? row_raw : R - 1;  // keep every lane in the shuffles; stores are masked
+
+  float reg[NK], tmpv[NK], lossv[NK], errv[NK];
+#pragma unroll
+  for (int k = 0; k < NK; ++k) {
+    const int j = k * LPR + l;
+    reg[k] = j < count ? W[row * C + i1 + j] : 0.f;
+    tmpv[k] = lossv[k] = errv[k] = 0.f;
+  }
+  int cur_g = -1;
+  float s = 1.f, z = 0.f;
+#pragma unroll
+  for (int k = 0; k < NK; ++k) {
+#pragma unroll 1
+    for (int l0 = 0; l0 < LPR; ++l0) {
+      const int i = k * LPR + l0;
+      if (i >= count) break;  // uniform
+      const float w = __shfl_sync(0xffffffffu, reg[k], (lane & ~(LPR - 1)) | l0);
+      const int col = i1 + i;
+      const int g = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
+      if (g != cur_g) {  // uniform across the CTA
+        cur_g = g;
+        s = gscales[(int64_t)g * R + row];
+        z = (gzeros && !gsp.sym) ? gzeros[(int64_t)g * R + row] : 0.f;
+      }
+      const float q = qdq_f32(w, s, z, gsp);
+      const float d = Hs[i * BSMAX + i];
+      const float diff = __fsub_rn(w, q);
+      const float err = __fdiv_rn(diff, d);                                             // (w - q) / d
+      const float loss = __fdiv_rn(__fmul_rn(diff, diff), __fmul_rn(2.f, __fmul_rn(d, d)));  // (w-q)^2 / (2 d^2)
+      if (l == l0) {
+        tmpv[k] = w;
+        lossv[k] = loss;
+        errv[k] = err;
+      }
+      const float* hrow = Hs + i * BSMAX + l;
+#pragma unroll
+      for (int kk = k; kk < NK; ++kk) {
+        if (kk > k || l > l0) reg[kk] = __fsub_rn(reg[kk], __fmul_rn(err, hrow[kk * LPR]));
+      }
+    }
+  }
+  if (!row_ok) return;
+#pragma unroll
+  for (int k = 0; k < NK; ++k) {
+    const int j = k * LPR + l;
+    if (j < count) {
+      Out[row * C + i1 + j] = tmpv[k];
+      Losses[row * C + i1 + j] = lossv[k];
+      const __nv_bfloat16 h = __float2bfloat16_rn(errv[k]);
+      err_hi[row * err_ld + err_col0 + j] = h;
+      err_lo[row * err_ld + err_col0 + j] = __float2bfloat16_rn(__fsub_rn(errv[k], __bfloat162float(h)));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) split_f32_2d_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ hi,
+                                                           __nv_bfloat16* __restrict__ lo, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v = x[i];
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    hi[i] = h;
+    lo[i] = __float2bfloat16_rn(v - __bfloat162float(h));
+  }
+}
+
+inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+inline int super_block(int blocksize) { return blocksize * std::max(1, 1024 / blocksize); }
+
+}  // namespace
+}  // namespace lcb
+
+extern "C" int64_t lcb_gptq_workspace_bytes(int64_t R, int64_t C, int32_t blocksize) {
+  if (blocksize < 1) return 0;
+  const int64_t sb = lcb::super_block(blocksize);
+  return 2 * lcb::align_up(C * C * 2, 256) + 2 * lcb::align_up(R * sb * 2, 256) + 512;
+}
+
+extern "C" int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out, float* Losses, float* gscales,
+                                         float* gzeros, const int32_t* col_group, int64_t R, int64_t C, int64_t n_nonout,
+                                         int32_t blocksize, int32_t group_size, int32_t static_groups,
+                                         const lcb_quant_spec* spec, void* workspace, void* stream) {
+  using namespace lcb;
+  if (!W || !Hinv || !Out || !Losses || !gscales || !spec || !workspace) return LCB_E_INVALID;
+  if (R < 1 || C < 1 || n_nonout < 0 || n_nonout > C) return LCB_E_INVALID;
+  if (spec->kind != LCB_KIND_INT) return LCB_E_UNSUPPORTED;        // FloatQuantizer inside GPTQ: not on the CUDA path
+  if (blocksize < 8 || blocksize > BSMAX || blocksize % 8) return LCB_E_UNSUPPORTED;
+  if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  if (!spec->sym && !gzeros) return LCB_E_INVALID;
+  if (C % 8 || (reinterpret_cast<uintptr_t>(W) & 15) || (reinterpret_cast<uintptr_t>(Hinv) & 15)) return LCB_E_ALIGN;
+  const bool dynamic_groups = group_size > 0 && !static_groups;
+  if (dynamic_groups && col_group) return LCB_E_INVALID;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+
+  const int sb = super_block(blocksize);
+  uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
+  __nv_bfloat16* hinv_hi = reinterpret_cast<__nv_bfloat16*>(ws);
+  __nv_bfloat16* hinv_lo = reinterpret_cast<__nv_bfloat16*>(ws + align_up(C * C * 2, 256));
+  __nv_bfloat16* err_hi = reinterpret_cast<__nv_bfloat16*>(ws + 2 * align_up(C * C * 2, 256));
+  __nv_bfloat16* err_lo = reinterpret_cast<__nv_bfloat16*>(ws + 2 * align_up(C * C * 2, 256) + align_up(R * sb * 2, 256));
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gptq_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BSMAX * BSMAX * 4) != cudaSuccess) {
+      set_last_error("cudaFuncSetAttribute(gptq_block)", cudaGetLastError());
+      return LCB_E_CUDA;
+    }
+    attr_set = true;
+  }
+  {
+    const int64_t n = C * C;
+    split_f32_2d_kernel<<<(int)std::min<int64_t>((n + 255) / 256, kNumSMs * 16), 256, 0, st>>>(Hinv, hinv_hi, hinv_lo, n);
+    LCB_CUDA_CHECK_LAUNCH("gptq_split_hinv");
+  }
+  GSpec gsp;
+  gsp.qmin = spec->qmin;
+  gsp.qmax = spec->qmax;
+  gsp.sym = spec->sym;
+  gsp.round_zp = spec->round_zp;
+  SpecD sp;  // fp32 math everywhere: W is fp32 (gptq.py:137)
+  sp.dtype = sp.math_dtype = sp.qparam_dtype = sp.qp_math = LCB_F32;
+  sp.kind = LCB_KIND_INT;
+  sp.sym = spec->sym;
+  sp.round_zp = spec->round_zp;
+  sp.out_mode = LCB_OUT_NONE;
+  sp.fast_ok = 0;
+  sp.qmin = spec->qmin;
+  sp.qmax = spec->qmax;
+  sp.osf = 1.0f;
+  sp.clip = 1.0f;
+
+  const int row_ctas = (int)((R + 31) / 32);
+  for (int64_t s1 = 0; s1 < n_nonout; s1 += sb) {
+    const int64_t s2 = std::min<int64_t>(s1 + sb, n_nonout);
+    for (int64_t i1 = s1; i1 < s2; i1 += blocksize) {
+      const int64_t i2 = std::min<int64_t>(i1 + blocksize, s2);
+      const int count = (int)(i2 - i1);
+      if (dynamic_groups) {
+        const int g0 = (int)((i1 + group_size - 1) / group_size);       // first group starting at or after i1
+        const int g1 = (int)((i2 + group_size - 1) / group_size);       // first group starting at or after i2
+        const int ng = g1 - g0;
+        if (ng > 0) {
+          const int64_t warps = R * ng;
+          gptq_group_qparams_kernel<<<(int)((warps + 7) / 8), 256, 0, st>>>(W, gscales, spec->sym ? nullptr : gzeros, R, C,
+                                                                           n_nonout, group_size, g0, ng, sp);
+          LCB_CUDA_CHECK_LAUNCH("gptq_group_qparams");
+        }
+      }
+      gptq_block_kernel<<<row_ctas, 256, BSMAX * BSMAX * 4, st>>>(W, Hinv, Out, Losses, err_hi, err_lo, gscales, gzeros,
+                                                                 col_group, R, C, (int)i1, count, (int)(i1 - s1), sb,
+                                                                 group_size, gsp);
+      LCB_CUDA_CHECK_LAUNCH("gptq_block");
+      if (i2 < s2) {  // level 1: rest of the super-block
+        const void* aa[3] = {err_hi + (i1 - s1), err_hi + (i1 - s1), err_lo + (i1 - s1)};
+        const void* bb[3] = {hinv_hi + i1 * C + i2, hinv_lo + i1 * C + i2, hinv_hi + i1 * C + i2};
+        int rc = tc_gemm_launch(true, false, true, 1, aa, bb, 3, W + i2, R, s2 - i2, count, sb, C, C, st);
+        if (rc != LCB_OK) return rc;
+      }
+    }
+    if (s2 < C) {  // level 2: everything right of the super-block (including OWQ outlier columns)
+      const void* aa[3] = {err_hi, err_hi, err_lo};
+      const void* bb[3] = {hinv_hi + s1 * C + s2, hinv_lo + s1 * C + s2, hinv_hi + s1 * C + s2};
+      int rc = tc_gemm_launch(true, false, true, 1, aa, bb, 3, W + s2, R, C - s2, s2 - s1, sb, C, C, st);
+      if (rc != LCB_OK) return rc;
+    }
+  }
+  return LCB_OK;
+}

@@ -1,0 +1,109 @@
+// tc_gemm.cu — host side of the tcgen05 contraction (tc_gemm.cuh): tensor-map encoding and launch.
+#include "tc_gemm.cuh"
+
+namespace lcb {
+
+lcb_encode_tiled_fn get_encode_tiled() {
+  static lcb_encode_tiled_fn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<lcb_encode_tiled_fn>(p);
+  }
+  return fn;
+}
+
+bool make_tmap_2d(CUtensorMap* m, const void* base, CUtensorMapDataType dt, int elem_bytes, uint64_t rows, uint64_t cols,
+                  uint64_t row_stride_bytes, uint32_t box_rows, uint32_t box_cols) {
+  lcb_encode_tiled_fn enc = get_encode_tiled();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  (void)elem_bytes;
+  return enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+namespace {
+template <bool AK, bool SY, bool NG>
+int launch_variant(const tcg::Maps& maps, const tcg::Params& p, int grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(tcg::gemm_kernel<AK, SY, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcg::SMEM_BYTES) !=
+        cudaSuccess) {
+      set_last_error("cudaFuncSetAttribute(tc_gemm)", cudaGetLastError());
+      return LCB_E_CUDA;
+    }
+    attr_set = true;
+  }
+  tcg::gemm_kernel<AK, SY, NG><<<grid, tcg::NTHREADS, tcg::SMEM_BYTES, st>>>(maps, p);
+  LCB_CUDA_CHECK_LAUNCH("tc_gemm");
+  return LCB_OK;
+}
+}  // namespace
+
+int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* const* a, const void* const* b, int n_seg,
+                   float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldd, cudaStream_t st) {
+  using namespace tcg;
+  if (M <= 0 || N <= 0 || K <= 0) return LCB_OK;
+  if (n_seg < 1 || n_seg > MAX_SEG) return LCB_E_INVALID;
+  if (syrk && M != N) return LCB_E_INVALID;
+  if (M > (1 << 30) || N > (1 << 30) || K > (1 << 30)) return LCB_E_SHAPE;
+  // TMA: 16-byte aligned bases and row pitches
+  if ((lda % 8) || (ldb % 8) || (ldd % 4) || (reinterpret_cast<uintptr_t>(D) & 15)) return LCB_E_ALIGN;
+  for (int s = 0; s < n_seg; ++s)
+    if ((reinterpret_cast<uintptr_t>(a[s]) & 15) || (reinterpret_cast<uintptr_t>(b[s]) & 15)) return LCB_E_ALIGN;
+
+  Maps maps;
+  Params p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K = (int)K;
+  p.nblk_i = (int)((M + BM - 1) / BM);
+  p.nblk_j = (int)((N + BN - 1) / BN);
+  if (syrk) {
+    p.n_tiles = 0;
+    for (int i = 0; i < p.nblk_i; ++i) p.n_tiles += p.nblk_j - (i >> 1);
+  } else {
+    p.n_tiles = p.nblk_i * p.nblk_j;
+  }
+  const int kb_total = (int)((K + BK - 1) / BK);
+  // split K until the grid is filled about twice, keeping >= 8 K blocks (512 deep) per split
+  int nsplit = 1;
+  while (p.n_tiles * nsplit < 2 * kNumSMs && kb_total / (nsplit * 2) >= 8) nsplit *= 2;
+  p.kb_per_split = (kb_total + nsplit - 1) / nsplit;
+  p.nsplit = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.n_seg = n_seg;
+  p.idesc = tc::idesc_f16(fmt, BM, BN, a_kmajor ? 0 : 1, 1);
+
+  const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  bool ok = true;
+  for (int s = 0; s < MAX_SEG; ++s) {
+    const int u = s < n_seg ? s : 0;
+    if (a_kmajor)
+      ok = ok && make_tmap_2d(&maps.a[s], a[u], dt16, 2, M, K, lda * 2, BM, BK);   // [M, K]: box 128 rows x 64 k
+    else
+      ok = ok && make_tmap_2d(&maps.a[s], a[u], dt16, 2, K, M, lda * 2, BK, 64);   // [K, M]: box 64 k-rows x 64 m
+    ok = ok && make_tmap_2d(&maps.b[s], b[u], dt16, 2, K, N, ldb * 2, BK, 64);     // [K, N]: box 64 k-rows x 64 n
+  }
+  ok = ok && make_tmap_2d(&maps.d, D, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, M, N, ldd * 4, 32, 32);
+  if (!ok) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return LCB_E_CUDA;
+  }
+  const int n_items = p.n_tiles * p.nsplit;
+  const int grid = n_items < kNumSMs ? n_items : kNumSMs;
+  if (!a_kmajor && syrk && !neg) return launch_variant<false, true, false>(maps, p, grid, st);
+  if (a_kmajor && !syrk && neg) return launch_variant<true, false, true>(maps, p, grid, st);
+  if (a_kmajor && !syrk && !neg) return launch_variant<true, false, false>(maps, p, grid, st);
+  if (!a_kmajor && !syrk && !neg) return launch_variant<false, false, false>(maps, p, grid, st);
+  return LCB_E_UNSUPPORTED;
+}
+
+}  // namespace lcb

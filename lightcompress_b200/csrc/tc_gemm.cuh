@@ -1,0 +1,248 @@
+// tc_gemm.cuh — the tcgen05 contraction shared by the Hessian (S += X^T X) and the GPTQ lazy-batch updates
+// (W -= Err * Hinv):      D[M, N] (+/-)= sum_seg A_seg[M, K] * B_seg[K, N]      fp32 accumulate in TMEM, fp32 D.
+//
+// One CTA per SM, persistent, warp-specialised (192 threads):
+//   warp 0   : TMA producer, 4-stage ring of (A 128 x 64, B 64 x 256) 16-bit tiles, 128-byte swizzle (48 KB / stage).
+//              B is always [K, N] row-major (MN-major operand). A is either [K, M] row-major (A_KMAJOR = false: the
+//              Hessian's X^T, MN-major) or [M, K] row-major (A_KMAJOR = true: the GPTQ Err block, K-major).
+//   warp 1   : MMA issuer: one thread, tcgen05.mma.cta_group::1.kind::f16, M = 128, N = 256, K = 16 per instruction,
+//              two 256-column TMEM accumulators so the epilogue of tile t overlaps the main loop of tile t + 1.
+//   warps 2-5: epilogue: tcgen05.ld (32 lanes x 32 columns) -> 128B-swizzled smem -> TMA reduce-add into D. The L2
+//              performs the read-modify-write, so split-K needs no workspace and no second pass.
+// Segments let an fp32 operand enter as bf16 hi + lo: (Ah,Bh) + (Ah,Bl) + (Al,Bh) run as three K ranges into the
+// same accumulator. Out-of-range rows / columns are zero-filled on load and clipped on store by TMA.
+// SYRK = true: only tiles touching the upper triangle (128-row block i, 128-column block jb >= i) are computed/stored.
+#pragma once
+#include <algorithm>
+#include "tc.cuh"
+
+namespace lcb {
+namespace tcg {
+
+constexpr int BM = 128, BN = 256, BK = 64, STAGES = 4;
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int BOX_BYTES = 64 * BK * 2;              // one MN-major TMA box: 64 k-rows x 64 elements
+constexpr int EPI_BUF = 32 * 32 * 4;                // 32 rows x 32 fp32 columns
+constexpr int SMEM_MAIN = STAGES * STAGE_BYTES;     // 196608
+constexpr int SMEM_EPI = 4 * 2 * EPI_BUF;           // 32768
+constexpr int SMEM_BYTES = SMEM_MAIN + SMEM_EPI + 256 + 1024;  // + barriers + alignment slack
+constexpr int NTHREADS = 192;
+constexpr int MAX_SEG = 3;
+
+struct Params {
+  int M, N, K;
+  int nblk_i;        // 128-row blocks of D
+  int nblk_j;        // 256-column blocks of D
+  int n_tiles;
+  int nsplit;        // K splits per tile
+  int kb_per_split;  // 64-deep K blocks per split (per segment)
+  int n_seg;
+  uint32_t idesc;
+};
+
+struct Maps {
+  CUtensorMap a[MAX_SEG];
+  CUtensorMap b[MAX_SEG];
+  CUtensorMap d;
+};
+
+// item -> (row block i, column block j). SYRK: row block i owns column blocks j = i/2 .. nblk_j-1
+template <bool SYRK>
+__device__ __forceinline__ void tile_of(int t, int nblk_j, int& ti, int& tj) {
+  if (!SYRK) {
+    ti = t / nblk_j;
+    tj = t % nblk_j;
+    return;
+  }
+  int i = 0;
+  while (true) {
+    const int cnt = nblk_j - (i >> 1);
+    if (t < cnt) break;
+    t -= cnt;
+    ++i;
+  }
+  ti = i;
+  tj = (i >> 1) + t;
+}
+
+template <bool A_KMAJOR, bool SYRK, bool NEG>
+__global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant__ Maps maps, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* epi = smem + SMEM_MAIN;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + SMEM_MAIN + SMEM_EPI);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < p.n_seg; ++s) {
+      tc::tma_prefetch_desc(&maps.a[s]);
+      tc::tma_prefetch_desc(&maps.b[s]);
+    }
+    tc::tma_prefetch_desc(&maps.d);
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(&full[s], 1);
+      tc::mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(&tfull[a], 1);
+      tc::mbar_init(&tempty[a], 4);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int n_items = p.n_tiles * p.nsplit;
+  const int kb_total = (p.K + BK - 1) / BK;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        int ti, tj;
+        tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
+        const int split = item % p.nsplit;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+        for (int seg = 0; seg < p.n_seg; ++seg) {
+          for (int kb = kb0; kb < kb1; ++kb) {
+            tc::mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * STAGE_BYTES;
+            uint8_t* sb = sa + A_BYTES;
+            tc::mbar_expect_tx(&full[stage], STAGE_BYTES);
+            if (A_KMAJOR) {
+              tc::tma_load_2d(sa, &maps.a[seg], &full[stage], kb * BK, ti * BM);  // box: 128 m-rows x 64 k
+            } else {
+#pragma unroll
+              for (int b = 0; b < BM / 64; ++b)
+                tc::tma_load_2d(sa + b * BOX_BYTES, &maps.a[seg], &full[stage], ti * BM + b * 64, kb * BK);
+            }
+#pragma unroll
+            for (int b = 0; b < BN / 64; ++b)
+              tc::tma_load_2d(sb + b * BOX_BYTES, &maps.b[seg], &full[stage], tj * BN + b * 64, kb * BK);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    // MN-major SWIZZLE_128B: LBO = bytes between 64-element chunks (one TMA box), SBO = bytes between 8-k groups.
+    // K-major SWIZZLE_128B : SBO = bytes between 8-row groups (1024), LBO unused; a K = 16 step is +32 B in the row.
+    const uint64_t desc_mn = tc::smem_desc_sw128(BOX_BYTES, 1024);
+    const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const int split = item % p.nsplit;
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+      const int n_kb = (kb1 - kb0) * p.n_seg;
+      tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
+      tc::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
+      for (int it = 0; it < n_kb; ++it) {
+        tc::mbar_wait(&full[stage], phase);
+        tc::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = A_KMAJOR ? tc::smem_desc_at(desc_k, sa + k * 32) : tc::smem_desc_at(desc_mn, sa + k * 2048);
+            const uint64_t bd = tc::smem_desc_at(desc_mn, sb + k * 2048);  // 16 k-rows = 2 swizzle atoms of 1024 B
+            tc::mma_f16_ss(d_tmem, ad, bd, p.idesc, (it | k) != 0 ? 1u : 0u);
+          }
+          tc::mma_commit(&empty[stage]);                     // frees the smem slot once these MMAs have read it
+          if (it == n_kb - 1) tc::mma_commit(&tfull[acc]);   // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  } else {
+    // ===== epilogue warps: TMEM -> registers -> swizzled smem -> TMA reduce-add =====
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    uint8_t* my_epi = epi + (warp - 2) * 2 * EPI_BUF;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      int ti, tj;
+      tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
+      tc::mbar_wait(&tfull[acc], acc_phase);
+      tc::tc_fence_after();
+      const int row0 = ti * BM + q * 32;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = tj * BN + c * 32;
+        if (SYRK && (col0 >> 7) < ti) continue;            // warp-uniform: 128-column block below the diagonal
+        if (col0 >= p.N || row0 >= p.M) continue;          // warp-uniform: out of range
+        uint32_t v[32];
+        tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
+        tc::tmem_ld_wait();
+        // staging buffer `buf` was handed to TMA two chunks ago: wait until that read is done
+        if (lane == 0) tc::bulk_wait_read<1>();
+        __syncwarp();
+        uint8_t* dst = my_epi + buf * EPI_BUF + lane * 128;
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) {
+          const int pch = ch ^ (lane & 7);  // 128B swizzle: 16-byte chunk index xor (row mod 8)
+          const uint32_t sg = NEG ? 0x80000000u : 0u;
+          *reinterpret_cast<uint4*>(dst + pch * 16) =
+              make_uint4(v[4 * ch] ^ sg, v[4 * ch + 1] ^ sg, v[4 * ch + 2] ^ sg, v[4 * ch + 3] ^ sg);
+        }
+        tc::fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tc::tma_reduce_add_2d(&maps.d, my_epi + buf * EPI_BUF, col0, row0);
+          tc::bulk_commit();
+        }
+        buf ^= 1;
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+    if (lane == 0) tc::bulk_wait_all();
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace tcg
+
+// Host launcher (defined in tc_gemm.cu). 16-bit operands; a[s] / b[s] are the segment base pointers.
+//   a_kmajor: A_seg is [M, K] row-major with leading dimension lda (elements); else [K, M] row-major.
+//   B_seg is [K, N] row-major, leading dimension ldb. D is fp32 [M, N], leading dimension ldd.
+//   fmt: 0 = fp16, 1 = bf16. syrk requires M == N. neg: D -= instead of D +=.
+int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* const* a, const void* const* b, int n_seg,
+                   float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldd, cudaStream_t st);
+
+}  // namespace lcb

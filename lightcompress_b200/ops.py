@@ -61,3 +61,47 @@ def col_absstat(x, out, mean=False):
                                  1 if mean else 0, _stream(x.device.index))
     _cabi.check(st, 'lcb_col_absstat')
     return out
+
+
+def gptq_weight_transform(W, Hinv, blocksize, group_size, qmin, qmax, sym, round_zp=True, n_nonout=None,
+                          static_scales=None, static_zeros=None, col_group=None):
+    """GPTQ.weight_transform (gptq.py:199-244) on the GPU. W fp32 [R, C] is updated in place like the reference's W
+    (trailing columns receive the lazy updates); Hinv is the upper Cholesky factor of the inverse damped Hessian.
+
+    group_size > 0 and no static_scales: per-group qparams are searched on the fly (gptq.py:215-223) and returned as
+    [ceil(n_nonout / group_size), R]. With static_scales [G, R] (+ static_zeros, col_group int32 [C] or None = col //
+    group_size, or group 0 when group_size <= 0) they are inputs. Returns (tmp, Losses, scales, zeros|None).
+    """
+    _need_cuda(W, Hinv, static_scales, static_zeros, col_group)
+    assert W.dtype == torch.float32 and W.is_contiguous() and Hinv.dtype == torch.float32 and Hinv.is_contiguous()
+    R, C = W.shape
+    n_nonout = C if n_nonout is None else int(n_nonout)
+    lib = _cabi.load()
+    spec = _cabi.QuantSpec()
+    spec.dtype = spec.math_dtype = spec.qparam_dtype = _cabi.LCB_F32
+    spec.kind, spec.sym, spec.round_zp, spec.out_mode = _cabi.KIND_INT, int(bool(sym)), int(bool(round_zp)), _cabi.OUT_FAKE
+    spec.qmin, spec.qmax, spec.output_scale_factor, spec.clip_ratio = float(qmin), float(qmax), 1.0, 1.0
+    static = static_scales is not None
+    if static:
+        gs = static_scales.to(torch.float32).contiguous()
+        gz = static_zeros.to(torch.float32).contiguous() if (static_zeros is not None and not sym) else None
+        if not sym and gz is None:
+            raise ValueError('asymmetric static groups need static_zeros')
+        cg = col_group.to(torch.int32).contiguous() if col_group is not None else None
+    else:
+        if group_size <= 0:
+            raise ValueError('per-channel GPTQ needs the layer qparams (static_scales)')
+        G = -(-n_nonout // group_size)
+        gs = torch.empty((G, R), dtype=torch.float32, device=W.device)
+        gz = None if sym else torch.empty((G, R), dtype=torch.float32, device=W.device)
+        cg = None
+    tmp = torch.zeros_like(W)
+    losses = torch.zeros_like(W)
+    ws = torch.empty(int(lib.lcb_gptq_workspace_bytes(R, C, blocksize)), dtype=torch.uint8, device=W.device)
+    with _on_device(W.device):
+        st = lib.lcb_gptq_weight_transform(
+            W.data_ptr(), Hinv.data_ptr(), tmp.data_ptr(), losses.data_ptr(), gs.data_ptr(),
+            gz.data_ptr() if gz is not None else None, cg.data_ptr() if cg is not None else None, R, C, n_nonout,
+            int(blocksize), int(group_size), 1 if static else 0, spec, ws.data_ptr(), _stream(W.device.index))
+    _cabi.check(st, 'lcb_gptq_weight_transform')
+    return tmp, losses, gs, gz
