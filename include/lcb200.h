@@ -146,18 +146,34 @@ int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out, float* Lo
 int64_t lcb_gptq_workspace_bytes(int64_t R, int64_t C, int32_t blocksize);
 
 /*
- * AWQ scale-search candidate, one fused pass per candidate ratio (awq.py:202-248):
- *   Wq = fake_quant(W * s[None, :])          (awq.py:147-164, weight scaled in place then fake-quantised)
- *   out = (x / s) @ Wq^T                      (base_bq.py:877-889 scaling_input + F.linear)
- *   loss[cand] += sum((out - org_out)^2)      (awq.py:134-145; caller divides by numel)
- * W [R, C] and x [T, C] and org_out [T, R] are bf16/f16 row-major; cand_scales [n_cand, C] in the same
- * dtype (awq.py:100-107 computes them in the activation dtype). loss is fp32 [n_cand] (sum of squared
- * error, accumulated; zero it first). The scaled + fake-quantised weight tile is produced in shared
- * memory and fed to tcgen05 directly — it never round-trips HBM.
+ * out[r, c] = in[r, c] * scales[c] (op 0) or in[r, c] / scales[c] (op 1, IEEE division), computed in fp32 and rounded
+ * to `dtype` — the tensor-dtype arithmetic of Awq.scaling_weight (awq.py:41-47: W.mul_(scales)) and
+ * scaling_input (base_bq.py:877-889: x / scales). in / out / scales share `dtype`; out may alias in.
  */
-int lcb_awq_candidates(const void* W, const void* x, const void* org_out, const void* cand_scales,
-                       float* loss, int64_t T, int64_t R, int64_t C, int32_t n_cand,
-                       int32_t group_size, const lcb_quant_spec* spec, void* workspace, void* stream);
+int lcb_scale_cols(const void* in, const void* scales, void* out, int64_t rows, int64_t cols, int32_t dtype, int32_t op,
+                   void* stream);
+
+/*
+ * loss[0] += sum_{t, r} rd(org_out[t, r] - rd(sum_c x[t, c] * w[r, c]))^2     (rd = round to `dtype`, bf16 / f16)
+ * = F.linear(x, w) followed by the squared-error sum of Awq.calculate_loss (awq.py:134-145: (org_out - out) is taken
+ * in the tensor dtype, then .float().pow(2)); the caller divides by T * R for the mean. One tcgen05 GEMM (fp32
+ * accumulation in TMEM) whose epilogue does the rounding, the subtraction and the reduction: `out` is never stored.
+ * x [T, C], w [R, C], org_out [T, R] row-major contiguous; loss is a device double (accumulated with atomics).
+ */
+int lcb_linear_mse(const void* x, const void* w, const void* org_out, double* loss, int64_t T, int64_t R, int64_t C,
+                   int32_t dtype, void* stream);
+
+/*
+ * AWQ scale search over n_cand candidates for a subset whose inspect module is the linear itself (awq.py:202-248):
+ *   Wq = fake_quant(W * s_n[None, :]);  x_n = x / s_n;  loss[n] += sum (org_out - x_n Wq^T)^2      n = 0 .. n_cand-1
+ * via lcb_scale_cols + lcb_fakequant + lcb_linear_mse. cand_scales [n_cand, C] in the tensor dtype (awq.py:100-107
+ * computes them in the activation dtype). spec: the weight quantizer (dynamic; unit = group_size columns, or the whole
+ * row when group_size <= 0), dtype = math_dtype = the tensor dtype, out_mode = LCB_OUT_FAKE. loss: device doubles,
+ * zeroed by the caller. workspace: lcb_awq_workspace_bytes(T, R, C, n_cand).
+ */
+int lcb_awq_candidates(const void* W, const void* x, const void* org_out, const void* cand_scales, double* loss,
+                       int64_t T, int64_t R, int64_t C, int32_t n_cand, int32_t group_size,
+                       const lcb_quant_spec* spec, void* workspace, void* stream);
 int64_t lcb_awq_workspace_bytes(int64_t T, int64_t R, int64_t C, int32_t n_cand);
 
 /* column absmax of a [rows, cols] matrix -> fp32 [cols] (running max: out = max(out, colmax)).

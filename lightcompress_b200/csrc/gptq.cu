@@ -57,13 +57,21 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---- IntegerQuantizer.quant_dequant of one fp32 value (quant.py:699-717), math dtype fp32 ------------------------------
-__device__ __forceinline__ float qdq_f32(float x, float s, float z, const GSpec& g) {
+// x / s is RN(x / s): by a Markstein step on r = RN(1 / s) when (s, x) are inside the window where that step is exact
+// (tests/test_fq_math_identity.py), by the IEEE division otherwise. `fast` is per (row, group).
+__device__ __forceinline__ float div_exact(float x, float s, float r, bool fast) {
+  if (fast && (fabsf(x) >= 1e-30f || x == 0.f) && fabsf(x) <= 1e30f) {
+    const float q0 = __fmul_rn(x, r);
+    return __fmaf_rn(__fmaf_rn(-s, q0, x), r, q0);
+  }
+  return __fdiv_rn(x, s);
+}
+__device__ __forceinline__ float qdq_f32(float x, float s, float r, bool fast, float z, const GSpec& g) {
   float q;
   if (g.round_zp) {
-    q = clamp_nan(__fadd_rn(rintf(__fdiv_rn(x, s)), z), g.qmin, g.qmax);
+    q = clamp_nan(__fadd_rn(rintf(div_exact(x, s, r, fast)), z), g.qmin, g.qmax);
   } else {
-    const float sc = max_nan(s, 1e-9f);
-    q = clamp_nan(rintf(__fadd_rn(__fdiv_rn(x, sc), z)), g.qmin, g.qmax);
+    q = clamp_nan(rintf(__fadd_rn(__fdiv_rn(x, max_nan(s, 1e-9f)), z)), g.qmin, g.qmax);
   }
   return __fmul_rn(__fsub_rn(q, z), s);
 }
@@ -71,18 +79,32 @@ __device__ __forceinline__ float qdq_f32(float x, float s, float z, const GSpec&
 constexpr int LPR = 8;    // lanes per weight row
 constexpr int NK = 16;    // columns per lane (block of up to 128 columns)
 constexpr int BSMAX = LPR * NK;
+constexpr int BLOCK_SMEM = BSMAX * BSMAX * 4 + BSMAX * 8;  // Hinv1 + per-step 1/d + per-step group index
 
-// grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BSMAX * BSMAX floats (Hinv1)
+// grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BLOCK_SMEM
+// FUSED_QP: the quantization groups of this block start inside it, are aligned to multiples of 8 columns and end inside
+// it, so their (min, max) are taken from the block's own (not yet updated) register copy — exactly the outer W the
+// reference searches (gptq.py:215-223) — and no separate qparams kernel runs.
+template <bool FUSED_QP>
 __global__ void __launch_bounds__(256)
     gptq_block_kernel(const float* __restrict__ W, const float* __restrict__ Hinv, float* __restrict__ Out,
                       float* __restrict__ Losses, __nv_bfloat16* __restrict__ err_hi, __nv_bfloat16* __restrict__ err_lo,
-                      const float* __restrict__ gscales, const float* __restrict__ gzeros,
+                      float* __restrict__ gscales, float* __restrict__ gzeros,
                       const int32_t* __restrict__ col_group, int64_t R, int64_t C, int i1, int count, int err_col0,
-                      int err_ld, int group_size, GSpec gsp) {
+                      int err_ld, int group_size, GSpec gsp, SpecD sp) {
   extern __shared__ float Hs[];  // [BSMAX][BSMAX], rows/cols >= count are zero
+  float* rdiag = Hs + BSMAX * BSMAX;                      // RN(1 / Hinv1[i, i])
+  int* gidx = reinterpret_cast<int*>(rdiag + BSMAX);      // group of column i1 + i
   for (int idx = threadIdx.x; idx < BSMAX * BSMAX; idx += blockDim.x) {
     const int r = idx / BSMAX, c = idx % BSMAX;
     Hs[idx] = (r < count && c < count) ? Hinv[(int64_t)(i1 + r) * C + i1 + c] : 0.f;
+  }
+  if (threadIdx.x < BSMAX) {
+    const int i = threadIdx.x;
+    const float d = i < count ? Hinv[(int64_t)(i1 + i) * C + i1 + i] : 1.f;
+    rdiag[i] = (fabsf(d) >= 1e-20f && fabsf(d) <= 1e20f) ? __frcp_rn(d) : 0.f;  // 0: take the IEEE division
+    const int col = i1 + (i < count ? i : count - 1);
+    gidx[i] = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
   }
   __syncthreads();
   const int lane = threadIdx.x & 31;
@@ -91,15 +113,49 @@ __global__ void __launch_bounds__(256)
   const bool row_ok = row_raw < R;
   const int64_t row = row_ok ? row_raw : R - 1;  // keep every lane in the shuffles; stores are masked
 
-  float reg[NK], tmpv[NK], lossv[NK], errv[NK];
+  float reg[NK], tmpv[NK], diffv[NK], errv[NK];
 #pragma unroll
   for (int k = 0; k < NK; ++k) {
     const int j = k * LPR + l;
     reg[k] = j < count ? W[row * C + i1 + j] : 0.f;
-    tmpv[k] = lossv[k] = errv[k] = 0.f;
+    tmpv[k] = diffv[k] = errv[k] = 0.f;
+  }
+  float sq[4] = {1.f, 1.f, 1.f, 1.f}, zq[4] = {0.f, 0.f, 0.f, 0.f};  // FUSED_QP: qparams of the (<= 4) groups of this block
+  if (FUSED_QP) {
+    // groups of gk = group_size / 8 register slots; after the xor-shuffles every lane of the row holds the group's
+    // range and computes the qparams itself (registers only: no global round trip inside the kernel)
+    const int gk = group_size / LPR;
+#pragma unroll
+    for (int gi = 0; gi < 4; ++gi) {
+      const int k0 = gi * gk;
+      if (k0 * LPR >= count) break;  // uniform
+      float mx = -INFINITY, mn = INFINITY;
+#pragma unroll
+      for (int k = 0; k < NK; ++k) {
+        if (k >= k0 && k < k0 + gk && k * LPR + l < count) {
+          mx = max_nan(mx, reg[k]);
+          mn = min_nan(mn, reg[k]);
+        }
+      }
+#pragma unroll
+      for (int o = LPR / 2; o > 0; o >>= 1) {
+        mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      }
+      UnitQ u;
+      qparams_from_range(mn, mx, sp, u);
+      sq[gi] = u.s;
+      zq[gi] = u.z;
+      if (l == 0 && row_ok) {
+        const int g = gidx[k0 * LPR];
+        gscales[(int64_t)g * R + row] = u.s;
+        if (gzeros && !gsp.sym) gzeros[(int64_t)g * R + row] = u.z;
+      }
+    }
   }
   int cur_g = -1;
-  float s = 1.f, z = 0.f;
+  float s = 1.f, z = 0.f, rs = 1.f;
+  bool fast = false;
 #pragma unroll
   for (int k = 0; k < NK; ++k) {
 #pragma unroll 1
@@ -107,21 +163,28 @@ __global__ void __launch_bounds__(256)
       const int i = k * LPR + l0;
       if (i >= count) break;  // uniform
       const float w = __shfl_sync(0xffffffffu, reg[k], (lane & ~(LPR - 1)) | l0);
-      const int col = i1 + i;
-      const int g = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
+      const int g = gidx[i];
       if (g != cur_g) {  // uniform across the CTA
         cur_g = g;
-        s = gscales[(int64_t)g * R + row];
-        z = (gzeros && !gsp.sym) ? gzeros[(int64_t)g * R + row] : 0.f;
+        if (FUSED_QP) {
+          const int gi = i / group_size;
+          s = gi == 0 ? sq[0] : gi == 1 ? sq[1] : gi == 2 ? sq[2] : sq[3];
+          z = gi == 0 ? zq[0] : gi == 1 ? zq[1] : gi == 2 ? zq[2] : zq[3];
+        } else {
+          s = gscales[(int64_t)g * R + row];
+          z = (gzeros && !gsp.sym) ? gzeros[(int64_t)g * R + row] : 0.f;
+        }
+        fast = (s >= 1e-20f) && (s <= 1e20f);
+        rs = fast ? __frcp_rn(s) : 1.f;
       }
-      const float q = qdq_f32(w, s, z, gsp);
+      const float q = qdq_f32(w, s, rs, fast, z, gsp);
       const float d = Hs[i * BSMAX + i];
+      const float rd = rdiag[i];
       const float diff = __fsub_rn(w, q);
-      const float err = __fdiv_rn(diff, d);                                             // (w - q) / d
-      const float loss = __fdiv_rn(__fmul_rn(diff, diff), __fmul_rn(2.f, __fmul_rn(d, d)));  // (w-q)^2 / (2 d^2)
+      const float err = div_exact(diff, d, rd, rd != 0.f);   // (w - q) / d
       if (l == l0) {
         tmpv[k] = w;
-        lossv[k] = loss;
+        diffv[k] = diff;
         errv[k] = err;
       }
       const float* hrow = Hs + i * BSMAX + l;
@@ -136,8 +199,9 @@ __global__ void __launch_bounds__(256)
   for (int k = 0; k < NK; ++k) {
     const int j = k * LPR + l;
     if (j < count) {
+      const float d = Hs[j * BSMAX + j];
       Out[row * C + i1 + j] = tmpv[k];
-      Losses[row * C + i1 + j] = lossv[k];
+      Losses[row * C + i1 + j] = __fdiv_rn(__fmul_rn(diffv[k], diffv[k]), __fmul_rn(2.f, __fmul_rn(d, d)));  // (w-q)^2 / (2 d^2)
       const __nv_bfloat16 h = __float2bfloat16_rn(errv[k]);
       err_hi[row * err_ld + err_col0 + j] = h;
       err_lo[row * err_ld + err_col0 + j] = __float2bfloat16_rn(__fsub_rn(errv[k], __bfloat162float(h)));
@@ -193,7 +257,8 @@ extern "C" int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out
 
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(gptq_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BSMAX * BSMAX * 4) != cudaSuccess) {
+    if (cudaFuncSetAttribute(gptq_block_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BLOCK_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(gptq_block_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BLOCK_SMEM) != cudaSuccess) {
       set_last_error("cudaFuncSetAttribute(gptq_block)", cudaGetLastError());
       return LCB_E_CUDA;
     }
@@ -227,20 +292,29 @@ extern "C" int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out
     for (int64_t i1 = s1; i1 < s2; i1 += blocksize) {
       const int64_t i2 = std::min<int64_t>(i1 + blocksize, s2);
       const int count = (int)(i2 - i1);
+      // groups that start in this block; fused into the block kernel when they also end in it and are 8-aligned
+      bool fused = false;
       if (dynamic_groups) {
         const int g0 = (int)((i1 + group_size - 1) / group_size);       // first group starting at or after i1
         const int g1 = (int)((i2 + group_size - 1) / group_size);       // first group starting at or after i2
         const int ng = g1 - g0;
-        if (ng > 0) {
+        fused = (group_size % LPR == 0) && (i1 % group_size == 0) && (count % group_size == 0 || i2 == n_nonout) &&
+                group_size <= count && (count + group_size - 1) / group_size <= 4;
+        if (ng > 0 && !fused) {
           const int64_t warps = R * ng;
           gptq_group_qparams_kernel<<<(int)((warps + 7) / 8), 256, 0, st>>>(W, gscales, spec->sym ? nullptr : gzeros, R, C,
                                                                            n_nonout, group_size, g0, ng, sp);
           LCB_CUDA_CHECK_LAUNCH("gptq_group_qparams");
         }
       }
-      gptq_block_kernel<<<row_ctas, 256, BSMAX * BSMAX * 4, st>>>(W, Hinv, Out, Losses, err_hi, err_lo, gscales, gzeros,
-                                                                 col_group, R, C, (int)i1, count, (int)(i1 - s1), sb,
-                                                                 group_size, gsp);
+      if (fused)
+        gptq_block_kernel<true><<<row_ctas, 256, BLOCK_SMEM, st>>>(W, Hinv, Out, Losses, err_hi, err_lo, gscales, gzeros,
+                                                                  col_group, R, C, (int)i1, count, (int)(i1 - s1), sb,
+                                                                  group_size, gsp, sp);
+      else
+        gptq_block_kernel<false><<<row_ctas, 256, BLOCK_SMEM, st>>>(W, Hinv, Out, Losses, err_hi, err_lo, gscales, gzeros,
+                                                                   col_group, R, C, (int)i1, count, (int)(i1 - s1), sb,
+                                                                   group_size, gsp, sp);
       LCB_CUDA_CHECK_LAUNCH("gptq_block");
       if (i2 < s2) {  // level 1: rest of the super-block
         const void* aa[3] = {err_hi + (i1 - s1), err_hi + (i1 - s1), err_lo + (i1 - s1)};

@@ -31,18 +31,18 @@ bool make_tmap_2d(CUtensorMap* m, const void* base, CUtensorMapDataType dt, int 
 }
 
 namespace {
-template <bool AK, bool SY, bool NG>
+template <bool AK, bool BK_, bool SY, bool NG, int EP>
 int launch_variant(const tcg::Maps& maps, const tcg::Params& p, int grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(tcg::gemm_kernel<AK, SY, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcg::SMEM_BYTES) !=
+    if (cudaFuncSetAttribute(tcg::gemm_kernel<AK, BK_, SY, NG, EP>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcg::SMEM_BYTES) !=
         cudaSuccess) {
       set_last_error("cudaFuncSetAttribute(tc_gemm)", cudaGetLastError());
       return LCB_E_CUDA;
     }
     attr_set = true;
   }
-  tcg::gemm_kernel<AK, SY, NG><<<grid, tcg::NTHREADS, tcg::SMEM_BYTES, st>>>(maps, p);
+  tcg::gemm_kernel<AK, BK_, SY, NG, EP><<<grid, tcg::NTHREADS, tcg::SMEM_BYTES, st>>>(maps, p);
   LCB_CUDA_CHECK_LAUNCH("tc_gemm");
   return LCB_OK;
 }
@@ -81,6 +81,10 @@ int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* cons
   p.nsplit = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.n_seg = n_seg;
   p.idesc = tc::idesc_f16(fmt, BM, BN, a_kmajor ? 0 : 1, 1);
+  p.org = nullptr;
+  p.ld_org = 0;
+  p.org_fmt = fmt;
+  p.loss = nullptr;
 
   const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   bool ok = true;
@@ -99,11 +103,50 @@ int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* cons
   }
   const int n_items = p.n_tiles * p.nsplit;
   const int grid = n_items < kNumSMs ? n_items : kNumSMs;
-  if (!a_kmajor && syrk && !neg) return launch_variant<false, true, false>(maps, p, grid, st);
-  if (a_kmajor && !syrk && neg) return launch_variant<true, false, true>(maps, p, grid, st);
-  if (a_kmajor && !syrk && !neg) return launch_variant<true, false, false>(maps, p, grid, st);
-  if (!a_kmajor && !syrk && !neg) return launch_variant<false, false, false>(maps, p, grid, st);
+  if (!a_kmajor && syrk && !neg) return launch_variant<false, false, true, false, EPI_REDUCE_ADD>(maps, p, grid, st);
+  if (a_kmajor && !syrk && neg) return launch_variant<true, false, false, true, EPI_REDUCE_ADD>(maps, p, grid, st);
+  if (a_kmajor && !syrk && !neg) return launch_variant<true, false, false, false, EPI_REDUCE_ADD>(maps, p, grid, st);
   return LCB_E_UNSUPPORTED;
+}
+
+int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org, double* loss, int64_t M, int64_t N,
+                         int64_t K, int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st) {
+  using namespace tcg;
+  if (M <= 0 || N <= 0) return LCB_OK;
+  if (K <= 0) return LCB_E_INVALID;
+  if (M > (1 << 30) || N > (1 << 30) || K > (1 << 30)) return LCB_E_SHAPE;
+  if ((ldx % 8) || (ldw % 8) || (ldo % 8) || (N % 8) || (reinterpret_cast<uintptr_t>(x) & 15) ||
+      (reinterpret_cast<uintptr_t>(w) & 15) || (reinterpret_cast<uintptr_t>(org) & 15))
+    return LCB_E_ALIGN;
+  Maps maps;
+  Params p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K = (int)K;
+  p.nblk_i = (int)((M + BM - 1) / BM);
+  p.nblk_j = (int)((N + BN - 1) / BN);
+  p.n_tiles = p.nblk_i * p.nblk_j;
+  p.nsplit = 1;  // the output is rounded before it is compared: no split-K
+  p.kb_per_split = (int)((K + BK - 1) / BK);
+  p.n_seg = 1;
+  p.idesc = tc::idesc_f16(fmt, BM, BN, 0, 0);
+  p.org = org;
+  p.ld_org = ldo;
+  p.org_fmt = fmt;
+  p.loss = loss;
+  const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  bool ok = true;
+  for (int s = 0; s < MAX_SEG; ++s) {
+    ok = ok && make_tmap_2d(&maps.a[s], x, dt16, 2, M, K, ldx * 2, BM, BK);   // [M, K]: box 128 rows x 64 k
+    ok = ok && make_tmap_2d(&maps.b[s], w, dt16, 2, N, K, ldw * 2, BN, BK);   // [N, K]: box 256 rows x 64 k
+  }
+  maps.d = maps.a[0];  // unused by the MSE epilogue
+  if (!ok) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return LCB_E_CUDA;
+  }
+  const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
+  return launch_variant<true, true, false, false, EPI_MSE>(maps, p, grid, st);
 }
 
 }  // namespace lcb

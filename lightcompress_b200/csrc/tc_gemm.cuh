@@ -29,6 +29,8 @@ constexpr int SMEM_BYTES = SMEM_MAIN + SMEM_EPI + 256 + 1024;  // + barriers + a
 constexpr int NTHREADS = 192;
 constexpr int MAX_SEG = 3;
 
+enum { EPI_REDUCE_ADD = 0, EPI_MSE = 1 };
+
 struct Params {
   int M, N, K;
   int nblk_i;        // 128-row blocks of D
@@ -38,6 +40,11 @@ struct Params {
   int kb_per_split;  // 64-deep K blocks per split (per segment)
   int n_seg;
   uint32_t idesc;
+  // EPI_MSE: loss[0] += sum over the tile of rd16(rd16(org) - rd16(acc))^2   (awq.py:134-145 on 16-bit tensors)
+  const void* org;   // [M, N] row-major 16-bit, leading dimension ld_org
+  int64_t ld_org;
+  int org_fmt;       // 0 = fp16, 1 = bf16
+  double* loss;
 };
 
 struct Maps {
@@ -65,7 +72,43 @@ __device__ __forceinline__ void tile_of(int t, int nblk_j, int& ti, int& tj) {
   tj = (i >> 1) + t;
 }
 
-template <bool A_KMAJOR, bool SYRK, bool NEG>
+template <int FMT>
+__device__ __forceinline__ float rd16(float x) {
+  if (FMT == 1) {
+    uint32_t d;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(0.0f), "f"(x));
+    return __uint_as_float(d << 16);
+  }
+  return __half2float(__float2half_rn(x));
+}
+template <int FMT>
+__device__ __forceinline__ float2 unpack16x2(uint32_t w) {
+  if (FMT == 1) return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+  return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+// sum over 32 columns of rd16(org - rd16(acc))^2 for one row
+template <int FMT>
+__device__ __forceinline__ float mse_row32(const uint32_t (&v)[32], const uint8_t* org_row, int ncols) {
+  float sum = 0.f;
+#pragma unroll
+  for (int c8 = 0; c8 < 4; ++c8) {
+    if (c8 * 8 < ncols) {
+      const uint4 o = *reinterpret_cast<const uint4*>(org_row + c8 * 16);
+      const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 og = unpack16x2<FMT>(ow[j]);
+        const float d0 = rd16<FMT>(__fsub_rn(og.x, rd16<FMT>(__uint_as_float(v[c8 * 8 + 2 * j]))));
+        const float d1 = rd16<FMT>(__fsub_rn(og.y, rd16<FMT>(__uint_as_float(v[c8 * 8 + 2 * j + 1]))));
+        sum = __fmaf_rn(d0, d0, sum);
+        sum = __fmaf_rn(d1, d1, sum);
+      }
+    }
+  }
+  return sum;
+}
+
+template <bool A_KMAJOR, bool B_KMAJOR, bool SYRK, bool NEG, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant__ Maps maps, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -126,9 +169,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
               for (int b = 0; b < BM / 64; ++b)
                 tc::tma_load_2d(sa + b * BOX_BYTES, &maps.a[seg], &full[stage], ti * BM + b * 64, kb * BK);
             }
+            if (B_KMAJOR) {
+              tc::tma_load_2d(sb, &maps.b[seg], &full[stage], kb * BK, tj * BN);  // box: 256 n-rows x 64 k
+            } else {
 #pragma unroll
-            for (int b = 0; b < BN / 64; ++b)
-              tc::tma_load_2d(sb + b * BOX_BYTES, &maps.b[seg], &full[stage], tj * BN + b * 64, kb * BK);
+              for (int b = 0; b < BN / 64; ++b)
+                tc::tma_load_2d(sb + b * BOX_BYTES, &maps.b[seg], &full[stage], tj * BN + b * 64, kb * BK);
+            }
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -164,7 +211,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = A_KMAJOR ? tc::smem_desc_at(desc_k, sa + k * 32) : tc::smem_desc_at(desc_mn, sa + k * 2048);
-            const uint64_t bd = tc::smem_desc_at(desc_mn, sb + k * 2048);  // 16 k-rows = 2 swizzle atoms of 1024 B
+            // MN-major: 16 k-rows = 2 swizzle atoms of 1024 B
+            const uint64_t bd = B_KMAJOR ? tc::smem_desc_at(desc_k, sb + k * 32) : tc::smem_desc_at(desc_mn, sb + k * 2048);
             tc::mma_f16_ss(d_tmem, ad, bd, p.idesc, (it | k) != 0 ? 1u : 0u);
           }
           tc::mma_commit(&empty[stage]);                     // frees the smem slot once these MMAs have read it
@@ -180,18 +228,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
       if (acc == 0) acc_phase ^= 1;
     }
   } else {
-    // ===== epilogue warps: TMEM -> registers -> swizzled smem -> TMA reduce-add =====
+    // ===== epilogue warps =====
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     uint8_t* my_epi = epi + (warp - 2) * 2 * EPI_BUF;
     int acc = 0;
     uint32_t acc_phase = 0;
     int buf = 0;
+    double mse_sum = 0.0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       int ti, tj;
       tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
       tc::mbar_wait(&tfull[acc], acc_phase);
       tc::tc_fence_after();
       const int row0 = ti * BM + q * 32;
+      float tile_sum = 0.f;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = tj * BN + c * 32;
@@ -200,32 +250,50 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
         uint32_t v[32];
         tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
         tc::tmem_ld_wait();
-        // staging buffer `buf` was handed to TMA two chunks ago: wait until that read is done
-        if (lane == 0) tc::bulk_wait_read<1>();
-        __syncwarp();
-        uint8_t* dst = my_epi + buf * EPI_BUF + lane * 128;
+        if (EPI == EPI_MSE) {
+          // TMEM -> registers -> round to the 16-bit output dtype -> squared error against org_out
+          const int row = row0 + lane;
+          if (row < p.M) {
+            const uint8_t* org_row = reinterpret_cast<const uint8_t*>(p.org) + ((int64_t)row * p.ld_org + col0) * 2;
+            const int ncols = min(32, p.N - col0);
+            tile_sum += p.org_fmt == 1 ? mse_row32<1>(v, org_row, ncols) : mse_row32<0>(v, org_row, ncols);
+          }
+        } else {
+          // TMEM -> registers -> 128B-swizzled smem -> TMA reduce-add into D.
+          // staging buffer `buf` was handed to TMA two chunks ago: wait until that read is done
+          if (lane == 0) tc::bulk_wait_read<1>();
+          __syncwarp();
+          uint8_t* dst = my_epi + buf * EPI_BUF + lane * 128;
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) {
-          const int pch = ch ^ (lane & 7);  // 128B swizzle: 16-byte chunk index xor (row mod 8)
-          const uint32_t sg = NEG ? 0x80000000u : 0u;
-          *reinterpret_cast<uint4*>(dst + pch * 16) =
-              make_uint4(v[4 * ch] ^ sg, v[4 * ch + 1] ^ sg, v[4 * ch + 2] ^ sg, v[4 * ch + 3] ^ sg);
+          for (int ch = 0; ch < 8; ++ch) {
+            const int pch = ch ^ (lane & 7);  // 128B swizzle: 16-byte chunk index xor (row mod 8)
+            const uint32_t sg = NEG ? 0x80000000u : 0u;
+            *reinterpret_cast<uint4*>(dst + pch * 16) =
+                make_uint4(v[4 * ch] ^ sg, v[4 * ch + 1] ^ sg, v[4 * ch + 2] ^ sg, v[4 * ch + 3] ^ sg);
+          }
+          tc::fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tc::tma_reduce_add_2d(&maps.d, my_epi + buf * EPI_BUF, col0, row0);
+            tc::bulk_commit();
+          }
+          buf ^= 1;
         }
-        tc::fence_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          tc::tma_reduce_add_2d(&maps.d, my_epi + buf * EPI_BUF, col0, row0);
-          tc::bulk_commit();
-        }
-        buf ^= 1;
       }
+      mse_sum += (double)tile_sum;
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[acc]);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
-    if (lane == 0) tc::bulk_wait_all();
+    if (EPI == EPI_MSE) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mse_sum += __shfl_xor_sync(0xffffffffu, mse_sum, o);
+      if (lane == 0 && mse_sum != 0.0) atomicAdd(p.loss, mse_sum);
+    } else {
+      if (lane == 0) tc::bulk_wait_all();
+    }
   }
 
   tc::tc_fence_before();
@@ -244,5 +312,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
 //   fmt: 0 = fp16, 1 = bf16. syrk requires M == N. neg: D -= instead of D +=.
 int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* const* a, const void* const* b, int n_seg,
                    float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldd, cudaStream_t st);
+
+// loss[0] += sum_{t, r} rd16(org[t, r] - rd16(sum_k x[t, k] * w[r, k]))^2 — F.linear + the squared-error part of
+// Awq.calculate_loss (awq.py:134-145) without writing the output. x [M, K], w [N, K], org [M, N], all 16-bit row-major.
+int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org, double* loss, int64_t M, int64_t N,
+                         int64_t K, int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st);
 
 }  // namespace lcb

@@ -105,3 +105,68 @@ def gptq_weight_transform(W, Hinv, blocksize, group_size, qmin, qmax, sym, round
             int(blocksize), int(group_size), 1 if static else 0, spec, ws.data_ptr(), _stream(W.device.index))
     _cabi.check(st, 'lcb_gptq_weight_transform')
     return tmp, losses, gs, gz
+
+
+def scale_cols(x, scales, div=False, out=None):
+    """x * scales[None, :] (Awq.scaling_weight, awq.py:41-47) or x / scales[None, :] (scaling_input, base_bq.py:877-889),
+    in the tensor dtype with one rounding, IEEE division. x: [..., C] contiguous; scales: [C] of the same dtype."""
+    _need_cuda(x, scales)
+    x = x if x.is_contiguous() else x.contiguous()
+    s = scales.reshape(-1).to(x.dtype).contiguous()
+    C = x.shape[-1]
+    assert s.numel() == C
+    out = torch.empty_like(x) if out is None else out
+    lib = _cabi.load()
+    with _on_device(x.device):
+        st = lib.lcb_scale_cols(x.data_ptr(), s.data_ptr(), out.data_ptr(), x.numel() // C, C, _DT[x.dtype],
+                                1 if div else 0, _stream(x.device.index))
+    _cabi.check(st, 'lcb_scale_cols')
+    return out
+
+
+def linear_mse(x, w, org_out, loss=None):
+    """sum((org_out - F.linear(x, w))^2) with the reference's roundings (awq.py:134-145) without materialising the
+    output. Returns a 1-element float64 device tensor (accumulated into `loss` when given)."""
+    _need_cuda(x, w, org_out)
+    x2 = x.reshape(-1, x.shape[-1])
+    o2 = org_out.reshape(-1, org_out.shape[-1])
+    assert x2.is_contiguous() and w.is_contiguous() and o2.is_contiguous()
+    assert x2.dtype == w.dtype == o2.dtype and x2.shape[1] == w.shape[1] and o2.shape == (x2.shape[0], w.shape[0])
+    if loss is None:
+        loss = torch.zeros(1, dtype=torch.float64, device=x.device)
+    lib = _cabi.load()
+    with _on_device(x.device):
+        st = lib.lcb_linear_mse(x2.data_ptr(), w.data_ptr(), o2.data_ptr(), loss.data_ptr(), x2.shape[0], w.shape[0],
+                                x2.shape[1], _DT[x2.dtype], _stream(x.device.index))
+    _cabi.check(st, 'lcb_linear_mse')
+    return loss
+
+
+def awq_candidates(W, x, org_out, cand_scales, wquantizer):
+    """Losses (mean squared error, float64 [n_cand]) of every AWQ scale candidate for a subset whose inspect module is
+    the linear itself (awq.py:202-248). cand_scales: [n_cand, C] in the tensor dtype."""
+    _need_cuda(W, x, org_out, cand_scales)
+    x2 = x.reshape(-1, x.shape[-1]).contiguous()
+    o2 = org_out.reshape(-1, org_out.shape[-1]).contiguous()
+    W = W.contiguous()
+    cs = cand_scales.to(W.dtype).contiguous()
+    R, C = W.shape
+    T = x2.shape[0]
+    n = cs.shape[0]
+    g = wquantizer.granularity
+    if g == 'per_group':
+        gs = wquantizer.group_size
+    elif g == 'per_channel':
+        gs = 0
+    else:
+        raise NotImplementedError(f'awq_candidates: weight granularity {g}')
+    qmin, qmax = wquantizer._qrange()
+    spec = wquantizer._spec(W.dtype, W.dtype, W.dtype, _cabi.OUT_FAKE, qmin, qmax, 1.0, 1.0, _DT[W.dtype] + 1)
+    lib = _cabi.load()
+    loss = torch.zeros(n, dtype=torch.float64, device=W.device)
+    ws = torch.empty(int(lib.lcb_awq_workspace_bytes(T, R, C, n)), dtype=torch.uint8, device=W.device)
+    with _on_device(W.device):
+        st = lib.lcb_awq_candidates(W.data_ptr(), x2.data_ptr(), o2.data_ptr(), cs.data_ptr(), loss.data_ptr(), T, R, C, n,
+                                    gs, spec, ws.data_ptr(), _stream(W.device.index))
+    _cabi.check(st, 'lcb_awq_candidates')
+    return loss / float(T * R)

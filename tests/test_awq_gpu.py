@@ -1,0 +1,58 @@
+"""GPU parity of the AWQ scale-search kernels against the oracle restatement of awq.py:202-248.
+Bar (north star): the same selected candidate index; losses are also compared (GEMM summation order differs, so the
+16-bit rounding of `out` may flip on isolated elements: 1e-3 relative on the loss)."""
+import pytest
+import torch
+
+from lightcompress_b200 import ops
+from lightcompress_b200 import quant as Q
+from oracle import awq_oracle as ao
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def _case(T, C, R, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    gain = torch.exp(torch.randn(C, generator=g))
+    x = (torch.randn(T, C, generator=g) * gain).to(dtype)
+    W = (torch.randn(R, C, generator=g) * 0.02).to(dtype)
+    return x, W
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+def test_scale_cols_bit_exact(dtype):
+    x, _ = _case(300, 520, 8, dtype, 0)
+    s = (torch.rand(520) + 0.5).to(dtype)
+    for div in (False, True):
+        ref = (x / s.view(1, -1)) if div else (x * s.view(1, -1))
+        got = ops.scale_cols(x.to(DEV), s.to(DEV), div=div).cpu()
+        assert torch.equal(got.view(torch.int16), ref.view(torch.int16))
+
+
+@pytest.mark.parametrize('T,C,R', [(256, 512, 384), (200, 320, 136), (1024, 1024, 1024)])
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+def test_linear_mse_matches_torch(T, C, R, dtype):
+    x, W = _case(T, C, R, dtype, 1)
+    org = torch.nn.functional.linear(x, W)
+    W2 = (W.float() * (1 + 0.05 * torch.randn(R, C))).to(dtype)
+    out = torch.nn.functional.linear(x, W2)
+    ref = float((org - out).float().pow(2).sum())
+    got = float(ops.linear_mse(x.to(DEV), W2.to(DEV), org.to(DEV)).item())
+    assert abs(got - ref) <= 2e-3 * ref
+
+
+@pytest.mark.parametrize('dtype,bit,sym,gs', [(torch.bfloat16, 4, False, 128), (torch.float16, 4, False, 128),
+                                              (torch.bfloat16, 3, True, 64), (torch.bfloat16, 8, True, 0)])
+def test_awq_candidates_same_argmin(dtype, bit, sym, gs):
+    T, C, R = 512, 512, 384
+    x, W = _case(T, C, R, dtype, 7)
+    w_max = ao.get_weight_scale([W], gs)
+    cands = torch.stack([ao.get_scales(x, w_max, n / 20) for n in range(20)])
+    qmin, qmax = (-(2.0 ** (bit - 1)), 2.0 ** (bit - 1) - 1) if sym else (0.0, 2.0 ** bit - 1)
+    losses, best_i, org = ao.search_losses(W, x, cands, gs, dict(kind=0, sym=sym, qmin=qmin, qmax=qmax))
+    wq = Q.IntegerQuantizer(bit, sym, 'per_group' if gs > 0 else 'per_channel', **({'group_size': gs} if gs > 0 else {}))
+    got = ops.awq_candidates(W.to(DEV), x.to(DEV), org.to(DEV), cands.to(DEV), wq).cpu()
+    ref = torch.tensor(losses, dtype=torch.float64)
+    assert float(((got - ref).abs() / ref).max()) < 2e-3
+    assert int(got.argmin()) == best_i
