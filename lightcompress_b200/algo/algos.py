@@ -1,0 +1,112 @@
+"""GPTQ and Awq as block-loop plug-ins (gptq.py:22-478, awq.py:29-372) on top of the kernel-level pieces."""
+import torch
+import torch.nn as nn
+
+from .. import ops
+from . import awq as lcawq
+from .blockwise import ALGO_REGISTRY, BaseBlockwiseQuantization
+from .gptq import GPTQLayer
+
+
+@ALGO_REGISTRY
+class GPTQ(BaseBlockwiseQuantization):
+    def __init__(self, model, quant_config, input, padding_mask, config, modality='language'):
+        super().__init__(model, quant_config, input, padding_mask, config)
+        sp = self.special
+        self.true_sequential = sp.get('true_sequential', True)
+        self.static_groups = sp.get('static_groups', False)
+        self.actorder = sp.get('actorder', False)
+        self.percdamp = sp.get('percdamp', 0.01)
+        self.blocksize = sp.get('blocksize', 128)
+        if sp.get('owq', False):
+            raise NotImplementedError('OWQ outlier columns: use ops.gptq_weight_transform(n_nonout=...) directly')
+        self.model_dtype = next(self.blocks[0].parameters()).dtype
+        self.layers_cache = {}
+        self.qparams = {}     # module -> (scales [R*C/g, 1], zeros) for deploy (update_model_qparams, gptq.py:398-409)
+
+    def _new_layer(self, m):
+        return GPTQLayer(m.weight, self.wquantizer, self.blocksize, self.percdamp, self.actorder, self.static_groups)
+
+    def block_init(self, block):                       # gptq.py:318-322
+        self.named_layers = self.model.get_block_linears(block)
+        self.layers_cache = {n: self._new_layer(m) for n, m in self.named_layers.items()}
+
+    def subset_init(self, subset):                     # gptq.py:311-315: the next subset's Hessians start over
+        for n, m in subset['layers'].items():
+            self.layers_cache[n] = self._new_layer(m)
+
+    def cache_input_hook(self, m, x, y, name, feat_dict):   # gptq.py:247-251: accumulate, do not keep the input
+        if name in self.layers_cache:
+            self.layers_cache[name].add_batch(x[0].detach())
+
+    @torch.no_grad()
+    def subset_transform(self, subset, input_feat, subset_kwargs):   # gptq.py:97-126
+        for name, layer in subset['layers'].items():
+            if not isinstance(layer, nn.Linear):
+                continue
+            g = self.layers_cache.pop(name)
+            layer.weight.data = g.quantize()
+            if g.scales is not None and self.wquantizer.granularity == 'per_group':
+                self.qparams[layer] = g.buf_qparams() + (g.perm, g.invperm)
+            self.last_losses = g.losses
+
+    def w_qdq(self, module, wquantizer):               # gptq.py:425-452
+        if module not in self.qparams:
+            return wquantizer.fake_quant_weight_dynamic(module.weight.data.to(self.model_dtype))
+        scales, zeros, perm, invperm = self.qparams[module]
+        w = module.weight.data
+        need_perm = perm is not None and not self.static_groups
+        if need_perm:
+            w = w[:, perm]
+        args = {'scales': scales, 'zeros': zeros, 'qmax': wquantizer.qmax, 'qmin': wquantizer.qmin}
+        q = wquantizer.fake_quant_weight_static(w, args).to(self.model_dtype)
+        return q[:, invperm] if need_perm else q
+
+
+@ALGO_REGISTRY
+class Awq(BaseBlockwiseQuantization):
+    def __init__(self, model, quant_config, input, padding_mask, config):
+        super().__init__(model, quant_config, input, padding_mask, config)
+        sp = self.special
+        self.trans = sp.get('trans', True)
+        self.trans_version = sp.get('trans_version', 'v2')
+        self.weight_clip = sp.get('weight_clip', False)
+        self.clip_sym = sp.get('clip_sym', self.wquantizer.sym)
+        self.true_sequential = False
+        self.best_index = {}   # (block, first layer name) -> selected candidate, for parity reports
+
+    @torch.no_grad()
+    def block_transform(self, block, input_feat, block_kwargs):   # awq.py:280-298
+        if self.trans:
+            super().block_transform(block, input_feat, block_kwargs)
+        if self.weight_clip:
+            from .autoclip import auto_clip_block
+            auto_clip_block(self.model.get_block_linears(block), input_feat, self.wquantizer, self.clip_sym,
+                            n_sample_token=(self.config or {}).get('calib', {}).get('seq_len', None)
+                            if isinstance(self.config, dict) else None)
+
+    @torch.no_grad()
+    def subset_transform(self, subset, input_feat, subset_kwargs):   # awq.py:300-372
+        layers_dict, prev_op = subset['layers'], subset['prev_op']
+        if not subset.get('do_trans', True):
+            return
+        if len(prev_op) == 0 or prev_op[0] is None:
+            return
+        p = prev_op[0]
+        layers = list(layers_dict.values())
+        if isinstance(p, nn.Linear) and p.out_features not in (layers[0].in_features, layers[0].in_features * 2,
+                                                               layers[0].in_features * 3):
+            return   # GQA v -> o: "Cannot apply scale" unless do_gqa_trans (not covered)
+        xs = input_feat[subset['input'][0]]
+        x = xs[0] if len(xs) == 1 else torch.cat(xs, 0)
+        inspect = subset['inspect']
+        kwargs = subset_kwargs[0] if isinstance(subset_kwargs, list) and subset_kwargs else (subset_kwargs or {})
+        if isinstance(inspect, nn.Linear) and len(layers) == 1 and inspect is layers[0] and inspect.bias is None \
+                and self.w_only and x.dtype in (torch.bfloat16, torch.float16):
+            scale, best, _ = lcawq.awq_search_scale(x, inspect.weight.data, self.wquantizer, self.trans_version)
+        else:
+            scale, best, _ = lcawq.awq_search_scale_module(x, layers, inspect, self.wquantizer, kwargs,
+                                                           self.trans_version)
+        self.best_index[(self.block_idx, next(iter(layers_dict)))] = best
+        self.apply_scale(scale, prev_op, layers)
+        self.update_input_feat(scale, input_feat, layers_dict)

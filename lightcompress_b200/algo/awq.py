@@ -1,0 +1,91 @@
+"""AWQ scale search on the GPU kernels: the compute of awq.py:48-278 with explicit tensors.
+
+`awq_search_scale(x, weights, wquantizer)` covers subsets whose inspect module is the linear itself (o_proj, down_proj,
+fc2, ...): 20 candidates through lcb_awq_candidates. For multi-linear inspect modules (attention, gated MLP) use
+`awq_search_scale_module`, which keeps the reference's structure (scale -> fake-quant -> forward -> MSE) but with the
+fused scale / fake-quant kernels and no CPU round trip of the state dict (awq.py:199, 244)."""
+import torch
+
+from .. import ops
+from . import dist as lcdist
+
+N_GRID = 20  # awq.py:198
+
+
+def get_weight_scale(weights, wquantizer):
+    """awq.py:48-72: mean over rows of |W| / per-group max |W|, averaged over the layers -> [C_in]."""
+    total = None
+    for w in weights:
+        org_shape = w.shape
+        r = wquantizer.reshape_tensor(w.clone())
+        a = r.abs()
+        ls = a.div_(a.amax(dim=1, keepdim=True)).view(org_shape)
+        total = ls.mean(0) if total is None else total.add_(ls.mean(0))
+    return total.div_(len(weights))
+
+
+def get_act_scale(x):
+    """awq.py:74-85 for one batch: mean |x| per input channel, in the activation dtype (like the reference).
+    Accumulated in fp32 by lcb_col_absstat, then rounded to x.dtype (torch's mean also accumulates in fp32)."""
+    C = x.shape[-1]
+    acc = torch.zeros(C, dtype=torch.float32, device=x.device)
+    ops.col_absstat(x, acc, mean=True)
+    return (acc / float(x.numel() // C)).to(x.dtype)
+
+
+def get_scales(x_mean, w_max, ratio, version='v2'):
+    """awq.py:87-108."""
+    if version == 'v1':
+        scales = (x_mean.pow(ratio) / w_max.pow(1 - ratio)).clamp(min=1e-4).view(-1)
+    else:
+        scales = x_mean.pow(ratio).clamp(min=1e-4).view(-1)
+    return scales / (scales.max() * scales.min()).sqrt()
+
+
+@torch.no_grad()
+def awq_search_scale(x, weight, wquantizer, version='v2', org_out=None, n_grid=N_GRID, x_mean=None):
+    """Best per-input-channel scales for one linear whose output is the search objective.
+    Returns (best_scales [C], best_index, losses float64 [n_grid] with NaN for candidates of other ranks).
+    Multi-GPU: candidates are sharded n = rank (mod world) on identical data; (loss, n) is reduced with MIN."""
+    if org_out is None:
+        org_out = torch.nn.functional.linear(x, weight)
+    x_mean = get_act_scale(x) if x_mean is None else x_mean
+    w_max = get_weight_scale([weight], wquantizer) if version == 'v1' else None
+    mine = lcdist.shard_candidates(n_grid)
+    cands = torch.stack([get_scales(x_mean, w_max, n / n_grid, version) for n in mine]) if mine else None
+    losses = torch.full((n_grid,), float('nan'), dtype=torch.float64)
+    if mine:
+        l = ops.awq_candidates(weight, x, org_out, cands, wquantizer).cpu()
+        for k, n in enumerate(mine):
+            losses[n] = l[k]
+    _, best = lcdist.argmin_across_ranks([float(losses[n]) for n in mine], mine, x.device)
+    best_scales = get_scales(x_mean, w_max, best / n_grid, version)
+    return best_scales, best, losses
+
+
+@torch.no_grad()
+def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, version='v2', n_grid=N_GRID):
+    """awq.py:179-278 for any inspect module (one batch). `layers`: the nn.Linear modules that share the input x.
+    Weights are restored from an on-device copy (the reference reloads a CPU state dict every candidate)."""
+    kwargs = kwargs or {}
+
+    def fwd(inp):
+        out = inspect_module(inp, **kwargs)
+        return out[0] if isinstance(out, tuple) else out
+
+    org_out = fwd(x)
+    x_mean = get_act_scale(x)
+    w_max = get_weight_scale([m.weight.data for m in layers], wquantizer) if version == 'v1' else None
+    saved = [m.weight.data.clone() for m in layers]
+    mine = lcdist.shard_candidates(n_grid)
+    losses = []
+    for n in mine:
+        scales = get_scales(x_mean, w_max, n / n_grid, version)
+        for m, w0 in zip(layers, saved):
+            m.weight.data = wquantizer.fake_quant_weight_dynamic(ops.scale_cols(w0, scales))
+        out = fwd(ops.scale_cols(x, scales, div=True))
+        losses.append((org_out - out).float().pow(2).mean().item())
+        for m, w0 in zip(layers, saved):
+            m.weight.data = w0
+    _, best = lcdist.argmin_across_ranks(losses, mine, x.device)
+    return get_scales(x_mean, w_max, best / n_grid, version), best, losses

@@ -1,0 +1,249 @@
+"""Block loop and plug-in registry: the standalone counterpart of blockwise_optimization.py:8-114 and
+base_blockwise_quantization.py:41-1029, reduced to what RTN / GPTQ / Awq / SmoothQuant need.
+
+Same plug-in contract as the reference: `ALGO_REGISTRY[name](model, quant_config, input, padding_mask, config)`, then
+`.run_block_loop()` and `.deploy('fake_quant')`. `model` is any object with the reference adapter protocol
+(`get_blocks()`, `get_block_linears(block)`, `get_subsets_in_block(block)`): the reference's own `llmc.models.*` classes
+qualify, and `lightcompress_b200.algo.adapters` has minimal Llama / OPT ones. All tensors stay on the GPU (the
+reference shuttles cached inputs and state dicts through host memory: blockwise_optimization.py:53-61, awq.py:199).
+"""
+import functools
+from collections import defaultdict
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..quant import FloatQuantizer, IntegerQuantizer
+
+
+class Register(dict):
+    """registry_factory.py:1-49: decorator registry keyed by class __name__."""
+
+    def __call__(self, target):
+        self[target.__name__] = target
+        return target
+
+
+ALGO_REGISTRY = Register()
+
+
+def make_quantizer(cfg):
+    """base_bq.py:152-179: quant_config['weight' | 'act'] -> quantizer instance."""
+    cfg = dict(cfg)
+    bit, sym, gran = cfg.pop('bit'), cfg.pop('symmetric'), cfg.pop('granularity')
+    qtype = cfg.pop('quant_type', 'int-quant')
+    cls = FloatQuantizer if qtype == 'float-quant' else IntegerQuantizer
+    return cls(bit, sym, gran, **cfg)
+
+
+class BaseBlockwiseQuantization(object):
+    def __init__(self, model, quant_config, input, padding_mask, config):
+        self.model = model
+        self.blocks = model.get_blocks()
+        self.quant_config = quant_config
+        self.input = input
+        self.padding_mask = padding_mask
+        self.config = config
+        self.data_free = not input
+        self.block_idx = None
+        self.dev = torch.device('cuda')
+        self.wquantizer = make_quantizer(quant_config['weight'])
+        self.w_only = not quant_config.get('act')
+        self.aquantizer = None if self.w_only else make_quantizer(quant_config['act'])
+        self.act_static = (not self.w_only) and quant_config['act'].get('static', False)
+        if self.act_static:
+            raise NotImplementedError('static activation quantization is not on the CUDA hot path')
+        self.special = quant_config.get('special', {}) or {}
+        self.true_sequential = self.special.get('true_sequential', False)
+        if self.input:
+            for kw in self.input['kwargs']:   # blockwise_optimization.py:20-25
+                kw.pop('use_cache', None)
+                for k in ('past_key_value', 'past_key_values'):
+                    if k in kw:
+                        kw[k] = None
+            self.n_samples = sum(d.shape[0] for d in self.input['data'])
+
+    # ---- closures bound into modules at deploy time (base_bq.py:46-82) ------------------------------------------------
+    def w_qdq(self, module, wquantizer):
+        return wquantizer.fake_quant_weight_dynamic(module.weight.data)
+
+    def a_qdq(self, act, module, aquantizer):
+        return aquantizer.fake_quant_act_dynamic(act)
+
+    # ---- block loop (blockwise_optimization.py:31-51, base_bq.py:367-452) ----------------------------------------------
+    def run_block_loop(self):
+        for i, block in enumerate(self.blocks):
+            self.block_idx = i
+            self.block_opt(block)
+
+    @torch.no_grad()
+    def block_forward(self, block, input_data=None):
+        data = self.input['data'] if input_data is None else input_data
+        dev = next(block.parameters()).device
+        out = []
+        for i, x in enumerate(data):
+            kw = self.input['kwargs'][i]
+            for k, v in list(kw.items()):
+                if torch.is_tensor(v):
+                    kw[k] = v.to(dev)
+                elif isinstance(v, tuple):
+                    kw[k] = tuple(t.to(dev) if torch.is_tensor(t) else t for t in v)
+            y = block(x.to(dev), **kw)
+            out.append(y[0] if isinstance(y, tuple) else y)
+        return out
+
+    def cache_input_hook(self, m, x, y, name, feat_dict):
+        inp = x[0].detach()
+        feat_dict[name].append(inp.unsqueeze(0) if inp.dim() == 2 else inp)
+
+    def register_hooks(self, modules, feat_dict):
+        return [m.register_forward_hook(functools.partial(self.cache_input_hook, name=n, feat_dict=feat_dict))
+                for n, m in modules.items()]
+
+    def block_init(self, block):
+        pass
+
+    def subset_init(self, subset):
+        pass
+
+    def block_opt(self, block):
+        block = block.to(self.dev)
+        named_linears = self.model.get_block_linears(block)
+        input_feat = defaultdict(list)
+        if not self.data_free:
+            handles = self.register_hooks(named_linears, input_feat)
+            self.block_init(block)
+            self.input['data'] = self.block_forward(block)   # quant_out = False: next block sees the float output
+            for h in handles:
+                h.remove()
+            self.block_transform(block, input_feat, self.input['kwargs'])
+        else:
+            self.block_transform(block, input_feat, None)
+
+    def block_transform(self, block, input_feat, block_kwargs):
+        subsets = self.model.get_subsets_in_block(block)
+        self._done_layers = {}
+        for index, subset in enumerate(subsets):
+            if subset['has_kwargs']:
+                if 'sub_keys' in subset:
+                    subset_kwargs = [{k: kw[v] for k, v in subset['sub_keys'].items()} for kw in block_kwargs]
+                else:
+                    subset_kwargs = block_kwargs
+            else:
+                subset_kwargs = {}
+            self.subset_transform(subset, input_feat, subset_kwargs)
+            if self.true_sequential and index != len(subsets) - 1:
+                input_feat.update(self.rehook_next_subset(block, subset, subsets[index + 1]))
+
+    def rehook_next_subset(self, block, subset, next_subset):
+        """base_bq.py:505-526: the transformed subset runs fake-quantised while the next subset's inputs are re-collected."""
+        self.subset_init(next_subset)
+        self._done_layers.update(subset['layers'])   # every subset transformed so far stays fake-quantised (FakeQuantLinear)
+        saved = {n: m.weight.data for n, m in self._done_layers.items()}
+        mdt = getattr(self, 'model_dtype', None)
+        for n, m in self._done_layers.items():
+            m.weight.data = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+        feat = defaultdict(list)
+        handles = self.register_hooks(next_subset['layers'], feat)
+        self.block_forward(block)
+        for h in handles:
+            h.remove()
+        for n, m in self._done_layers.items():
+            m.weight.data = saved[n]
+        return feat
+
+    def subset_transform(self, subset, input_feat, subset_kwargs):
+        pass
+
+    # ---- scale application (base_bq.py:597-778, 877-897) --------------------------------------------------------------
+    @torch.no_grad()
+    def apply_scale(self, scales, prev_op, layers):
+        assert len(prev_op) == 1, 'Only support single prev_op.'
+        p = prev_op[0]
+        if isinstance(p, nn.Linear):
+            assert len(layers) == 1
+            self.scale_fc_fc(p, layers[0], scales)
+        elif hasattr(p, 'weight') and p.weight.dim() == 1:   # any LayerNorm / RMSNorm flavour
+            self.scale_ln_fcs(p, layers, scales)
+        else:
+            raise NotImplementedError(f'prev_op {type(p)} not supported yet!')
+
+    @torch.no_grad()
+    def scale_ln_fcs(self, ln, fcs, scales):
+        s = scales.to(device=ln.weight.device, dtype=ln.weight.dtype)
+        ln.weight.div_(s)
+        if getattr(ln, 'bias', None) is not None:
+            ln.bias.div_(s)
+        for fc in fcs:
+            ops.scale_cols(fc.weight.data, s.to(fc.weight.dtype), out=fc.weight.data)   # fc.weight *= s[None, :]
+
+    @torch.no_grad()
+    def scale_fc_fc(self, fc1, fc2, scales):
+        s = scales.to(fc1.weight.device)
+        if fc1.out_features == fc2.in_features * 2:
+            half = fc1.weight.data.shape[0] // 2
+            fc1.weight.data[half:].div_(s.view(-1, 1))
+            if fc1.bias is not None:
+                fc1.bias.data[half:].div_(s.view(-1))
+        elif fc1.out_features == fc2.in_features:
+            if fc1.bias is not None:
+                fc1.bias.div_(s.view(-1))
+            fc1.weight.div_(s.view(-1, 1))
+        else:
+            raise NotImplementedError('Can not scale this fc-fc (fused qkv / GQA repeat are not covered).')
+        ops.scale_cols(fc2.weight.data, s.to(fc2.weight.dtype), out=fc2.weight.data)
+
+    @torch.no_grad()
+    def update_input_feat(self, scale, input_feat, layers_dict):
+        for name in layers_dict:
+            input_feat[name] = [ops.scale_cols(x, scale.to(x.dtype), div=True) for x in input_feat[name]]
+
+    # ---- deploy (base_bq.py:899-1006, fake_quant only) ------------------------------------------------------------------
+    @torch.no_grad()
+    def deploy(self, quant_format='fake_quant'):
+        if quant_format == 'origin_float':
+            return
+        if quant_format != 'fake_quant':
+            raise NotImplementedError('real-quant export formats are out of scope (SURVEY.md §8f N3); use '
+                                      'wquantizer.real_quant_weight_dynamic per layer')
+        for block in self.blocks:
+            block.to(self.dev)
+            for name, m in self.model.get_block_linears(block).items():
+                m.weight.data = self.w_qdq(m, self.wquantizer).to(getattr(self, 'model_dtype', None) or m.weight.dtype)
+                if not self.w_only:
+                    m.register_forward_pre_hook(self._act_hook)
+
+    def _act_hook(self, module, args):
+        return (self.a_qdq(args[0], module, self.aquantizer),) + tuple(args[1:])
+
+
+@ALGO_REGISTRY
+class RTN(BaseBlockwiseQuantization):
+    """rtn.py:10-28: nothing to calibrate; quantization happens at deploy."""
+
+    def block_opt(self, block):
+        pass
+
+
+@ALGO_REGISTRY
+class SmoothQuant(BaseBlockwiseQuantization):
+    """smoothquant.py:14-79."""
+
+    def __init__(self, model, quant_config, input, padding_mask, config):
+        super().__init__(model, quant_config, input, padding_mask, config)
+        self.alpha = self.special.get('alpha', 0.5)
+
+    @torch.no_grad()
+    def subset_transform(self, subset, input_feat, subset_kwargs):
+        from . import smoothquant as sq
+        prev_op = subset['prev_op']
+        if not (len(prev_op) == 1 and hasattr(prev_op[0], 'weight') and prev_op[0].weight.dim() == 1):
+            return   # filter_subset: LN -> FC subsets only (smoothquant.py:21-24)
+        layers = list(subset['layers'].values())
+        tensors = input_feat[subset['input'][0]]
+        am = sq.ActMax(layers[0].in_features, layers[0].weight.device)
+        for x in tensors:
+            am.update(x)
+        scale = sq.smoothquant_scale(am.result(), [m.weight.data for m in layers], self.alpha)
+        self.apply_scale(scale, prev_op, layers)

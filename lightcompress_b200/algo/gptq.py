@@ -1,0 +1,112 @@
+"""GPTQ per-linear calibration on the GPU kernels: the compute of gptq.py:128-295 with explicit tensors.
+
+    g = GPTQLayer(layer.weight, wquantizer, blocksize=128, percdamp=0.01)
+    for x in calibration_inputs: g.add_batch(x)          # GPTQ.add_batch           (gptq.py:254-295)
+    W_new = g.quantize()                                  # process_hessian_and_weights + weight_transform (:128-244)
+    g.scales, g.zeros                                     # per-group qparams for deploy (update_model_qparams :398-409)
+"""
+import torch
+
+from .. import ops
+from . import dist as lcdist
+
+
+class GPTQLayer(object):
+    def __init__(self, weight, wquantizer, blocksize=128, percdamp=0.01, actorder=False, static_groups=False):
+        if not weight.is_cuda:
+            raise RuntimeError('GPTQLayer: weight must live on a CUDA device (no CPU path)')
+        self.weight = weight
+        self.wquantizer = wquantizer
+        self.blocksize = blocksize
+        self.percdamp = percdamp
+        self.actorder = actorder
+        self.static_groups = static_groups
+        self.rows, self.columns = weight.shape[0], weight.shape[1]
+        # layer_init (gptq.py:297-309): H zeros, nsamples 0. Here H is the UN-NORMALISED sum until finalize().
+        self.S = torch.zeros((self.columns, self.columns), dtype=torch.float32, device=weight.device)
+        self.nsamples = 0
+        self.H = None
+        self.scales = self.zeros = None
+        self.losses = None
+        self.perm = self.invperm = None
+
+    @torch.no_grad()
+    def add_batch(self, inp):
+        """gptq.py:254-295 for Linear layers: `nsamples` counts batches (inp.shape[0]), not tokens."""
+        if inp.dim() == 2:
+            inp = inp.unsqueeze(0)
+        self.nsamples += inp.shape[0]
+        ops.hessian_accum(self.S, inp)
+
+    @torch.no_grad()
+    def finalize(self):
+        """One all-reduce of (S, nsamples) over the ranks, then H = (2 / n) * sym(S)."""
+        n = lcdist.allreduce_hessian(self.S, self.nsamples)
+        self.nsamples = n
+        self.H = ops.hessian_finalize(self.S, n)
+        self.S = None
+        return self.H
+
+    def _qrange(self):
+        return self.wquantizer._qrange()
+
+    @torch.no_grad()
+    def process_hessian_and_weights(self):
+        """gptq.py:128-176: dead columns, optional act-order permutation, damping, Cholesky inverse upper factor.
+        The three factorisations stay on torch.linalg (cuSOLVER): SURVEY.md §8f N1."""
+        if self.H is None:
+            self.finalize()
+        H = self.H
+        W = self.weight.data.clone().float()
+        dead = torch.diag(H) == 0
+        H[dead, dead] = 1
+        W[:, dead] = 0
+        if self.actorder:
+            self.perm = torch.argsort(torch.diag(H), descending=True)
+            W = W[:, self.perm].contiguous()
+            H = H[self.perm][:, self.perm]
+            self.invperm = torch.argsort(self.perm)
+        damp = self.percdamp * torch.mean(torch.diag(H))
+        diag = torch.arange(self.columns, device=H.device)
+        H[diag, diag] += damp
+        H = torch.linalg.cholesky(H)
+        H = torch.cholesky_inverse(H)
+        H = torch.linalg.cholesky(H, upper=True)
+        self.H = None
+        return W, H.contiguous()
+
+    @torch.no_grad()
+    def quantize(self, static_scales=None, static_zeros=None):
+        """Returns the error-compensated float weight `tmp` in fp32 like the reference (gptq.py:178-197: the layer keeps
+        fp32 weights until deploy's w_qdq casts to the model dtype); per-group scales /
+        zeros are left in self.scales / self.zeros as [C/g, R] fp32 (`groups` of the reference, :380-409)."""
+        W, Hinv = self.process_hessian_and_weights()
+        wq = self.wquantizer
+        qmin, qmax = self._qrange()
+        gs = wq.group_size if wq.granularity == 'per_group' else 0
+        col_group = None
+        if gs > 0 and self.static_groups:
+            if static_scales is None:   # search_group_qparams (gptq.py:380-395): qparams of the original weight
+                _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data.float())
+                static_scales = s.reshape(self.rows, -1).t().contiguous()
+                static_zeros = None if wq.sym else z.reshape(self.rows, -1).t().contiguous()
+            if self.actorder:
+                col_group = (self.perm // gs).to(torch.int32)
+        elif gs <= 0 and static_scales is None:   # per_channel: search_layer_qparams (gptq.py:368-378)
+            _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data.float())
+            static_scales = s.reshape(1, self.rows)
+            static_zeros = None if wq.sym else z.reshape(1, self.rows)
+        tmp, losses, scales, zeros = ops.gptq_weight_transform(
+            W, Hinv, self.blocksize, gs, qmin, qmax, wq.sym, wq.round_zp, static_scales=static_scales,
+            static_zeros=static_zeros, col_group=col_group)
+        self.losses = losses
+        self.scales, self.zeros = scales, zeros
+        if self.actorder:
+            tmp = tmp[:, self.invperm]
+        return tmp.reshape(self.weight.shape)
+
+    def buf_qparams(self):
+        """Per-group qparams in the layout `FakeQuantLinear` buffers use: [R * C/g, 1] (merge_qparams, gptq.py:345-356)."""
+        s = self.scales.t().reshape(-1, 1)
+        z = self.zeros.t().reshape(-1, 1) if self.zeros is not None else None
+        return s, z

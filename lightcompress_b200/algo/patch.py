@@ -1,0 +1,131 @@
+"""`patch_reference(ALGO_REGISTRY)`: rebind the hot methods of the reference's own algorithm classes onto the sm_100a
+kernels, leaving their block loop, hooks, bookkeeping and deploy untouched.
+
+The reference is not importable on the GPU box, so these bindings are exercised in tests/test_algo_gpu.py with stand-in
+classes that reproduce the attribute contract of gptq.py / awq.py / smoothquant.py (layers_cache, groups, qparams, ...).
+"""
+import os
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from . import awq as lcawq
+from . import dist as lcdist
+
+
+# ---- GPTQ (gptq.py) ------------------------------------------------------------------------------------------------------
+def _gptq_add_batch(orig):
+    def add_batch(self, layer, name, inp, out):
+        if not isinstance(layer, nn.Linear) or type(layer).__name__ == 'RotateLinear':
+            return orig(self, layer, name, inp, out)      # Conv2d / Conv1D / online rotation: reference path
+        if inp.dim() == 2:
+            inp = inp.unsqueeze(0)
+        cache = self.layers_cache[name]
+        cache['nsamples'] += inp.shape[0]
+        cache['lcb_unnormalised'] = True                   # H holds sum x x^T until process_hessian_and_weights
+        ops.hessian_accum(cache['H'], inp)
+    return add_batch
+
+
+def _gptq_process(orig):
+    def process_hessian_and_weights(self, layer, name):
+        cache = self.layers_cache[name]
+        if cache.pop('lcb_unnormalised', False):
+            n = lcdist.allreduce_hessian(cache['H'], cache['nsamples'])   # one collective per linear (gptq.py:292-295)
+            ops.hessian_finalize(cache['H'], n)
+        return orig(self, layer, name)
+    return process_hessian_and_weights
+
+
+def _gptq_weight_transform(orig):
+    def weight_transform(self, W, Hinv, Losses, tmp):
+        wq = self.wquantizer
+        if type(wq).__name__ != 'IntegerQuantizer' or self.blocksize > 128 or self.blocksize % 8 or W.shape[1] % 8:
+            return orig(self, W, Hinv, Losses, tmp)
+        R = W.shape[0]
+        per_group = wq.granularity == 'per_group'
+        gs = wq.group_size if per_group else 0
+        static_scales = static_zeros = col_group = None
+        if per_group and self.static_groups:
+            static_scales = torch.stack([g['scale'].reshape(-1).float() for g in self.groups])
+            if not wq.sym:
+                static_zeros = torch.stack([g['zero'].reshape(-1).float() for g in self.groups])
+            if self.actorder:
+                col_group = (self.perm // gs).to(torch.int32)
+        elif not per_group:
+            static_scales = self.qparams['scale'].reshape(1, R).float()
+            if not wq.sym:
+                static_zeros = self.qparams['zero'].reshape(1, R).float()
+        Wc = W if W.is_contiguous() else W.contiguous()
+        t, l, sc, zp = ops.gptq_weight_transform(Wc, Hinv.contiguous(), self.blocksize, gs, float(wq.qmin), float(wq.qmax),
+                                                 wq.sym, wq.round_zp, n_nonout=self.n_nonout, static_scales=static_scales,
+                                                 static_zeros=static_zeros, col_group=col_group)
+        if Wc is not W:
+            W.copy_(Wc)
+        tmp.copy_(t)
+        Losses.copy_(l)
+        if per_group and not self.static_groups:            # search_column_qparams bookkeeping (gptq.py:359-366)
+            dev = W.device
+            for g in range(sc.shape[0]):
+                q = {'scale': sc[g].reshape(R, 1), 'zero': zp[g].reshape(R, 1) if zp is not None else torch.tensor(0.0),
+                     'qmax': wq.qmax.to(dev), 'qmin': wq.qmin.to(dev)}
+                if g < len(self.groups):
+                    self.groups[g] = q
+                else:
+                    self.groups.append(q)
+            self.qparams = dict(self.groups[sc.shape[0] - 1])
+    return weight_transform
+
+
+# ---- AWQ (awq.py) ----------------------------------------------------------------------------------------------------------
+def _awq_search(orig):
+    def search_scale_subset(self, prev_op, layers_dict, input, inspect_module, is_gqa, subset_kwargs):
+        layers = list(layers_dict.values())
+        fused = (len(layers) == 1 and inspect_module is layers[0] and isinstance(inspect_module, nn.Linear)
+                 and inspect_module.bias is None and len(input) == 1 and not is_gqa and self.w_only
+                 and not self.padding_mask and getattr(self, 'awq_bs', None) is None
+                 and input[0].dtype in (torch.bfloat16, torch.float16)
+                 and inspect_module.weight.dtype == input[0].dtype and int(os.environ.get('WORLD_SIZE', '1')) == 1)
+        if not fused:
+            return orig(self, prev_op, layers_dict, input, inspect_module, is_gqa, subset_kwargs)
+        x = input[0].to(inspect_module.weight.device)
+        scales, _, _ = lcawq.awq_search_scale(x, inspect_module.weight.data, self.wquantizer, self.trans_version)
+        return scales
+    return search_scale_subset
+
+
+# ---- SmoothQuant (smoothquant.py) ----------------------------------------------------------------------------------------
+def _sq_act_scale(orig):
+    def get_act_scale(self, tensors):
+        acc = None
+        for x in tensors:
+            x = x.cuda()
+            if acc is None:
+                acc = torch.zeros(x.shape[-1], dtype=torch.float32, device=x.device)
+            ops.col_absstat(x, acc, mean=False)
+        return acc
+    return get_act_scale
+
+
+def patch_reference(registry):
+    """registry: llmc.utils.registry_factory.ALGO_REGISTRY (or any dict name -> class). Returns the patched names."""
+    done = []
+    g = registry.get('GPTQ')
+    if g is not None and not getattr(g, '_lcb_patched', False):
+        g.add_batch = _gptq_add_batch(g.add_batch)
+        g.process_hessian_and_weights = _gptq_process(g.process_hessian_and_weights)
+        g.weight_transform = _gptq_weight_transform(g.weight_transform)
+        g._lcb_patched = True
+        done.append('GPTQ')
+    a = registry.get('Awq')
+    if a is not None and not getattr(a, '_lcb_patched', False):
+        a.search_scale_subset = _awq_search(a.search_scale_subset)
+        a._lcb_patched = True
+        done.append('Awq')
+    s = registry.get('SmoothQuant')
+    if s is not None and not getattr(s, '_lcb_patched', False):
+        s.get_act_scale = _sq_act_scale(s.get_act_scale)
+        s._lcb_patched = True
+        done.append('SmoothQuant')
+    return done

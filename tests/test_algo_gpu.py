@@ -1,0 +1,183 @@
+"""GPU tests of the algorithm layer: GPTQLayer vs the oracle, the four ALGO_REGISTRY plug-ins end to end on a tiny
+random-init Llama, and patch_reference on stand-in classes with the reference's attribute contract."""
+import copy
+
+import pytest
+import torch
+import torch.nn as nn
+
+from lightcompress_b200 import algo
+from lightcompress_b200 import quant as Q
+from oracle import gptq_oracle as go
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm())
+
+
+def test_gptq_layer_matches_oracle():
+    g = torch.Generator().manual_seed(0)
+    R, C, T = 96, 384, 512
+    W = (torch.randn(R, C, generator=g) * 0.02).to(torch.bfloat16)
+    xs = [(torch.randn(1, T, C, generator=g) * torch.exp(0.5 * torch.randn(C, generator=g))).to(torch.bfloat16) for _ in range(3)]
+    H = torch.zeros(C, C)
+    n = 0
+    for x in xs:
+        n = go.add_batch(H, n, x)
+    Wf, Hinv = go.process_hessian(H, W, 0.01)
+    tmp_o, loss_o, sc_o, zp_o = go.weight_transform(Wf, Hinv, 128, 128, dict(kind=0, sym=False, qmin=0.0, qmax=15.0))
+    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=128)
+    layer = algo.GPTQLayer(W.to(DEV), wq, blocksize=128, percdamp=0.01)
+    for x in xs:
+        layer.add_batch(x.to(DEV))
+    tmp = layer.quantize()
+    assert tmp.dtype == torch.float32 and tmp.shape == W.shape
+    assert _rel(tmp.cpu(), tmp_o) < 2e-3
+    assert _rel(layer.scales.cpu(), sc_o) < 2e-3
+    s, z = layer.buf_qparams()
+    assert s.shape == (R * C // 128, 1) and z.shape == s.shape
+    # deploy-time fake quant with the stored qparams lands on the quantization grid
+    args = {'scales': s, 'zeros': z, 'qmax': wq.qmax, 'qmin': wq.qmin}
+    fq = wq.fake_quant_weight_static(tmp, args)
+    codes = torch.round(fq.reshape(-1, 128) / s + z)
+    assert float(codes.min()) >= 0 and float(codes.max()) <= 15
+
+
+def _tiny_llama(dtype=torch.bfloat16, seed=0):
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(seed)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=4, max_position_embeddings=256)
+    m = LlamaForCausalLM(cfg).to(dtype).to(DEV).eval()
+    return m
+
+
+def _calib(n=4, seq=128, vocab=512, seed=1):
+    g = torch.Generator().manual_seed(seed)
+    return [{'input_ids': torch.randint(0, vocab, (1, seq), generator=g).to(DEV)} for _ in range(n)]
+
+
+def _run(method, quant_cfg, model, data):
+    ad = algo.adapters.LlamaAdapter(model)
+    inp = ad.collect_first_block_input(data)
+    a = algo.ALGO_REGISTRY[method](ad, quant_cfg, inp, None, {'calib': {'seq_len': 128}})
+    a.run_block_loop()
+    a.deploy('fake_quant')
+    return a
+
+
+W4 = {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128}
+
+
+@torch.no_grad()
+def _logits(model, data):
+    return torch.cat([model(**b).logits.float() for b in data])
+
+
+@pytest.mark.parametrize('method,cfg', [
+    ('RTN', {'weight': W4}),
+    ('GPTQ', {'weight': W4, 'special': {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
+                                        'true_sequential': True}}),
+    ('Awq', {'weight': W4, 'special': {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}}),
+    ('SmoothQuant', {'weight': {'bit': 8, 'symmetric': True, 'granularity': 'per_channel'},
+                     'act': {'bit': 8, 'symmetric': True, 'granularity': 'per_token'}, 'special': {'alpha': 0.8}}),
+])
+def test_block_loop_end_to_end(method, cfg):
+    import lightcompress_b200.algo.adapters  # noqa: F401
+    model = _tiny_llama()
+    data = _calib()
+    ref = _logits(model, data)
+    q = copy.deepcopy(model)
+    a = _run(method, copy.deepcopy(cfg), q, data)
+    out = _logits(q, data)
+    assert torch.isfinite(out).all()
+    err = float((out - ref).pow(2).mean() / ref.pow(2).mean())
+    assert err < 0.2, err
+    # every block linear is on a 4-bit grid: at most 16 distinct values per group of 128 (w-only methods)
+    if method in ('RTN', 'Awq'):
+        for blk in a.blocks:
+            for n, m in a.model.get_block_linears(blk).items():
+                g = m.weight.data.float().reshape(-1, 128).sort(dim=1).values
+                distinct = 1 + (g[:, 1:] != g[:, :-1]).sum(dim=1)
+                assert int(distinct.max()) <= 16, n
+    if method == 'Awq':
+        assert len(a.best_index) == 2 * 4   # 4 subsets per block searched (v->o has matching shapes here)
+
+
+def test_gptq_beats_rtn_on_calibration_data():
+    model = _tiny_llama(seed=3)
+    data = _calib(n=8, seed=4)
+    ref = _logits(model, data)
+    errs = {}
+    for method, cfg in (('RTN', {'weight': W4}),
+                        ('GPTQ', {'weight': W4, 'special': {'actorder': False, 'static_groups': False, 'percdamp': 0.01,
+                                                            'blocksize': 128, 'true_sequential': True}})):
+        q = copy.deepcopy(model)
+        _run(method, copy.deepcopy(cfg), q, data)
+        errs[method] = float((_logits(q, data) - ref).pow(2).mean())
+    assert errs['GPTQ'] < errs['RTN'], errs
+
+
+# ---- patch_reference on stand-ins that follow the reference's attribute contract (gptq.py / awq.py) ------------------------
+class _RefLikeGPTQ(object):
+    """Attributes as gptq.py:29-56, 104-176, 297-309; the three hot methods raise unless patched."""
+
+    def __init__(self, wquantizer, blocksize=128):
+        self.wquantizer, self.blocksize = wquantizer, blocksize
+        self.static_groups = self.actorder = self.owq = False
+        self.percdamp = 0.01
+        self.layers_cache, self.groups, self.qparams = {}, [], {}
+
+    def layer_init(self, layer, name):
+        C = layer.weight.shape[1]
+        self.layers_cache[name] = {'H': torch.zeros((C, C), device=layer.weight.device), 'nsamples': 0, 'columns': C}
+        self.columns, self.n_out, self.n_nonout = C, 0, C
+
+    def add_batch(self, layer, name, inp, out):
+        raise AssertionError('reference path taken')
+
+    def process_hessian_and_weights(self, layer, name):   # the torch part of gptq.py:128-176
+        W = layer.weight.data.clone().float()
+        H = self.layers_cache[name]['H']
+        dead = torch.diag(H) == 0
+        H[dead, dead] = 1
+        W[:, dead] = 0
+        d = torch.arange(self.columns, device=H.device)
+        H[d, d] += self.percdamp * torch.mean(torch.diag(H))
+        H = torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(H)), upper=True)
+        return W, H
+
+    def weight_transform(self, W, Hinv, Losses, tmp):
+        raise AssertionError('reference path taken')
+
+
+def test_patch_reference_gptq_contract():
+    reg = {'GPTQ': _RefLikeGPTQ}
+    assert algo.patch_reference(reg) == ['GPTQ'] and algo.patch_reference(reg) == []
+    g = torch.Generator().manual_seed(5)
+    R, C = 64, 256
+    layer = nn.Linear(C, R, bias=False).to(DEV)
+    layer.weight.data = (torch.randn(R, C, generator=g) * 0.02).to(DEV)
+    xs = [torch.randn(1, 300, C, generator=g).to(torch.bfloat16) for _ in range(2)]
+    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=128)
+    obj = _RefLikeGPTQ(wq)
+    obj.layer_init(layer, 'l')
+    for x in xs:
+        obj.add_batch(layer, 'l', x.to(DEV), None)
+    assert obj.layers_cache['l']['nsamples'] == 2
+    W, Hinv = obj.process_hessian_and_weights(layer, 'l')
+    Losses, tmp = torch.zeros_like(W), torch.zeros_like(W)
+    obj.weight_transform(W, Hinv, Losses, tmp)
+    # oracle on the same inputs
+    H = torch.zeros(C, C)
+    n = 0
+    for x in xs:
+        n = go.add_batch(H, n, x)
+    Wf, Hinv_o = go.process_hessian(H, layer.weight.data.cpu(), 0.01)
+    tmp_o, loss_o, sc_o, zp_o = go.weight_transform(Wf, Hinv_o, 128, 128, dict(kind=0, sym=False, qmin=0.0, qmax=15.0))
+    assert _rel(tmp.cpu(), tmp_o) < 2e-3
+    assert len(obj.groups) == C // 128 and obj.groups[0]['scale'].shape == (R, 1) and obj.groups[1]['zero'].shape == (R, 1)
+    assert _rel(torch.stack([g_['scale'].reshape(-1) for g_ in obj.groups]).cpu(), sc_o) < 2e-3

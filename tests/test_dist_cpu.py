@@ -1,0 +1,70 @@
+"""Host logic of the sharded paths on gloo, world_size 2 (CPU): result-only collectives of SURVEY.md §8e."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from lightcompress_b200.algo import dist as lcdist
+    out = {}
+    # token-sharded Hessian: S_r = X_r^T X_r, one all-reduce, global batch count
+    g = torch.Generator().manual_seed(0)
+    X = torch.randn(4, 64, 16, generator=g)
+    mine = X[rank::world]
+    S = sum(x.t() @ x for x in mine)
+    n = lcdist.allreduce_hessian(S, mine.shape[0])
+    out['n'] = n
+    out['H'] = S * (2.0 / n)
+    # candidate sharding + MINLOC with ties -> lowest index
+    cands = lcdist.shard_candidates(20)
+    out['cands'] = cands
+    losses_all = [abs(i - 7) * 0.5 + (0.0 if i != 11 else -2.0) for i in range(20)]   # min at 7 (0.0) and 11 (0.0): tie
+    out['best'] = lcdist.argmin_across_ranks([losses_all[i] for i in cands], cands, torch.device('cpu'))
+    t = torch.tensor([float(rank), 5.0 - rank])
+    out['max'] = lcdist.allreduce_max(t)
+    q.put((rank, out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_result_only_collectives_world2():
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    g = torch.Generator().manual_seed(0)
+    X = torch.randn(4, 64, 16, generator=g)
+    H = sum(x.t() @ x for x in X) * (2.0 / 4)
+    for r in range(2):
+        assert res[r]['n'] == 4.0
+        assert torch.allclose(res[r]['H'], H, rtol=1e-6, atol=1e-6)
+        assert res[r]['cands'] == list(range(r, 20, 2))
+        assert res[r]['best'] == (0.0, 7)          # tie between 7 (rank 1) and 11 (rank 1)... lowest index wins
+        assert torch.equal(res[r]['max'], torch.tensor([1.0, 5.0]))
+
+
+def test_single_process_is_identity():
+    from lightcompress_b200.algo import dist as lcdist
+    S = torch.eye(3)
+    assert lcdist.allreduce_hessian(S, 5) == 5 and torch.equal(S, torch.eye(3))
+    assert lcdist.shard_candidates(4) == [0, 1, 2, 3]
+    assert lcdist.argmin_across_ranks([3.0, 1.0, 1.0], [0, 1, 2], torch.device('cpu')) == (1.0, 1)
