@@ -1,10 +1,11 @@
 """bench.py — headline benchmark of the B200-native LLMC quantization hot path.
 
 Metric (BASELINE.json): fake-quant HBM GB/s on Llama-3-8B shapes (+ GPTQ calibration s/block as extra keys).
-A "step" = one pass of the w4a16 group-128 fake-quant (IntegerQuantizer(4, asym, per_group 128)
-.fake_quant_weight_dynamic, the quantization of BASELINE configs[1]) over the 7 linear weights of one
-Llama-3-8B transformer block (218.1 M bf16 elements, 436 MB in + 436 MB out: larger than the 126 MB L2, so no
-flush is needed between iterations).
+A "step" = one pass of the w4a16 group-128 fake-quant (IntegerQuantizer(4, asym, per_group 128), the quantization
+of BASELINE configs[1]) over the 7 linear weights of one Llama-3-8B transformer block (218.1 M bf16 elements,
+436 MB in + 436 MB out: larger than the 126 MB L2, so no flush is needed between iterations), issued as ONE
+multi-tensor launch (fake_quant_weights_dynamic -> lcb_fakequant_multi), the way the block loop deploys a block.
+`extras.per_tensor_calls_GBps` is the same work through 7 reference-API calls (fake_quant_weight_dynamic).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
@@ -101,6 +102,50 @@ def cpu_baseline(steps=3, sample=('q_proj', 4096, 4096)):
             'sample': f'{sample[0]} [{r},{c}] bf16 w4 asym g128, best of {steps} (oracle/lc_oracle.c, OpenMP)'}, best
 
 
+def extras(torch, dev, tf_peak):
+    """Tensor-path numbers of the same hot path (short runs): Hessian, GPTQ update, AWQ candidate at Llama-3-8B shapes."""
+    from lightcompress_b200 import ops
+    from lightcompress_b200.quant import IntegerQuantizer
+    res = {}
+
+    def ev(fn, rep):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(rep):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) * 1e-3 / rep
+
+    C, T = 4096, 8192
+    g = torch.Generator(device=dev).manual_seed(0)
+    x = torch.randn(T, C, device=dev, generator=g).to(torch.bfloat16)
+    S = torch.zeros(C, C, device=dev)
+    t = ev(lambda: ops.hessian_accum(S, x), 20)
+    res['hessian'] = {'C': C, 'T': T, 'ms': t * 1e3, 'gemm_equiv_TFLOPs': 2.0 * T * C * C / t / 1e12,
+                      'hw_syrk_TFLOPs': 2.0 * T * C * C / t / 1e12 * 33 / 64, 'frac_of_bf16_peak_hw': 2.0 * T * C * C / t / 1e12 * 33 / 64 / tf_peak}
+    ops.hessian_finalize(S, 20)
+    d = torch.arange(C, device=dev)
+    S[d, d] += 0.01 * torch.mean(torch.diag(S))
+    t0 = time.perf_counter()
+    Hinv = torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(S)), upper=True).contiguous()
+    torch.cuda.synchronize()
+    res['cholesky_chain_ms_C4096'] = (time.perf_counter() - t0) * 1e3
+    W = torch.randn(C, C, device=dev, generator=g) * 0.02
+    t = ev(lambda: ops.gptq_weight_transform(W.clone(), Hinv, 128, 128, 0.0, 15.0, False), 2)
+    res['gptq_update_q_proj_ms'] = t * 1e3
+    Wb = W.to(torch.bfloat16)
+    org = torch.nn.functional.linear(x, Wb)
+    cand = (torch.rand(4, C, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    wq = IntegerQuantizer(4, False, 'per_group', group_size=128)
+    t = ev(lambda: ops.awq_candidates(Wb, x, org, cand, wq), 3) / 4
+    res['awq_candidate'] = {'T': T, 'R': C, 'C': C, 'ms': t * 1e3, 'TFLOPs': 2.0 * T * C * C / t / 1e12,
+                            'frac_of_bf16_peak': 2.0 * T * C * C / t / 1e12 / tf_peak}
+    return res
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
@@ -155,6 +200,9 @@ def main():
     q = IntegerQuantizer(4, False, 'per_group', group_size=128)
 
     def step():
+        return q.fake_quant_weights_dynamic(ws)
+
+    def step_per_tensor():
         return [q.fake_quant_weight_dynamic(w) for w in ws]
 
     def sync():
@@ -187,9 +235,30 @@ def main():
     for h, w in zip(hin, ws):
         h.copy_(w)
 
+    # three streams: H2D of tensor i+1, fake-quant of tensor i and D2H of tensor i-1 overlap (PCIe is full duplex)
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    din = [torch.empty_like(w) for w in ws]
+
     def e2e_step():
-        for h, o in zip(hin, hout):
-            o.copy_(q.fake_quant_weight_dynamic(h.to(dev, non_blocking=True)), non_blocking=True)
+        cur = torch.cuda.current_stream(dev)
+        s_in.wait_stream(cur)
+        evs = []
+        for h, d in zip(hin, din):
+            with torch.cuda.stream(s_in):
+                d.copy_(h, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(s_in)
+            evs.append(ev)
+        for ev, d, o in zip(evs, din, hout):
+            cur.wait_event(ev)
+            r = q.fake_quant_weight_dynamic(d)
+            done = torch.cuda.Event()
+            done.record(cur)
+            r.record_stream(s_out)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(done)
+                o.copy_(r, non_blocking=True)
+        cur.wait_stream(s_out)
 
     e2e_steps = max(2, min(args.steps, 5))
     e2e_step()
@@ -208,10 +277,10 @@ def main():
 
     hbm_peak, tf_peak, which = peaks()
     per_gpu = alg_bytes / (ms * 1e-3) / 1e9
-    roofline = {'bound': 'hbm', 'kernel': 'fq_subwarp_kernel<bf16,NV=1,UNROLL=4,int>', 'achieved': per_gpu,
+    roofline = {'bound': 'hbm', 'kernel': 'fq_group_multi_kernel<bf16,NV=2,int,CHAIN_BF16_SMALL>', 'achieved': per_gpu,
                 'peak': hbm_peak, 'peak_source': f'{which} (MEASURED_PEAKS.json hbm_gbs)', 'unit': 'GB/s',
                 'frac': per_gpu / hbm_peak, 'frac_of_nominal_8TBs': per_gpu / 8000.0, 'traffic': None,
-                'algorithmic_bytes_per_launch': 'numel*4 (bf16 in + bf16 out); 7 launches per step'}
+                'algorithmic_bytes_per_launch': 'numel*4 = 872.4 MB (bf16 in + bf16 out of 218.1M elements); 1 launch per step'}
     tr = os.path.join(ROOT, 'profiles', 'fakequant_traffic.json')
     if os.path.exists(tr):
         roofline['traffic'] = json.load(open(tr)).get('dram_bytes_per_launch')
@@ -221,14 +290,22 @@ def main():
            'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
            'config': {'workload': WORKLOAD, 'l2': 'inputs (436 MB) + outputs (436 MB) per step exceed the 126 MB L2',
                       'parallelism': f'layers/blocks sharded x{world}, no collective'},
-           'clocks': clocks, 'e2e': e2e, 'gpu_launches': 7 * args.steps, 'roofline': roofline}
+           'clocks': clocks, 'e2e': e2e, 'gpu_launches': args.steps, 'roofline': roofline}
 
     if rank == 0 and not args.no_extras:
-        try:
-            from bench_extras import extras
-            out['extras'] = extras(torch, dev, hbm_peak, tf_peak)
-        except ImportError:
-            pass
+        for _ in range(3):
+            step_per_tensor()
+        sync()
+        e0.record()
+        for _ in range(args.steps):
+            step_per_tensor()
+        e1.record()
+        sync()
+        pt_ms = e0.elapsed_time(e1) / args.steps
+        out['extras'] = {'per_tensor_calls_GBps': alg_bytes / (pt_ms * 1e-3) / 1e9, 'per_tensor_calls_ms': pt_ms}
+        del ws, hin, hout
+        torch.cuda.empty_cache()
+        out['extras'].update(extras(torch, dev, tf_peak))
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out['cpu_baseline'] = cpu_baseline()[0]
     if rank == 0:

@@ -98,6 +98,16 @@ int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t 
 int64_t lcb_fakequant_workspace_bytes(void);
 
 /*
+ * Dynamic fake-quant (LCB_OUT_FAKE, IntegerQuantizer, units of 1 x unit_cols with unit_cols * sizeof(dtype) <= 1 KiB)
+ * of up to 16 tensors in ONE launch — e.g. the 7 linear weights of a transformer block at deploy time
+ * (base_bq.py:899-1006 calls w_qdq once per linear). ins / outs / rows / cols are HOST arrays of n entries; every
+ * tensor is a contiguous [rows[i], cols[i]] matrix of spec->dtype with cols[i] % unit_cols == 0. Same arithmetic as
+ * lcb_fakequant. Returns LCB_E_UNSUPPORTED for specs outside that envelope (callers then loop over lcb_fakequant).
+ */
+int lcb_fakequant_multi(const void* const* ins, void* const* outs, const int64_t* rows, const int64_t* cols, int32_t n,
+                        int64_t unit_cols, const lcb_quant_spec* spec, void* stream);
+
+/*
  * Block-wise FP8 dequantisation y = x_fp8 * s[block] -> bf16/f16/f32
  * Replaces weight_cast_to_bf16 (quant.py:18-31, kernel.py:86-138).
  */

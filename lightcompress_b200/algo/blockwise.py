@@ -209,9 +209,16 @@ class BaseBlockwiseQuantization(object):
                                       'wquantizer.real_quant_weight_dynamic per layer')
         for block in self.blocks:
             block.to(self.dev)
-            for name, m in self.model.get_block_linears(block).items():
-                m.weight.data = self.w_qdq(m, self.wquantizer).to(getattr(self, 'model_dtype', None) or m.weight.dtype)
-                if not self.w_only:
+            linears = list(self.model.get_block_linears(block).values())
+            if type(self).w_qdq is BaseBlockwiseQuantization.w_qdq:
+                # plain dynamic w_qdq: all linears of the block in one launch (lcb_fakequant_multi)
+                for m, q in zip(linears, self.wquantizer.fake_quant_weights_dynamic([m.weight.data for m in linears])):
+                    m.weight.data = q
+            else:
+                for m in linears:
+                    m.weight.data = self.w_qdq(m, self.wquantizer).to(getattr(self, 'model_dtype', None) or m.weight.dtype)
+            if not self.w_only:
+                for m in linears:
                     m.register_forward_pre_hook(self._act_hook)
 
     def _act_hook(self, module, args):

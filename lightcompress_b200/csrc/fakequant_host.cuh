@@ -203,6 +203,83 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
 
 }  // namespace lcb
 
+namespace lcb {
+// ---- several tensors, one launch (per_group / short-row dynamic fake-quant) ----------------------------------------------
+template <typename T>
+static int fakequant_multi_typed(const void* const* ins, void* const* outs, const int64_t* rows, const int64_t* cols, int n,
+                                 int64_t uc, SpecD sp, cudaStream_t st) {
+  constexpr int VEC = TI<T>::VEC;
+  if (sp.kind != LCB_KIND_INT || sp.out_mode != LCB_OUT_FAKE || sp.math_dtype != sp.dtype) return LCB_E_UNSUPPORTED;
+  if (uc % VEC) return LCB_E_UNSUPPORTED;
+  const int64_t nvec = uc / VEC;
+  if (nvec > 64) return LCB_E_UNSUPPORTED;
+  int lanes = 4;
+  while (lanes * 2 < nvec && lanes < 32) lanes <<= 1;
+  const int nv = (int)((nvec + lanes - 1) / lanes);
+  const int nvt = nv <= 1 ? 1 : 2;
+  const int u = 8 / nvt;
+  const int64_t upw = (int64_t)u * (32 / lanes);
+  MultiDesc md;
+  md.n = n;
+  md.chunk_start[0] = 0;
+  for (int t = 0; t < n; ++t) {
+    if (!ins[t] || !outs[t] || rows[t] < 0 || cols[t] < 0) return LCB_E_INVALID;
+    if (cols[t] % uc) return LCB_E_SHAPE;
+    if (!aligned16(ins[t]) || !aligned16(outs[t])) return LCB_E_ALIGN;
+    md.in[t] = ins[t];
+    md.out[t] = outs[t];
+    md.n_units[t] = rows[t] * (cols[t] / uc);
+    md.chunk_start[t + 1] = md.chunk_start[t] + (md.n_units[t] + upw - 1) / upw;
+  }
+  for (int t = n; t < kMaxMulti; ++t) {
+    md.in[t] = nullptr;
+    md.out[t] = nullptr;
+    md.n_units[t] = 0;
+    md.chunk_start[t + 1] = md.chunk_start[n];
+  }
+  const int64_t chunks = md.chunk_start[n];
+  if (chunks == 0) return LCB_OK;
+  const FastSpec fs = make_fastspec<T>(sp);
+  const int grid = grid_for((chunks + 7) / 8, 16);
+#define LCB_LAUNCH_MULTI(NVc, CH) \
+  fq_group_multi_kernel<T, NVc, 0, CH><<<grid, 256, 0, st>>>(md, (int)uc, lanes, sp, fs)
+#define LCB_LAUNCH_MULTI_NV(CH)              \
+  {                                          \
+    if (nvt == 1) LCB_LAUNCH_MULTI(1, CH);   \
+    else LCB_LAUNCH_MULTI(2, CH);            \
+  }
+  if (fs.chain == CHAIN_F32) LCB_LAUNCH_MULTI_NV(CHAIN_F32)
+  else if (TI<T>::ID == LCB_BF16 && fs.chain == CHAIN_BF16_SMALL) {
+    if constexpr (TI<T>::ID == LCB_BF16) LCB_LAUNCH_MULTI_NV(CHAIN_BF16_SMALL)
+  } else if (TI<T>::ID == LCB_BF16 && fs.chain == CHAIN_BF16_WIDE) {
+    if constexpr (TI<T>::ID == LCB_BF16) LCB_LAUNCH_MULTI_NV(CHAIN_BF16_WIDE)
+  } else if (TI<T>::ID == LCB_F16 && fs.chain == CHAIN_F16) {
+    if constexpr (TI<T>::ID == LCB_F16) LCB_LAUNCH_MULTI_NV(CHAIN_F16)
+  } else return LCB_E_UNSUPPORTED;
+#undef LCB_LAUNCH_MULTI_NV
+#undef LCB_LAUNCH_MULTI
+  LCB_CUDA_CHECK_LAUNCH("fq_group_multi");
+  return LCB_OK;
+}
+}  // namespace lcb
+
+extern "C" int lcb_fakequant_multi(const void* const* ins, void* const* outs, const int64_t* rows, const int64_t* cols,
+                                   int32_t n, int64_t unit_cols, const lcb_quant_spec* spec, void* stream) {
+  using namespace lcb;
+  if (!ins || !outs || !rows || !cols || !spec || n < 0 || unit_cols < 1) return LCB_E_INVALID;
+  if (n == 0) return LCB_OK;
+  if (n > kMaxMulti) return LCB_E_UNSUPPORTED;
+  if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  SpecD sp = make_specd(spec);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (spec->dtype) {
+    case LCB_F32: return fakequant_multi_typed<float>(ins, outs, rows, cols, n, unit_cols, sp, st);
+    case LCB_F16: return fakequant_multi_typed<__half>(ins, outs, rows, cols, n, unit_cols, sp, st);
+    case LCB_BF16: return fakequant_multi_typed<__nv_bfloat16>(ins, outs, rows, cols, n, unit_cols, sp, st);
+    default: return LCB_E_UNSUPPORTED;
+  }
+}
+
 extern "C" int64_t lcb_fakequant_workspace_bytes(void) { return (int64_t)(2 * lcb::kMaxParts + 8) * sizeof(float); }
 
 extern "C" int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t rows, int64_t cols,

@@ -169,10 +169,11 @@ enum { CHAIN_ANY_OUT = -1 };  // template value: runtime out_mode, out-of-line g
 
 // CHAIN: element chain compiled in. CHAIN_ANY_OUT serves every out_mode through quant_store_vec_generic; the others
 // are LCB_OUT_FAKE only (the host guarantees it).
+// One warp-iteration: the warp's chunk of U * (32 / lanes) consecutive units of the tensor (in, out, n_units).
 template <typename T, int NV, int KINDC, int CHAIN>
-__global__ void __launch_bounds__(256)
-    fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
-                    void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
+__device__ __forceinline__ void fq_group_chunk(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
+                                               void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes,
+                                               int64_t chunk, const SpecD& sp, const FastSpec& fs) {
   constexpr int VEC = TI<T>::VEC;
   constexpr int U = NV >= 8 ? 1 : 8 / NV;
   using R = Range<T>;
@@ -181,88 +182,120 @@ __global__ void __launch_bounds__(256)
   const int lane_in = lane & (lanes - 1);
   const int spw = 32 / lanes;          // sub-warps (units) per warp per k
   const int sub_in_warp = lane / lanes;
+  const int64_t upw = (int64_t)U * spw;  // units per warp per iteration
+  const int64_t unit0 = chunk * upw + sub_in_warp;  // unit of k: unit0 + k * spw
+  uint4 raw[U][NV];
+#pragma unroll
+  for (int k = 0; k < U; ++k) {
+    const int64_t unit = unit0 + (int64_t)k * spw;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = j * lanes + lane_in;
+      raw[k][j] = (unit < n_units && v < nvec) ? ld_stream(in + unit * unit_len + (int64_t)v * VEC)
+                                               : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < U; ++k) {
+    const int64_t unit = unit0 + (int64_t)k * spw;
+    typename R::P rg = R::init();
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = j * lanes + lane_in;
+      if (v < nvec) rg = R::join(rg, R::from_vec(raw[k][j]));
+    }
+    for (int o = lanes >> 1; o > 0; o >>= 1) rg = R::join(rg, R::shfl_xor(rg, o));
+    const float mx = R::mx(rg), mn = R::mn(rg);
+    UnitQ u;
+    qparams_unit<T>(mn, mx, sp, fs, u);
+    if (unit >= n_units) continue;  // sub-warp uniform; no shuffles below
+    const int64_t e0 = unit * unit_len + (int64_t)lane_in * VEC;
+    if (u.exact) {  // sub-warp uniform, rare: literal chain, qparams recomputed literally as well
+      if (lane_in == 0) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
+      if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j)
+          if (j * lanes + lane_in < nvec)
+            quant_store_vec_literal<T>(raw[k][j], mn, mx, sp, out, e0 + (int64_t)j * lanes * VEC);
+      }
+      continue;
+    }
+    if (lane_in == 0) write_qparams(scales, zeros, unit, u, sp);
+    if (CHAIN == CHAIN_ANY_OUT) {
+      if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j)
+          if (j * lanes + lane_in < nvec)
+            quant_store_vec_generic<T, KINDC>(raw[k][j], u, sp, out, e0 + (int64_t)j * lanes * VEC);
+      }
+      continue;
+    }
+    T* o = reinterpret_cast<T*>(out) + e0;
+    UnitP p;
+    if (CHAIN == CHAIN_BF16_SMALL || CHAIN == CHAIN_BF16_WIDE) {
+      p.lo2 = pack_bf16x2(u.lo, u.lo);
+      p.hi2 = pack_bf16x2(u.hi, u.hi);
+      p.s2 = pack_bf16x2(u.s_out, u.s_out);
+    } else if (CHAIN == CHAIN_F16) {
+      p.lo2 = pack_f16x2(u.lo, u.lo);
+      p.hi2 = pack_f16x2(u.hi, u.hi);
+      p.s2 = pack_f16x2(u.s_out, u.s_out);
+    }
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const uint4 w = raw[k][j];
+      uint4 r4;
+      if (CHAIN == CHAIN_BF16_SMALL)
+        r4 = make_uint4(fq2_bf16_small(w.x, u.r, p), fq2_bf16_small(w.y, u.r, p), fq2_bf16_small(w.z, u.r, p),
+                        fq2_bf16_small(w.w, u.r, p));
+      else if (CHAIN == CHAIN_BF16_WIDE)
+        r4 = make_uint4(fq2_bf16_wide(w.x, u.r, p, u.s_out), fq2_bf16_wide(w.y, u.r, p, u.s_out),
+                        fq2_bf16_wide(w.z, u.r, p, u.s_out), fq2_bf16_wide(w.w, u.r, p, u.s_out));
+      else if (CHAIN == CHAIN_F16)
+        r4 = make_uint4(fq2_f16(w.x, u.s, u.r, p), fq2_f16(w.y, u.s, u.r, p), fq2_f16(w.z, u.s, u.r, p),
+                        fq2_f16(w.w, u.s, u.r, p));
+      else
+        r4 = quant_vec_fast_f32<T, KINDC>(w, u, sp.kind);
+      if (j * lanes + lane_in < nvec) st_stream(o + (int64_t)j * lanes * VEC, r4);
+    }
+  }
+}
+
+template <typename T, int NV, int KINDC, int CHAIN>
+__global__ void __launch_bounds__(256)
+    fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
+                    void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
+  constexpr int U = NV >= 8 ? 1 : 8 / NV;
   const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  const int64_t upw = (int64_t)U * spw;  // units per warp per iteration
-  const int64_t iters = (n_units + n_warps * upw - 1) / (n_warps * upw);
+  const int64_t upw = (int64_t)U * (32 / lanes);
+  const int64_t chunks = (n_units + upw - 1) / upw;
+  for (int64_t c = warp_id; c < chunks; c += n_warps)
+    fq_group_chunk<T, NV, KINDC, CHAIN>(in, out, scales, zeros, n_units, unit_len, lanes, c, sp, fs);
+}
 
-  for (int64_t it = 0; it < iters; ++it) {
-    const int64_t unit0 = (it * n_warps + warp_id) * upw + sub_in_warp;  // unit of k: unit0 + k * spw
-    uint4 raw[U][NV];
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-      const int64_t unit = unit0 + (int64_t)k * spw;
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        raw[k][j] = (unit < n_units && v < nvec) ? ld_stream(in + unit * unit_len + (int64_t)v * VEC)
-                                                 : make_uint4(0u, 0u, 0u, 0u);
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < U; ++k) {
-      const int64_t unit = unit0 + (int64_t)k * spw;
-      typename R::P rg = R::init();
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const int v = j * lanes + lane_in;
-        if (v < nvec) rg = R::join(rg, R::from_vec(raw[k][j]));
-      }
-      for (int o = lanes >> 1; o > 0; o >>= 1) rg = R::join(rg, R::shfl_xor(rg, o));
-      const float mx = R::mx(rg), mn = R::mn(rg);
-      UnitQ u;
-      qparams_unit<T>(mn, mx, sp, fs, u);
-      if (unit >= n_units) continue;  // sub-warp uniform; no shuffles below
-      const int64_t e0 = unit * unit_len + (int64_t)lane_in * VEC;
-      if (u.exact) {  // sub-warp uniform, rare: literal chain, qparams recomputed literally as well
-        if (lane_in == 0) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
-        if (sp.out_mode != LCB_OUT_NONE) {
-#pragma unroll
-          for (int j = 0; j < NV; ++j)
-            if (j * lanes + lane_in < nvec)
-              quant_store_vec_literal<T>(raw[k][j], mn, mx, sp, out, e0 + (int64_t)j * lanes * VEC);
-        }
-        continue;
-      }
-      if (lane_in == 0) write_qparams(scales, zeros, unit, u, sp);
-      if (CHAIN == CHAIN_ANY_OUT) {
-        if (sp.out_mode != LCB_OUT_NONE) {
-#pragma unroll
-          for (int j = 0; j < NV; ++j)
-            if (j * lanes + lane_in < nvec)
-              quant_store_vec_generic<T, KINDC>(raw[k][j], u, sp, out, e0 + (int64_t)j * lanes * VEC);
-        }
-        continue;
-      }
-      T* o = reinterpret_cast<T*>(out) + e0;
-      UnitP p;
-      if (CHAIN == CHAIN_BF16_SMALL || CHAIN == CHAIN_BF16_WIDE) {
-        p.lo2 = pack_bf16x2(u.lo, u.lo);
-        p.hi2 = pack_bf16x2(u.hi, u.hi);
-        p.s2 = pack_bf16x2(u.s_out, u.s_out);
-      } else if (CHAIN == CHAIN_F16) {
-        p.lo2 = pack_f16x2(u.lo, u.lo);
-        p.hi2 = pack_f16x2(u.hi, u.hi);
-        p.s2 = pack_f16x2(u.s_out, u.s_out);
-      }
-#pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        const uint4 w = raw[k][j];
-        uint4 r4;
-        if (CHAIN == CHAIN_BF16_SMALL)
-          r4 = make_uint4(fq2_bf16_small(w.x, u.r, p), fq2_bf16_small(w.y, u.r, p), fq2_bf16_small(w.z, u.r, p),
-                          fq2_bf16_small(w.w, u.r, p));
-        else if (CHAIN == CHAIN_BF16_WIDE)
-          r4 = make_uint4(fq2_bf16_wide(w.x, u.r, p, u.s_out), fq2_bf16_wide(w.y, u.r, p, u.s_out),
-                          fq2_bf16_wide(w.z, u.r, p, u.s_out), fq2_bf16_wide(w.w, u.r, p, u.s_out));
-        else if (CHAIN == CHAIN_F16)
-          r4 = make_uint4(fq2_f16(w.x, u.s, u.r, p), fq2_f16(w.y, u.s, u.r, p), fq2_f16(w.z, u.s, u.r, p),
-                          fq2_f16(w.w, u.s, u.r, p));
-        else
-          r4 = quant_vec_fast_f32<T, KINDC>(w, u, sp.kind);
-        if (j * lanes + lane_in < nvec) st_stream(o + (int64_t)j * lanes * VEC, r4);
-      }
-    }
+// Several tensors in ONE launch (same dtype / spec / unit length): e.g. the 7 linear weights of a transformer block.
+// Chunks of all tensors are laid end to end; a warp finds its tensor with a warp-uniform scan of the prefix table.
+constexpr int kMaxMulti = 16;
+struct MultiDesc {
+  const void* in[kMaxMulti];
+  void* out[kMaxMulti];
+  int64_t n_units[kMaxMulti];
+  int64_t chunk_start[kMaxMulti + 1];
+  int n;
+};
+
+template <typename T, int NV, int KINDC, int CHAIN>
+__global__ void __launch_bounds__(256)
+    fq_group_multi_kernel(const __grid_constant__ MultiDesc md, int unit_len, int lanes, SpecD sp, FastSpec fs) {
+  const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t chunks = md.chunk_start[md.n];
+  int t = 0;
+  for (int64_t c = warp_id; c < chunks; c += n_warps) {
+    while (c >= md.chunk_start[t + 1]) ++t;  // warp-uniform, monotone in c
+    fq_group_chunk<T, NV, KINDC, CHAIN>(reinterpret_cast<const T*>(md.in[t]), md.out[t], nullptr, nullptr, md.n_units[t],
+                                        unit_len, lanes, c - md.chunk_start[t], sp, fs);
   }
 }
 

@@ -73,7 +73,8 @@ def gptq_weight_transform(W, Hinv, blocksize, group_size, qmin, qmax, sym, round
     group_size, or group 0 when group_size <= 0) they are inputs. Returns (tmp, Losses, scales, zeros|None).
     """
     _need_cuda(W, Hinv, static_scales, static_zeros, col_group)
-    assert W.dtype == torch.float32 and W.is_contiguous() and Hinv.dtype == torch.float32 and Hinv.is_contiguous()
+    assert W.dtype == torch.float32 and W.is_contiguous() and Hinv.dtype == torch.float32
+    Hinv = Hinv.contiguous()   # torch.linalg.cholesky(upper=True) returns a transposed view
     R, C = W.shape
     n_nonout = C if n_nonout is None else int(n_nonout)
     lib = _cabi.load()

@@ -376,6 +376,41 @@ class BaseQuantizer(object):
         """quant.py:754-783 / :1100-1109."""
         return self._fake_dynamic(act, args, False)
 
+    def fake_quant_weights_dynamic(self, weights):
+        """Extension (not in the reference API): fake_quant_weight_dynamic of a list of weights in ONE launch
+        (lcb_fakequant_multi) — the deploy-time w_qdq of all linears of a transformer block. Falls back to one launch per
+        tensor for specs / layouts outside the multi-tensor envelope; results are identical either way."""
+        import ctypes
+        ws = list(weights)
+        ok = (len(ws) > 0 and self.granularity == 'per_group' and self.calib_algo == 'minmax'
+              and all(w.is_cuda and w.is_contiguous() and w.dtype == ws[0].dtype and w.device == ws[0].device
+                      and w.dim() >= 1 and w.shape[-1] >= self.group_size and w.shape[-1] % self.group_size == 0
+                      for w in ws))
+        if not ok:
+            return [self.fake_quant_weight_dynamic(w) for w in ws]
+        outs_all = []
+        lib = _cabi._lib or _cabi.load()
+        dt = ws[0].dtype
+        qmin, qmax = self._qrange()
+        spec = self._spec(dt, dt, dt, _cabi.OUT_FAKE, qmin, qmax, 1.0, 1.0, _DT[dt] + 1)
+        with _on_device(ws[0].device):
+            for i0 in range(0, len(ws), 16):
+                part = ws[i0:i0 + 16]
+                outs = [torch.empty_like(w) for w in part]
+                n = len(part)
+                ins_a = (ctypes.c_void_p * n)(*[w.data_ptr() for w in part])
+                outs_a = (ctypes.c_void_p * n)(*[o.data_ptr() for o in outs])
+                rows_a = (ctypes.c_int64 * n)(*[w.numel() // w.shape[-1] for w in part])
+                cols_a = (ctypes.c_int64 * n)(*[w.shape[-1] for w in part])
+                st = lib.lcb_fakequant_multi(ins_a, outs_a, rows_a, cols_a, n, self.group_size, spec,
+                                             _stream(ws[0].device.index))
+                if st == -3:   # LCB_E_UNSUPPORTED: spec outside the multi-tensor envelope
+                    outs = [self.fake_quant_weight_dynamic(w) for w in part]
+                elif st:
+                    _cabi.check(st, 'lcb_fakequant_multi')
+                outs_all.extend(outs)
+        return outs_all
+
     def fake_quant_weight_static(self, weight, args):
         """quant.py:785-831 / :1111-1140."""
         return self._fake_static(weight, args, True)

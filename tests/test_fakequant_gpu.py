@@ -153,3 +153,23 @@ def test_fp8_block_roundtrip():
     assert torch.allclose(scales2, scales, rtol=2 ** -8)
     d = (codes2.float() - codes.float()).abs()
     assert bool((d <= codes.float().abs() * 0.13 + 2 ** -9).all())
+
+
+def test_multi_tensor_launch_equals_single_launches():
+    torch.manual_seed(5)
+    for dtype, bit, sym, gs in [(torch.bfloat16, 4, False, 128), (torch.bfloat16, 8, True, 64), (torch.float16, 4, True, 128),
+                                (torch.float32, 4, False, 128), (torch.bfloat16, 3, False, 32)]:
+        shapes = [(64, 256), (8, 1024), (130, 384), (1, 128), (300, 128)]
+        ws = [(torch.randn(s, device=DEV) * 0.02).to(dtype) for s in shapes]
+        q = Q.IntegerQuantizer(bit, sym, 'per_group', group_size=gs)
+        multi = q.fake_quant_weights_dynamic(ws)
+        for w, m in zip(ws, multi):
+            assert H.bits_equal(m.cpu(), q.fake_quant_weight_dynamic(w).cpu())
+    # 20 tensors -> two launches; ineligible layout -> per-tensor path
+    ws = [(torch.randn(16, 256, device=DEV) * 0.02).to(torch.bfloat16) for _ in range(20)]
+    q = Q.IntegerQuantizer(4, False, 'per_group', group_size=128)
+    for w, m in zip(ws, q.fake_quant_weights_dynamic(ws)):
+        assert H.bits_equal(m.cpu(), q.fake_quant_weight_dynamic(w).cpu())
+    qc = Q.IntegerQuantizer(8, True, 'per_channel')
+    for w, m in zip(ws, qc.fake_quant_weights_dynamic(ws)):
+        assert H.bits_equal(m.cpu(), qc.fake_quant_weight_dynamic(w).cpu())
