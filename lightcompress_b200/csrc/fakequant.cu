@@ -1,11 +1,11 @@
 // fakequant.cu — single-pass grouped quant-dequant (subsystem 1 of the north star).
 //
 // One HBM read + one HBM write per element. Kernels:
-//   fq_group_kernel   : (fq_group.cuh) units of <= 32 lanes x 8 x 16 B; a sub-warp of 4..32 lanes owns U units per
-//                       iteration, 128-bit coalesced loads, transposing xor-shuffle min/max, one qparam computation
-//                       per unit, round + clamp + dequant in registers.
-//   fq_row_kernel     : long units (per_channel / per_token rows): one CTA per row, row cached in registers,
-//                       warp-shuffle + smem block reduce.
+//   fq_group_kernel   : (fq_group.cuh) units of <= 32 lanes x 8 x 16 B; a sub-warp of 4..32 lanes owns a unit, 8 vectors
+//                       in flight per lane, 128-bit coalesced loads, packed xor-shuffle min/max, round + clamp + dequant
+//                       on packed 16-bit pairs in registers. fq_group_multi_kernel: several tensors in one launch.
+//   fq_wrow_kernel    : rows of up to 2048 vectors (per_channel / per_token): 2 / 4 / 8 warps per row, one named barrier.
+//   fq_row_stream_kernel : longer rows, CTA per row, second pass re-reads L2-resident data.
 //   fq_block2d_kernel : per_block 128x128 tiles (fp32 math), CTA per tile, ragged edges zero-padded.
 //   fq_static_kernel  : scales / zeros given (fake_quant_*_static, per_tensor phase 2), pure elementwise.
 //   fq_generic_kernel : any unit shape / alignment / exotic spec; literal arithmetic, warp per unit.
@@ -135,54 +135,6 @@ __device__ __forceinline__ void block_minmax(float& mx, float& mn, float* smem /
   mx = a;
   mn = b;
   __syncthreads();
-}
-
-template <typename T, int NV, int KINDC>
-__global__ void __launch_bounds__(512)
-    fq_row_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
-                  void* __restrict__ zeros, int64_t n_units, int64_t unit_len, SpecD sp) {
-  constexpr int VEC = TI<T>::VEC;
-  __shared__ float red[64];
-  const int64_t nvec = unit_len / VEC;
-  for (int64_t unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-    const T* src = in + unit * unit_len;
-    uint4 raw[NV];
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int64_t v = (int64_t)j * blockDim.x + threadIdx.x;
-      if (v < nvec) raw[j] = ld_stream(src + v * VEC);
-    }
-    float mx = -INFINITY, mn = INFINITY;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int64_t v = (int64_t)j * blockDim.x + threadIdx.x;
-      if (v < nvec) {
-        float f[VEC];
-        TI<T>::unpack(raw[j], f);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-          mx = max_nan(mx, f[i]);
-          mn = min_nan(mn, f[i]);
-        }
-      }
-    }
-    block_minmax(mx, mn, red);
-    UnitQ u;
-    qparams_from_range(mn, mx, sp, u);
-    finish_unit(sp, u);
-    if (!(finite_f(mx) && finite_f(mn))) u.exact = 1;
-    if (threadIdx.x == 0) write_qparams(scales, zeros, unit, u, sp);
-    if (sp.out_mode == LCB_OUT_NONE) continue;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int64_t v = (int64_t)j * blockDim.x + threadIdx.x;
-      if (v < nvec) {
-        float f[VEC];
-        TI<T>::unpack(raw[j], f);
-        quant_store_vec<T, T, KINDC>(f, u, sp, out, unit * unit_len + v * VEC);
-      }
-    }
-  }
 }
 
 // streaming variant for rows that do not fit the register cache: second pass re-reads (L2-resident) data

@@ -1,6 +1,7 @@
 // fakequant_host.cuh — host-side dispatch of lcb_fakequant (included by fakequant.cu)
 #pragma once
 #include <math.h>
+#include <stdlib.h>
 
 namespace lcb {
 
@@ -30,14 +31,6 @@ static int grid_for(int64_t work_ctas, int ctas_per_sm) {
   int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
   return (int)(work_ctas < cap ? (work_ctas < 1 ? 1 : work_ctas) : cap);
 }
-
-#define LCB_NV_SWITCH(NVV, ...)                   \
-  switch (NVV) {                                  \
-    case 1: { constexpr int NV = 1; __VA_ARGS__; } break; \
-    case 2: { constexpr int NV = 2; __VA_ARGS__; } break; \
-    case 4: { constexpr int NV = 4; __VA_ARGS__; } break; \
-    default: { constexpr int NV = 8; __VA_ARGS__; } break; \
-  }
 
 static inline float host_rd(float x, int dt) {
   if (dt == LCB_BF16) return __bfloat162float(__float2bfloat16_rn(x));
@@ -75,12 +68,16 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
                              const SpecD& sp, cudaStream_t st) {
   constexpr int VEC = TI<T>::VEC;
   const int64_t nvec = unit_len / VEC;
-  if (nvec <= 512) {
+  static const int64_t group_max_nvec = [] {   // tuning knob (tools/fq_sweep.py): largest unit served by the sub-warp kernel
+    const char* e = getenv("LCB_GROUP_MAX_NVEC");
+    return e ? (int64_t)atoll(e) : (int64_t)256;
+  }();
+  if (nvec <= group_max_nvec) {
     // sub-warp per unit: lanes = pow2 >= nvec / 2 in [4, 32], NV vectors per lane
     int lanes = 4;
     while (lanes * 2 < nvec && lanes < 32) lanes <<= 1;
     const int nv = (int)((nvec + lanes - 1) / lanes);
-    const int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : nv <= 8 ? 8 : 16;
+    const int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
     const int u = nvt >= 8 ? 1 : 8 / nvt;
     const FastSpec fs = make_fastspec<T>(sp);
     const int64_t units_per_cta = (int64_t)8 * u * (32 / lanes);
@@ -106,17 +103,35 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
       case 1: LCB_LAUNCH_GROUP(1) break;
       case 2: LCB_LAUNCH_GROUP(2) break;
       case 4: LCB_LAUNCH_GROUP(4) break;
-      case 8: LCB_LAUNCH_GROUP(8) break;
-      default: LCB_LAUNCH_GROUP(16) break;
+      default: LCB_LAUNCH_GROUP(8) break;
     }
 #undef LCB_LAUNCH_GROUP_C
 #undef LCB_LAUNCH_GROUP
-  } else if (nvec <= 4096) {
-    int threads = nvec <= 2048 ? 256 : 512;
-    int nv = (int)((nvec + threads - 1) / threads);
-    int nvt = nv <= 1 ? 1 : nv <= 2 ? 2 : nv <= 4 ? 4 : 8;
-    int grid = grid_for(n_units, threads == 256 ? 6 : 3);
-    LCB_NV_SWITCH(nvt, { fq_row_kernel<T, NV, KINDC><<<grid, threads, 0, st>>>(in, out, scales, zeros, n_units, unit_len, sp); });
+  } else if (nvec <= 2048) {
+    // W warps per row, 8 vectors per lane (fq_wrow_kernel)
+    const int w = nvec <= 512 ? 2 : nvec <= 1024 ? 4 : 8;
+    const FastSpec fs = make_fastspec<T>(sp);
+    int chain = CHAIN_ANY_OUT;
+    if (sp.out_mode == LCB_OUT_FAKE) chain = (KINDC == 0) ? fs.chain : CHAIN_F32;
+    const int grid = grid_for((n_units + (8 / w) - 1) / (8 / w), 8);
+#define LCB_LAUNCH_WROW_C(CH, Wc) \
+  fq_wrow_kernel<T, KINDC, CH, Wc><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, sp, fs)
+#define LCB_LAUNCH_WROW(CH)                      \
+  {                                              \
+    if (w == 2) LCB_LAUNCH_WROW_C(CH, 2);        \
+    else if (w == 4) LCB_LAUNCH_WROW_C(CH, 4);   \
+    else LCB_LAUNCH_WROW_C(CH, 8);               \
+  }
+    if (chain == CHAIN_F32) LCB_LAUNCH_WROW(CHAIN_F32)
+    else if (TI<T>::ID == LCB_BF16 && KINDC == 0 && chain == CHAIN_BF16_SMALL) {
+      if constexpr (TI<T>::ID == LCB_BF16 && KINDC == 0) LCB_LAUNCH_WROW(CHAIN_BF16_SMALL)
+    } else if (TI<T>::ID == LCB_BF16 && KINDC == 0 && chain == CHAIN_BF16_WIDE) {
+      if constexpr (TI<T>::ID == LCB_BF16 && KINDC == 0) LCB_LAUNCH_WROW(CHAIN_BF16_WIDE)
+    } else if (TI<T>::ID == LCB_F16 && KINDC == 0 && chain == CHAIN_F16) {
+      if constexpr (TI<T>::ID == LCB_F16 && KINDC == 0) LCB_LAUNCH_WROW(CHAIN_F16)
+    } else LCB_LAUNCH_WROW(CHAIN_ANY_OUT)
+#undef LCB_LAUNCH_WROW
+#undef LCB_LAUNCH_WROW_C
   } else {
     int grid = grid_for(n_units, 4);
     fq_row_stream_kernel<T, KINDC><<<grid, 512, 0, st>>>(in, out, scales, zeros, n_units, unit_len, sp);

@@ -169,6 +169,65 @@ enum { CHAIN_ANY_OUT = -1 };  // template value: runtime out_mode, out-of-line g
 
 // CHAIN: element chain compiled in. CHAIN_ANY_OUT serves every out_mode through quant_store_vec_generic; the others
 // are LCB_OUT_FAKE only (the host guarantees it).
+// qparams -> (rare) literal path or the compiled-in element chain -> stores, for the NV vectors one lane holds of a unit.
+// Lane's vector j sits at vector index v0 + j * vstride of the unit and at element offset e0 + j * vstride * VEC.
+template <typename T, int NV, int KINDC, int CHAIN>
+__device__ __forceinline__ void fq_finish_unit(const uint4 (&raw)[NV], float mn, float mx, int64_t unit, int64_t e0, int v0,
+                                               int vstride, int nvec, bool writer, void* __restrict__ out,
+                                               void* __restrict__ scales, void* __restrict__ zeros, const SpecD& sp,
+                                               const FastSpec& fs) {
+  constexpr int VEC = TI<T>::VEC;
+  UnitQ u;
+  qparams_unit<T>(mn, mx, sp, fs, u);
+  if (u.exact) {  // unit-uniform, rare: literal chain, qparams recomputed literally as well
+    if (writer) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
+    if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+      for (int j = 0; j < NV; ++j)
+        if (v0 + j * vstride < nvec) quant_store_vec_literal<T>(raw[j], mn, mx, sp, out, e0 + (int64_t)j * vstride * VEC);
+    }
+    return;
+  }
+  if (writer) write_qparams(scales, zeros, unit, u, sp);
+  if (CHAIN == CHAIN_ANY_OUT) {
+    if (sp.out_mode != LCB_OUT_NONE) {
+#pragma unroll
+      for (int j = 0; j < NV; ++j)
+        if (v0 + j * vstride < nvec)
+          quant_store_vec_generic<T, KINDC>(raw[j], u, sp, out, e0 + (int64_t)j * vstride * VEC);
+    }
+    return;
+  }
+  T* o = reinterpret_cast<T*>(out) + e0;
+  UnitP p;
+  if (CHAIN == CHAIN_BF16_SMALL || CHAIN == CHAIN_BF16_WIDE) {
+    p.lo2 = pack_bf16x2(u.lo, u.lo);
+    p.hi2 = pack_bf16x2(u.hi, u.hi);
+    p.s2 = pack_bf16x2(u.s_out, u.s_out);
+  } else if (CHAIN == CHAIN_F16) {
+    p.lo2 = pack_f16x2(u.lo, u.lo);
+    p.hi2 = pack_f16x2(u.hi, u.hi);
+    p.s2 = pack_f16x2(u.s_out, u.s_out);
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const uint4 w = raw[j];
+    uint4 r4;
+    if (CHAIN == CHAIN_BF16_SMALL)
+      r4 = make_uint4(fq2_bf16_small(w.x, u.r, p), fq2_bf16_small(w.y, u.r, p), fq2_bf16_small(w.z, u.r, p),
+                      fq2_bf16_small(w.w, u.r, p));
+    else if (CHAIN == CHAIN_BF16_WIDE)
+      r4 = make_uint4(fq2_bf16_wide(w.x, u.r, p, u.s_out), fq2_bf16_wide(w.y, u.r, p, u.s_out),
+                      fq2_bf16_wide(w.z, u.r, p, u.s_out), fq2_bf16_wide(w.w, u.r, p, u.s_out));
+    else if (CHAIN == CHAIN_F16)
+      r4 = make_uint4(fq2_f16(w.x, u.s, u.r, p), fq2_f16(w.y, u.s, u.r, p), fq2_f16(w.z, u.s, u.r, p),
+                      fq2_f16(w.w, u.s, u.r, p));
+    else
+      r4 = quant_vec_fast_f32<T, KINDC>(w, u, sp.kind);
+    if (v0 + j * vstride < nvec) st_stream(o + (int64_t)j * vstride * VEC, r4);
+  }
+}
+
 // One warp-iteration: the warp's chunk of U * (32 / lanes) consecutive units of the tensor (in, out, n_units).
 template <typename T, int NV, int KINDC, int CHAIN>
 __device__ __forceinline__ void fq_group_chunk(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
@@ -206,58 +265,9 @@ __device__ __forceinline__ void fq_group_chunk(const T* __restrict__ in, void* _
     }
     for (int o = lanes >> 1; o > 0; o >>= 1) rg = R::join(rg, R::shfl_xor(rg, o));
     const float mx = R::mx(rg), mn = R::mn(rg);
-    UnitQ u;
-    qparams_unit<T>(mn, mx, sp, fs, u);
     if (unit >= n_units) continue;  // sub-warp uniform; no shuffles below
-    const int64_t e0 = unit * unit_len + (int64_t)lane_in * VEC;
-    if (u.exact) {  // sub-warp uniform, rare: literal chain, qparams recomputed literally as well
-      if (lane_in == 0) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
-      if (sp.out_mode != LCB_OUT_NONE) {
-#pragma unroll
-        for (int j = 0; j < NV; ++j)
-          if (j * lanes + lane_in < nvec)
-            quant_store_vec_literal<T>(raw[k][j], mn, mx, sp, out, e0 + (int64_t)j * lanes * VEC);
-      }
-      continue;
-    }
-    if (lane_in == 0) write_qparams(scales, zeros, unit, u, sp);
-    if (CHAIN == CHAIN_ANY_OUT) {
-      if (sp.out_mode != LCB_OUT_NONE) {
-#pragma unroll
-        for (int j = 0; j < NV; ++j)
-          if (j * lanes + lane_in < nvec)
-            quant_store_vec_generic<T, KINDC>(raw[k][j], u, sp, out, e0 + (int64_t)j * lanes * VEC);
-      }
-      continue;
-    }
-    T* o = reinterpret_cast<T*>(out) + e0;
-    UnitP p;
-    if (CHAIN == CHAIN_BF16_SMALL || CHAIN == CHAIN_BF16_WIDE) {
-      p.lo2 = pack_bf16x2(u.lo, u.lo);
-      p.hi2 = pack_bf16x2(u.hi, u.hi);
-      p.s2 = pack_bf16x2(u.s_out, u.s_out);
-    } else if (CHAIN == CHAIN_F16) {
-      p.lo2 = pack_f16x2(u.lo, u.lo);
-      p.hi2 = pack_f16x2(u.hi, u.hi);
-      p.s2 = pack_f16x2(u.s_out, u.s_out);
-    }
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const uint4 w = raw[k][j];
-      uint4 r4;
-      if (CHAIN == CHAIN_BF16_SMALL)
-        r4 = make_uint4(fq2_bf16_small(w.x, u.r, p), fq2_bf16_small(w.y, u.r, p), fq2_bf16_small(w.z, u.r, p),
-                        fq2_bf16_small(w.w, u.r, p));
-      else if (CHAIN == CHAIN_BF16_WIDE)
-        r4 = make_uint4(fq2_bf16_wide(w.x, u.r, p, u.s_out), fq2_bf16_wide(w.y, u.r, p, u.s_out),
-                        fq2_bf16_wide(w.z, u.r, p, u.s_out), fq2_bf16_wide(w.w, u.r, p, u.s_out));
-      else if (CHAIN == CHAIN_F16)
-        r4 = make_uint4(fq2_f16(w.x, u.s, u.r, p), fq2_f16(w.y, u.s, u.r, p), fq2_f16(w.z, u.s, u.r, p),
-                        fq2_f16(w.w, u.s, u.r, p));
-      else
-        r4 = quant_vec_fast_f32<T, KINDC>(w, u, sp.kind);
-      if (j * lanes + lane_in < nvec) st_stream(o + (int64_t)j * lanes * VEC, r4);
-    }
+    fq_finish_unit<T, NV, KINDC, CHAIN>(raw[k], mn, mx, unit, unit * unit_len + (int64_t)lane_in * VEC, lane_in, lanes, nvec,
+                                        lane_in == 0, out, scales, zeros, sp, fs);
   }
 }
 
@@ -296,6 +306,50 @@ __global__ void __launch_bounds__(256)
     while (c >= md.chunk_start[t + 1]) ++t;  // warp-uniform, monotone in c
     fq_group_chunk<T, NV, KINDC, CHAIN>(reinterpret_cast<const T*>(md.in[t]), md.out[t], nullptr, nullptr, md.n_units[t],
                                         unit_len, lanes, c - md.chunk_start[t], sp, fs);
+  }
+}
+
+// Rows longer than one warp's registers (2048 < elements <= 16384 for 16-bit types): W warps share a row, NV = 8 vectors
+// per lane, cross-warp range through shared memory and ONE named barrier per row (slots double-buffered by iteration).
+// CTA = 8 warps = 8 / W rows at a time. Same element chains as the sub-warp kernel.
+template <typename T, int KINDC, int CHAIN, int W>
+__global__ void __launch_bounds__(256)
+    fq_wrow_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, void* __restrict__ zeros,
+                   int64_t n_units, int unit_len, SpecD sp, FastSpec fs) {
+  constexpr int VEC = TI<T>::VEC;
+  constexpr int NV = 8;
+  constexpr int RPC = 8 / W;  // rows per CTA per iteration
+  using R = Range<T>;
+  __shared__ typename R::P slot[2][RPC][W];
+  const int nvec = unit_len / VEC;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rsub = warp / W, wsub = warp % W;
+  const int v0 = wsub * 32 + lane;
+  const int64_t n_iter = (n_units + (int64_t)gridDim.x * RPC - 1) / ((int64_t)gridDim.x * RPC);
+  for (int64_t it = 0; it < n_iter; ++it) {
+    const int64_t unit = (it * gridDim.x + blockIdx.x) * RPC + rsub;
+    const bool valid = unit < n_units;
+    uint4 raw[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int v = v0 + j * W * 32;
+      raw[j] = (valid && v < nvec) ? ld_stream(in + unit * unit_len + (int64_t)v * VEC) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    typename R::P rg = R::init();
+#pragma unroll
+    for (int j = 0; j < NV; ++j)
+      if (v0 + j * W * 32 < nvec) rg = R::join(rg, R::from_vec(raw[j]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rg = R::join(rg, R::shfl_xor(rg, o));
+    const int par = (int)(it & 1);
+    if (lane == 0) slot[par][rsub][wsub] = rg;
+    asm volatile("bar.sync %0, %1;" ::"r"(rsub + 1), "r"(W * 32) : "memory");
+    rg = slot[par][rsub][0];
+#pragma unroll
+    for (int w = 1; w < W; ++w) rg = R::join(rg, slot[par][rsub][w]);
+    if (!valid) continue;  // row-group uniform
+    fq_finish_unit<T, NV, KINDC, CHAIN>(raw, R::mn(rg), R::mx(rg), unit, unit * unit_len + (int64_t)v0 * VEC, v0, W * 32, nvec,
+                                        wsub == 0 && lane == 0, out, scales, zeros, sp, fs);
   }
 }
 
