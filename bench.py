@@ -180,6 +180,9 @@ def main():
     if args.impl == 'reference':
         return run_reference(args)
 
+    if os.environ.get('LCB_BENCH_TRACE'):   # debugging aid: dump every thread's stack if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ['LCB_BENCH_TRACE']), exit=True, file=sys.stderr)
     import torch
     import torch.distributed as dist
     from lightcompress_b200 import _cabi

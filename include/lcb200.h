@@ -156,6 +156,24 @@ int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out, float* Lo
 int64_t lcb_gptq_workspace_bytes(int64_t R, int64_t C, int32_t blocksize);
 
 /*
+ * In place: H <- U, the UPPER Cholesky factor of inverse(H + percdamp * mean(diag H) * I), i.e. U^T U = (H + damp I)^-1.
+ * Replaces the damping and the three factorisations of GPTQ.process_hessian_and_weights (gptq.py:165-174:
+ * torch.linalg.cholesky -> torch.cholesky_inverse -> torch.linalg.cholesky(upper=True)) by one blocked reverse
+ * Cholesky H = R R^T (R upper) and one blocked triangular inverse U = R^-1, whose O(n^3) parts run as tcgen05 GEMMs
+ * over bf16 pieces of the fp32 operands (splits = 2: hi + lo, 3 products; splits = 3: hi + mid + lo, 6 products);
+ * diagonal blocks, substitutions and accumulators are fp32.
+ * H: fp32 [n, n] symmetric positive definite, leading dimension ld; only its upper triangle is read; on return the
+ * strict lower triangle is zero. n % 128 == 0 requires ld == n and a 16-byte aligned H (factorised in place);
+ * any other n / ld goes through a padded copy inside the workspace.
+ * info: device int32, 0 on success, else 1 + index of the first non-positive pivot (the reference raises
+ * torch.linalg.LinAlgError there; the host wrapper does the same after reading info).
+ * workspace: lcb_cholinv_workspace_bytes(n, splits) bytes.
+ */
+int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp, int32_t splits, void* workspace, int32_t* info,
+                      void* stream);
+int64_t lcb_cholinv_workspace_bytes(int64_t n, int32_t splits);
+
+/*
  * out[r, c] = in[r, c] * scales[c] (op 0) or in[r, c] / scales[c] (op 1, IEEE division), computed in fp32 and rounded
  * to `dtype` — the tensor-dtype arithmetic of Awq.scaling_weight (awq.py:41-47: W.mul_(scales)) and
  * scaling_input (base_bq.py:877-889: x / scales). in / out / scales share `dtype`; out may alias in.

@@ -50,7 +50,14 @@ int launch_variant(const tcg::Maps& maps, const tcg::Params& p, int grid, cudaSt
 
 int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* const* a, const void* const* b, int n_seg,
                    float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldd, cudaStream_t st) {
+  return tc_gemm_launch_ex(a_kmajor, false, syrk, neg, false, fmt, a, b, n_seg, D, M, N, K, lda, ldb, ldd, st);
+}
+
+int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tri_b, int fmt, const void* const* a,
+                      const void* const* b, int n_seg, float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                      int64_t ldd, cudaStream_t st) {
   using namespace tcg;
+  if (tri_b && b_kmajor) return LCB_E_INVALID;
   if (M <= 0 || N <= 0 || K <= 0) return LCB_OK;
   if (n_seg < 1 || n_seg > MAX_SEG) return LCB_E_INVALID;
   if (syrk && M != N) return LCB_E_INVALID;
@@ -80,7 +87,8 @@ int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* cons
   p.kb_per_split = (kb_total + nsplit - 1) / nsplit;
   p.nsplit = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.n_seg = n_seg;
-  p.idesc = tc::idesc_f16(fmt, BM, BN, a_kmajor ? 0 : 1, 1);
+  p.tri_b = tri_b ? 1 : 0;
+  p.idesc = tc::idesc_f16(fmt, BM, BN, a_kmajor ? 0 : 1, b_kmajor ? 0 : 1);
   p.org = nullptr;
   p.ld_org = 0;
   p.org_fmt = fmt;
@@ -88,13 +96,19 @@ int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* cons
 
   const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   bool ok = true;
-  for (int s = 0; s < MAX_SEG; ++s) {
-    const int u = s < n_seg ? s : 0;
+  for (int s = 0; s < n_seg; ++s) {
     if (a_kmajor)
-      ok = ok && make_tmap_2d(&maps.a[s], a[u], dt16, 2, M, K, lda * 2, BM, BK);   // [M, K]: box 128 rows x 64 k
+      ok = ok && make_tmap_2d(&maps.a[s], a[s], dt16, 2, M, K, lda * 2, BM, BK);   // [M, K]: box 128 rows x 64 k
     else
-      ok = ok && make_tmap_2d(&maps.a[s], a[u], dt16, 2, K, M, lda * 2, BK, 64);   // [K, M]: box 64 k-rows x 64 m
-    ok = ok && make_tmap_2d(&maps.b[s], b[u], dt16, 2, K, N, ldb * 2, BK, 64);     // [K, N]: box 64 k-rows x 64 n
+      ok = ok && make_tmap_2d(&maps.a[s], a[s], dt16, 2, K, M, lda * 2, BK, 64);   // [K, M]: box 64 k-rows x 64 m
+    if (b_kmajor)
+      ok = ok && make_tmap_2d(&maps.b[s], b[s], dt16, 2, N, K, ldb * 2, BN, BK);   // [N, K]: box 256 n-rows x 64 k
+    else
+      ok = ok && make_tmap_2d(&maps.b[s], b[s], dt16, 2, K, N, ldb * 2, BK, 64);   // [K, N]: box 64 k-rows x 64 n
+  }
+  for (int s = n_seg; s < MAX_SEG; ++s) {
+    maps.a[s] = maps.a[0];
+    maps.b[s] = maps.b[0];
   }
   ok = ok && make_tmap_2d(&maps.d, D, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, M, N, ldd * 4, 32, 32);
   if (!ok) {
@@ -103,6 +117,10 @@ int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* cons
   }
   const int n_items = p.n_tiles * p.nsplit;
   const int grid = n_items < kNumSMs ? n_items : kNumSMs;
+  if (b_kmajor) {
+    if (a_kmajor && syrk && neg) return launch_variant<true, true, true, true, EPI_REDUCE_ADD>(maps, p, grid, st);
+    return LCB_E_UNSUPPORTED;
+  }
   if (!a_kmajor && syrk && !neg) return launch_variant<false, false, true, false, EPI_REDUCE_ADD>(maps, p, grid, st);
   if (a_kmajor && !syrk && neg) return launch_variant<true, false, false, true, EPI_REDUCE_ADD>(maps, p, grid, st);
   if (a_kmajor && !syrk && !neg) return launch_variant<true, false, false, false, EPI_REDUCE_ADD>(maps, p, grid, st);
@@ -129,6 +147,7 @@ int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org,
   p.nsplit = 1;  // the output is rounded before it is compared: no split-K
   p.kb_per_split = (int)((K + BK - 1) / BK);
   p.n_seg = 1;
+  p.tri_b = 0;
   p.idesc = tc::idesc_f16(fmt, BM, BN, 0, 0);
   p.org = org;
   p.ld_org = ldo;

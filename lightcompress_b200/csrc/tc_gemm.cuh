@@ -27,7 +27,7 @@ constexpr int SMEM_MAIN = STAGES * STAGE_BYTES;     // 196608
 constexpr int SMEM_EPI = 4 * 2 * EPI_BUF;           // 32768
 constexpr int SMEM_BYTES = SMEM_MAIN + SMEM_EPI + 256 + 1024;  // + barriers + alignment slack
 constexpr int NTHREADS = 192;
-constexpr int MAX_SEG = 3;
+constexpr int MAX_SEG = 6;
 
 enum { EPI_REDUCE_ADD = 0, EPI_MSE = 1 };
 
@@ -39,6 +39,7 @@ struct Params {
   int nsplit;        // K splits per tile
   int kb_per_split;  // 64-deep K blocks per split (per segment)
   int n_seg;
+  int tri_b;         // B[k, n] == 0 for k > n (upper-triangular B): column block tj only needs k < (tj + 1) * BN
   uint32_t idesc;
   // EPI_MSE: loss[0] += sum over the tile of rd16(rd16(org) - rd16(acc))^2   (awq.py:134-145 on 16-bit tensors)
   const void* org;   // [M, N] row-major 16-bit, leading dimension ld_org
@@ -70,6 +71,10 @@ __device__ __forceinline__ void tile_of(int t, int nblk_j, int& ti, int& tj) {
   }
   ti = i;
   tj = (i >> 1) + t;
+}
+
+__device__ __forceinline__ int k_hi(const Params& p, int tj, int kb_total) {
+  return p.tri_b ? min(kb_total, ((tj + 1) * BN + BK - 1) / BK) : kb_total;
 }
 
 template <int FMT>
@@ -155,7 +160,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
         tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
         const int split = item % p.nsplit;
         const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+        const int kb1 = min(k_hi(p, tj, kb_total), kb0 + p.kb_per_split);
         for (int seg = 0; seg < p.n_seg; ++seg) {
           for (int kb = kb0; kb < kb1; ++kb) {
             tc::mbar_wait(&empty[stage], phase ^ 1);
@@ -195,10 +200,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
     const uint64_t desc_mn = tc::smem_desc_sw128(BOX_BYTES, 1024);
     const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      int ti, tj;
+      tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
       const int split = item % p.nsplit;
       const int kb0 = split * p.kb_per_split;
-      const int kb1 = min(kb_total, kb0 + p.kb_per_split);
+      const int kb1 = min(k_hi(p, tj, kb_total), kb0 + p.kb_per_split);
       const int n_kb = (kb1 - kb0) * p.n_seg;
+      if (n_kb <= 0) continue;   // tri_b: this K split lies entirely below the triangle (all roles skip it alike)
       tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
       tc::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
@@ -238,6 +246,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
       int ti, tj;
       tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
+      if (min(k_hi(p, tj, kb_total), (item % p.nsplit) * p.kb_per_split + p.kb_per_split) <= (item % p.nsplit) * p.kb_per_split)
+        continue;
       tc::mbar_wait(&tfull[acc], acc_phase);
       tc::tc_fence_after();
       const int row0 = ti * BM + q * 32;
@@ -312,6 +322,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
 //   fmt: 0 = fp16, 1 = bf16. syrk requires M == N. neg: D -= instead of D +=.
 int tc_gemm_launch(bool a_kmajor, bool syrk, bool neg, int fmt, const void* const* a, const void* const* b, int n_seg,
                    float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb, int64_t ldd, cudaStream_t st);
+// Same with: b_kmajor (B_seg given as [N, K] row-major), tri_b (B is upper triangular, B[k, n] = 0 for k > n: the K loop
+// of a column block stops at its last column; requires !b_kmajor).
+int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tri_b, int fmt, const void* const* a,
+                      const void* const* b, int n_seg, float* D, int64_t M, int64_t N, int64_t K, int64_t lda, int64_t ldb,
+                      int64_t ldd, cudaStream_t st);
 
 // loss[0] += sum_{t, r} rd16(org[t, r] - rd16(sum_k x[t, k] * w[r, k]))^2 — F.linear + the squared-error part of
 // Awq.calculate_loss (awq.py:134-145) without writing the output. x [M, K], w [N, K], org [M, N], all 16-bit row-major.

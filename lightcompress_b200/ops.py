@@ -48,6 +48,30 @@ def hessian_finalize(S, nsamples):
     return S
 
 
+def cholinv_upper(H, percdamp=0.0, splits=3, check=True):
+    """In place: H <- upper Cholesky factor of inverse(H + percdamp * mean(diag H) * I) — the damping plus
+    `cholesky -> cholesky_inverse -> cholesky(upper=True)` of GPTQ.process_hessian_and_weights (gptq.py:165-174) as one
+    blocked reverse Cholesky + triangular inverse on tcgen05 (lcb_cholinv_upper). H: fp32 [n, n] contiguous, SPD.
+    Raises torch.linalg.LinAlgError like the reference when a pivot is not positive (check=True costs one host sync)."""
+    _need_cuda(H)
+    assert H.dtype == torch.float32 and H.dim() == 2 and H.shape[0] == H.shape[1] and H.is_contiguous()
+    n = H.shape[0]
+    lib = _cabi.load()
+    ws = torch.empty(int(lib.lcb_cholinv_workspace_bytes(n, int(splits))), dtype=torch.uint8, device=H.device)
+    info = torch.zeros(1, dtype=torch.int32, device=H.device)
+    with _on_device(H.device):
+        st = lib.lcb_cholinv_upper(H.data_ptr(), n, n, float(percdamp), int(splits), ws.data_ptr(), info.data_ptr(),
+                                   _stream(H.device.index))
+    _cabi.check(st, 'lcb_cholinv_upper')
+    if check:
+        bad = int(info.item())
+        if bad:
+            raise torch.linalg.LinAlgError(
+                f'linalg.cholesky: The factorization could not be completed because the input is not positive-definite '
+                f'(the leading minor of order {bad} is not positive-definite).')
+    return H
+
+
 def col_absstat(x, out, mean=False):
     """out[c] = max(out[c], max_r |x[r, c]|) (or += sum_r |x[r, c]| when mean). x: [..., C]; out: fp32 [C]."""
     _need_cuda(x, out)
