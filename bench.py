@@ -127,12 +127,11 @@ def extras(torch, dev, tf_peak):
     res['hessian'] = {'C': C, 'T': T, 'ms': t * 1e3, 'gemm_equiv_TFLOPs': 2.0 * T * C * C / t / 1e12,
                       'hw_syrk_TFLOPs': 2.0 * T * C * C / t / 1e12 * 33 / 64, 'frac_of_bf16_peak_hw': 2.0 * T * C * C / t / 1e12 * 33 / 64 / tf_peak}
     ops.hessian_finalize(S, 20)
-    d = torch.arange(C, device=dev)
-    S[d, d] += 0.01 * torch.mean(torch.diag(S))
-    t0 = time.perf_counter()
-    Hinv = torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(S)), upper=True).contiguous()
-    torch.cuda.synchronize()
-    res['cholesky_chain_ms_C4096'] = (time.perf_counter() - t0) * 1e3
+    Hw = S.clone()
+    ops.cholinv_upper(Hw, 0.01, check=False)
+    t = ev(lambda: ops.cholinv_upper(Hw.copy_(S), 0.01, check=False), 3)
+    res['cholinv_ms_C4096'] = t * 1e3      # damping + cholesky -> cholesky_inverse -> cholesky(upper) of gptq.py:165-174
+    Hinv = Hw
     W = torch.randn(C, C, device=dev, generator=g) * 0.02
     t = ev(lambda: ops.gptq_weight_transform(W.clone(), Hinv, 128, 128, 0.0, 15.0, False), 2)
     res['gptq_update_q_proj_ms'] = t * 1e3

@@ -29,6 +29,7 @@ class GPTQLayer(object):
         self.scales = self.zeros = None
         self.losses = None
         self.perm = self.invperm = None
+        self.chol_splits = 3   # bf16 pieces per fp32 operand in the factorisation GEMMs (3 = fp32-class accuracy)
 
     @torch.no_grad()
     def add_batch(self, inp):
@@ -53,7 +54,9 @@ class GPTQLayer(object):
     @torch.no_grad()
     def process_hessian_and_weights(self):
         """gptq.py:128-176: dead columns, optional act-order permutation, damping, Cholesky inverse upper factor.
-        The three factorisations stay on torch.linalg (cuSOLVER): SURVEY.md §8f N1."""
+        Damping and the three factorisations (gptq.py:165-174) are one call of ops.cholinv_upper (blocked reverse
+        Cholesky + triangular inverse on tcgen05); it raises torch.linalg.LinAlgError like
+        torch.linalg.cholesky when the damped Hessian is not positive definite."""
         if self.H is None:
             self.finalize()
         H = self.H
@@ -66,14 +69,9 @@ class GPTQLayer(object):
             W = W[:, self.perm].contiguous()
             H = H[self.perm][:, self.perm]
             self.invperm = torch.argsort(self.perm)
-        damp = self.percdamp * torch.mean(torch.diag(H))
-        diag = torch.arange(self.columns, device=H.device)
-        H[diag, diag] += damp
-        H = torch.linalg.cholesky(H)
-        H = torch.cholesky_inverse(H)
-        H = torch.linalg.cholesky(H, upper=True)
+        H = ops.cholinv_upper(H.contiguous(), self.percdamp, splits=self.chol_splits)
         self.H = None
-        return W, H.contiguous()
+        return W, H
 
     @torch.no_grad()
     def quantize(self, static_scales=None, static_zeros=None):

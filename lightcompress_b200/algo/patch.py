@@ -28,13 +28,49 @@ def _gptq_add_batch(orig):
     return add_batch
 
 
+class _FusedCholeskyChain(object):
+    """While active, the reference's `H = torch.linalg.cholesky(H); H = torch.cholesky_inverse(H);
+    H = torch.linalg.cholesky(H, upper=True)` (gptq.py:172-174) runs as ONE ops.cholinv_upper call: the first call
+    computes the final factor and hands back a token, the other two pass it through. Anything that is not that exact
+    chain on an fp32 CUDA matrix falls through to torch."""
+
+    def __enter__(self):
+        self._chol, self._cinv = torch.linalg.cholesky, torch.cholesky_inverse
+        st = {}
+
+        def cholesky(A, *a, upper=False, **k):
+            if upper and st.get('tok') is A:
+                st.clear()
+                return A
+            if (not upper and not a and not k and A.is_cuda and A.dtype == torch.float32 and A.dim() == 2
+                    and A.shape[0] == A.shape[1]):
+                st['tok'] = ops.cholinv_upper(A.contiguous().clone(), 0.0)
+                st['stage'] = 1
+                return st['tok']
+            return self._chol(A, *a, upper=upper, **k)
+
+        def cholesky_inverse(L, *a, **k):
+            if st.get('tok') is L and st.get('stage') == 1:
+                st['stage'] = 2
+                return L
+            return self._cinv(L, *a, **k)
+
+        torch.linalg.cholesky, torch.cholesky_inverse = cholesky, cholesky_inverse
+        return self
+
+    def __exit__(self, *exc):
+        torch.linalg.cholesky, torch.cholesky_inverse = self._chol, self._cinv
+        return False
+
+
 def _gptq_process(orig):
     def process_hessian_and_weights(self, layer, name):
         cache = self.layers_cache[name]
         if cache.pop('lcb_unnormalised', False):
             n = lcdist.allreduce_hessian(cache['H'], cache['nsamples'])   # one collective per linear (gptq.py:292-295)
             ops.hessian_finalize(cache['H'], n)
-        return orig(self, layer, name)
+        with _FusedCholeskyChain():
+            return orig(self, layer, name)
     return process_hessian_and_weights
 
 

@@ -84,36 +84,101 @@ __global__ void __launch_bounds__(256) chol_zero_lower_kernel(float* __restrict_
 }
 
 // ---- reverse Cholesky of one 128 x 128 diagonal block: A = R R^T, R upper -------------------------------------------
-// One CTA of 512 threads, A's upper triangle in shared memory. Step j = 127 .. 0: R[j][j] = sqrt(A[j][j]),
-// R[i][j] = A[i][j] / R[j][j] (i < j), then the leading j x j block loses the rank-1 term R[:, j] R[:, j]^T.
+// One CTA of 512 threads, the block in shared memory, four 32-column panels from the last to the first:
+//   (a) warp 0 factors the 32 x 32 diagonal sub-block in registers (lane i = row i; step j = 31 .. 0 broadcasts the
+//       pivot and the column by shuffles): R[j][j] = sqrt(a[j][j]), R[i][j] = a[i][j] / R[j][j], a[i][i'] -= R[i][j] R[i'][j];
+//   (b) one thread per row above it solves x Rpp^T = a[row, panel] by back substitution (32 registers, Rpp broadcast);
+//   (c) all threads retire the rank-32 term from the leading block, 4 x 4 register tiles over interleaved rows.
+constexpr int PW = 32, XLD = PW + 1;
 __global__ void __launch_bounds__(512) chol_diag_kernel(float* __restrict__ H, Splits sp, int64_t ld, int kb,
                                                         int* __restrict__ info) {
   extern __shared__ float smf[];
-  float* A = smf;                  // [NB][LDS_]
-  float* col = smf + NB * LDS_;    // [NB]
+  float* A = smf;                        // [NB][LDS_]
+  float* X = smf + NB * LDS_;            // [NB - PW][XLD]  solved panel rows
+  float* Rp = X + (NB - PW) * XLD;       // [PW][XLD]       diagonal sub-block factor
   float* base = H + (int64_t)kb * NB * ld + (int64_t)kb * NB;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int idx = tid; idx < NB * NB; idx += 512) {
     const int r = idx >> 7, c = idx & 127;
     A[r * LDS_ + c] = base[(int64_t)r * ld + c];
   }
   __syncthreads();
-  const int tx = tid & 31, ty = tid >> 5;  // 16 x 32
-  for (int j = NB - 1; j >= 0; --j) {
-    const float ajj = A[j * LDS_ + j];
-    const float rjj = sqrtf(ajj);
-    if (tid == 0 && !(ajj > 0.f)) atomicCAS(info, 0, kb * NB + j + 1);
-    if (tid < j) {
-      const float c = __fdiv_rn(A[tid * LDS_ + j], rjj);
-      col[tid] = c;
-      A[tid * LDS_ + j] = c;
+#pragma unroll 1
+  for (int p = NB / PW - 1; p >= 0; --p) {
+    const int c0 = p * PW;
+    if (warp == 0) {
+      float d[PW];
+#pragma unroll
+      for (int j = 0; j < PW; ++j) d[j] = A[(c0 + lane) * LDS_ + c0 + j];
+#pragma unroll
+      for (int j = PW - 1; j >= 0; --j) {
+        const float ajj = __shfl_sync(0xffffffffu, d[j], j);
+        if (lane == 0 && !(ajj > 0.f)) atomicCAS(info, 0, kb * NB + c0 + j + 1);
+        // 1 / sqrt(a) by MUFU.RSQ + one Newton step (<= 1 ulp), so the serial chain has no IEEE sqrt / division
+        float y = rsqrtf(ajj);
+        y = __fmaf_rn(y, __fmaf_rn(-0.5f * ajj * y, y, 0.5f), y);
+        const float rjj = __fmaf_rn(__fmaf_rn(-ajj * y, ajj * y, ajj), 0.5f * y, ajj * y);   // sqrt(a) = a y, refined
+        const float c = lane < j ? d[j] * y : 0.f;
+        d[j] = lane == j ? rjj : c;
+        // entries below the diagonal (ip < lane) receive junk updates; they are never read
+#pragma unroll
+        for (int ip = 0; ip < j; ++ip) d[ip] = __fmaf_rn(-c, __shfl_sync(0xffffffffu, c, ip), d[ip]);
+      }
+#pragma unroll
+      for (int j = 0; j < PW; ++j) {
+        const float v = j >= lane ? d[j] : 0.f;
+        A[(c0 + lane) * LDS_ + c0 + j] = v;
+        Rp[lane * XLD + j] = v;
+      }
     }
     __syncthreads();
-    if (tid == 0) A[j * LDS_ + j] = rjj;
-    for (int i = ty; i < j; i += 16) {
-      const float ci = col[i];
-      for (int ip = (i & ~31) + tx; ip < j; ip += 32)
-        if (ip >= i) A[i * LDS_ + ip] = __fmaf_rn(-ci, col[ip], A[i * LDS_ + ip]);
+    if (p == 0) break;
+    if (tid < c0) {
+      float h[PW];
+#pragma unroll
+      for (int j = 0; j < PW; ++j) h[j] = A[tid * LDS_ + c0 + j];
+#pragma unroll
+      for (int j = PW - 1; j >= 0; --j) {
+        const float x = __fdiv_rn(h[j], Rp[j * XLD + j]);
+        h[j] = x;
+#pragma unroll
+        for (int i = 0; i < j; ++i) h[i] = __fmaf_rn(-x, Rp[i * XLD + j], h[i]);
+      }
+#pragma unroll
+      for (int j = 0; j < PW; ++j) {
+        A[tid * LDS_ + c0 + j] = h[j];
+        X[tid * XLD + j] = h[j];
+      }
+    }
+    __syncthreads();
+    const int q = c0 / 4;  // rows of one interleave class
+    for (int t = tid; t < q * q; t += 512) {
+      const int ti = t / q, tj = t % q;
+      float acc[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 8
+      for (int k = 0; k < PW; ++k) {
+        float xi[4], xj[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          xi[a] = X[(ti + a * q) * XLD + k];
+          xj[a] = X[(tj + a * q) * XLD + k];
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = __fmaf_rn(xi[a], xj[b], acc[a][b]);
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int i = ti + a * q, ip = tj + b * q;
+          if (ip >= i) A[i * LDS_ + ip] -= acc[a][b];
+        }
     }
     __syncthreads();
   }
@@ -139,6 +204,8 @@ __global__ void __launch_bounds__(256) chol_trsm_kernel(float* __restrict__ H, S
     const int i = idx >> 7, j = idx & 127;
     RT[j * LDS_ + i] = diag[(int64_t)i * ld + j];
   }
+  float* rinv = smf + NB * LDS_;  // [NB] 1 / R[j][j]: the chain multiplies instead of dividing
+  if (threadIdx.x < NB) rinv[threadIdx.x] = __fdiv_rn(1.f, diag[(int64_t)threadIdx.x * ld + threadIdx.x]);
   __syncthreads();
   const int lane = threadIdx.x & 31, l = lane & (TR_LPR - 1);
   const int64_t row = (int64_t)blockIdx.x * 32 + (threadIdx.x / TR_LPR);
@@ -151,11 +218,11 @@ __global__ void __launch_bounds__(256) chol_trsm_kernel(float* __restrict__ H, S
   }
 #pragma unroll
   for (int k = TR_NK - 1; k >= 0; --k) {
-#pragma unroll 1
+#pragma unroll 4
     for (int l0 = TR_LPR - 1; l0 >= 0; --l0) {
       const int j = k * TR_LPR + l0;
       const float hj = __shfl_sync(0xffffffffu, reg[k], (lane & ~(TR_LPR - 1)) | l0);
-      const float x = __fdiv_rn(hj, RT[j * LDS_ + j]);
+      const float x = __fmul_rn(hj, rinv[j]);
       if (l == l0) xv[k] = x;
       const float* rt = RT + j * LDS_ + l;
 #pragma unroll
@@ -203,17 +270,21 @@ __global__ void __launch_bounds__(128) tri_inv_diag_kernel(const float* __restri
 }
 
 // ---- U[i, cols] = -U_ii T[:, cols]; T is zeroed after it has been read; the last CTA writes U[i, i] = U_ii ----------
-__global__ void __launch_bounds__(128) tri_row_kernel(float* __restrict__ H, Splits sp, float* __restrict__ T,
-                                                      const float* __restrict__ Dinv, int64_t ld, int64_t n, int ib) {
+// CTA = 32 columns x 256 threads: lane = column, warp w = rows 16 w .. 16 w + 15. The T tile goes through shared memory
+// (coalesced), every thread keeps its column of T in registers and reads U_ii rows as broadcast float4.
+constexpr int RW_COLS = 32, RW_THREADS = 256, RW_ROWS = NB / (RW_THREADS / 32);
+__global__ void __launch_bounds__(RW_THREADS) tri_row_kernel(float* __restrict__ H, Splits sp, float* __restrict__ T,
+                                                             const float* __restrict__ Dinv, int64_t ld, int64_t n, int ib) {
   extern __shared__ float smf[];
-  float* Uii = smf;  // [NB][NB]
+  float* Uii = smf;             // [NB][NB]
+  float* Ts = smf + NB * NB;    // [NB][RW_COLS]
   const float* d = Dinv + (int64_t)ib * NB * NB;
-  for (int idx = threadIdx.x; idx < NB * NB / 4; idx += 128)
+  for (int idx = threadIdx.x; idx < NB * NB / 4; idx += RW_THREADS)
     reinterpret_cast<float4*>(Uii)[idx] = reinterpret_cast<const float4*>(d)[idx];
-  __syncthreads();
   const int64_t row0 = (int64_t)ib * NB;
   if (blockIdx.x == gridDim.x - 1) {   // the diagonal block itself
-    for (int idx = threadIdx.x; idx < NB * NB; idx += 128) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < NB * NB; idx += RW_THREADS) {
       const int r = idx >> 7, c = idx & 127;
       const int64_t g = (row0 + r) * ld + row0 + c;
       H[g] = Uii[idx];
@@ -221,21 +292,25 @@ __global__ void __launch_bounds__(128) tri_row_kernel(float* __restrict__ H, Spl
     }
     return;
   }
-  const int64_t col = row0 + NB + (int64_t)blockIdx.x * NB + threadIdx.x;
-  if (col >= n) return;
+  const int64_t col0 = row0 + NB + (int64_t)blockIdx.x * RW_COLS;
+  for (int idx = threadIdx.x; idx < NB * RW_COLS; idx += RW_THREADS) {
+    const int k = idx >> 5, c = idx & 31;
+    Ts[idx] = T[(int64_t)k * ld + col0 + c];
+    T[(int64_t)k * ld + col0 + c] = 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float t[NB];
 #pragma unroll
-  for (int k = 0; k < NB; ++k) {
-    t[k] = T[(int64_t)k * ld + col];
-    T[(int64_t)k * ld + col] = 0.f;
-  }
+  for (int k = 0; k < NB; ++k) t[k] = Ts[k * RW_COLS + lane];
 #pragma unroll 1
-  for (int r = 0; r < NB; ++r) {
+  for (int rr = 0; rr < RW_ROWS; ++rr) {
+    const int r = warp * RW_ROWS + rr;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     const float4* ur = reinterpret_cast<const float4*>(Uii + r * NB);
 #pragma unroll
     for (int kc = 0; kc < NB / 16; ++kc) {
-      if (kc * 16 + 15 >= r) {  // uniform: U_ii[r][k] = 0 for k < r
+      if (kc * 16 + 15 >= r) {  // warp-uniform: U_ii[r][k] = 0 for k < r
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const float4 u = ur[kc * 4 + q];
@@ -247,7 +322,7 @@ __global__ void __launch_bounds__(128) tri_row_kernel(float* __restrict__ H, Spl
       }
     }
     const float v = -((a0 + a1) + (a2 + a3));
-    const int64_t g = (row0 + r) * ld + col;
+    const int64_t g = (row0 + r) * ld + col0 + lane;
     H[g] = v;
     store_splits(sp, g, v);
   }
@@ -303,7 +378,7 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
   float* Dinv = reinterpret_cast<float*>(ws + L.off_dinv);
   float* T = reinterpret_cast<float*>(ws + L.off_T);
 
-  constexpr int SM_DIAG = (NB * LDS_ + NB) * 4, SM_TRSM = NB * LDS_ * 4, SM_INV = (NB * LDS_ + NB * NB) * 4, SM_ROW = NB * NB * 4;
+  constexpr int SM_DIAG = (NB * LDS_ + NB * XLD) * 4, SM_TRSM = (NB * LDS_ + NB) * 4, SM_INV = (NB * LDS_ + NB * NB) * 4, SM_ROW = (NB * NB + NB * RW_COLS) * 4;
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_DIAG) != cudaSuccess ||
@@ -372,7 +447,7 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
       const int rc = tc_gemm_launch_ex(true, false, false, false, true, 1, aa, bb, n_seg, T + c0, NB, nt, nt, lda, lda, np, st);
       if (rc != LCB_OK) return rc;
     }
-    tri_row_kernel<<<(int)(nt / NB) + 1, 128, SM_ROW, st>>>(A, sp, T, Dinv, lda, np, i);
+    tri_row_kernel<<<(int)(nt / RW_COLS) + 1, RW_THREADS, SM_ROW, st>>>(A, sp, T, Dinv, lda, np, i);
     LCB_CUDA_CHECK_LAUNCH("tri_row");
   }
   if (A != H) {

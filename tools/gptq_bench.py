@@ -1,7 +1,7 @@
 """GPTQ calibration seconds per Llama-3-8B transformer block on one B200 (BASELINE configs[1]).
 
 Per linear: Hessian accumulation over the calibration set (128 batches x 2048 tokens, gptq_w_only.yml), the damped
-Cholesky-inverse chain (torch / cuSOLVER: SURVEY.md §8f N1, not rewritten) and the blocked column update
+Cholesky-inverse factor (lcb_cholinv_upper; the torch / cuSOLVER chain is timed beside it) and the blocked column update
 (lcb_gptq_weight_transform). Synthetic activations / random weights of the named shapes.
 
     python tools/gptq_bench.py [--quick] [--batches N]
@@ -64,9 +64,11 @@ def main():
             L = torch.linalg.cholesky(Hd)
             Hi = torch.cholesky_inverse(L)
             return torch.linalg.cholesky(Hi, upper=True)
-        Hinv = chol()
-        t_c = ev_time(chol, 1)
-        Hinv = Hinv.contiguous()
+        t_c_torch = ev_time(chol, 1)                                      # the reference's cuSOLVER chain, for comparison
+        Hw = H.clone()
+        ops.cholinv_upper(Hw, 0.01, check=False)
+        t_c = ev_time(lambda: ops.cholinv_upper(Hw.copy_(H), 0.01, check=False), 2)
+        Hinv = Hw
         ops.gptq_weight_transform(W.clone(), Hinv, 128, 128, 0.0, 15.0, False)   # warm-up (attributes, allocator)
         Wc = W.clone()
         t0 = time.perf_counter()
@@ -75,14 +77,14 @@ def main():
         flops_h = 2.0 * T * C * C
         row = {'linear': name, 'R': R, 'C': C, 'x': mult, 'hessian_ms_per_batch': round(t_h * 1e3, 4),
                'hessian_ms_per_batch_4x': round(t_h4 * 1e3, 4), 'hessian_gemm_equiv_TFLOPs': round(flops_h / t_h4 / 1e12, 1),
-               'cholesky_chain_ms': round(t_c * 1e3, 2), 'update_ms': round(t_u * 1e3, 3), 'update_wall_ms': round(wall * 1e3, 3),
+               'cholinv_ms': round(t_c * 1e3, 2), 'torch_cholesky_chain_ms': round(t_c_torch * 1e3, 2), 'update_ms': round(t_u * 1e3, 3), 'update_wall_ms': round(wall * 1e3, 3),
                'update_gemm_equiv_TFLOPs': round(float(R) * C * C / t_u / 1e12, 2)}
         rows.append(row)
         print(json.dumps(row), flush=True)
         total['hessian_s'] += mult * nb * t_h4
         total['cholesky_s'] += mult * t_c
         total['update_s'] += mult * t_u
-        del xs, x4, S, H, W, Wc, Hinv
+        del xs, x4, S, H, W, Wc, Hinv, Hw
         torch.cuda.empty_cache()
         if quick and name.startswith('gate'):
             break
