@@ -140,6 +140,11 @@ def extras(torch, dev, tf_peak):
     cand = (torch.rand(4, C, device=dev, generator=g) + 0.5).to(torch.bfloat16)
     wq = IntegerQuantizer(4, False, 'per_group', group_size=128)
     t = ev(lambda: ops.awq_candidates(Wb, x, org, cand, wq), 3) / 4
+    del x, S, W, Wb, org, cand, Hinv, Hw
+    torch.cuda.empty_cache()
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import gptq_bench   # GPTQ calibration of one Llama-3-8B block: 128 x 2048 tokens, 7 linears (BASELINE configs[1])
+    res['gptq_calib_llama3_8b_block'] = gptq_bench.run(dev, nb=128)
     res['awq_candidate'] = {'T': T, 'R': C, 'C': C, 'ms': t * 1e3, 'TFLOPs': 2.0 * T * C * C / t / 1e12,
                             'frac_of_bf16_peak': 2.0 * T * C * C / t / 1e12 / tf_peak}
     return res
@@ -294,7 +299,7 @@ def main():
                       'parallelism': f'layers/blocks sharded x{world}, no collective'},
            'clocks': clocks, 'e2e': e2e, 'gpu_launches': args.steps, 'roofline': roofline}
 
-    if rank == 0 and not args.no_extras:
+    if rank == 0 and world == 1 and not args.no_extras:   # single-GPU side numbers; at N > 1 every rank leaves together
         for _ in range(3):
             step_per_tensor()
         sync()
@@ -311,8 +316,9 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out['cpu_baseline'] = cpu_baseline()[0]
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

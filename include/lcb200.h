@@ -71,7 +71,9 @@ typedef struct lcb_quant_spec {
   float qmin;          /* quant.py:666-677 (int) / :979-1003 (float)                */
   float qmax;
   float output_scale_factor; /* quant.py:716 (dequant only), 1.0f if unused        */
-  float clip_ratio;    /* AutoClip v1 shrink: range *= clip_ratio before qparams (auto_clip.py:139-141,258-262); 1.0f = off */
+  float clip_ratio;    /* AutoClip v1 (auto_clip.py:139-146, 258-260): every unit is clamped to [min * r, max * r] before it is
+                          quantized (r = |clip_ratio|; clip_ratio < 0 = clip_sym: [-absmax * r, absmax * r]); 1.0f = off.
+                          Dynamic 1-D units only. */
 } lcb_quant_spec;
 
 /*
@@ -203,6 +205,23 @@ int lcb_awq_candidates(const void* W, const void* x, const void* org_out, const 
                        int64_t T, int64_t R, int64_t C, int32_t n_cand, int32_t group_size,
                        const lcb_quant_spec* spec, void* workspace, void* stream);
 int64_t lcb_awq_workspace_bytes(int64_t T, int64_t R, int64_t C, int32_t n_cand);
+
+/*
+ * AutoClip v1 search (auto_clip.py:84-191, clip_version 'v1', w_only): for every (output channel r, group g)
+ *   for i_s in 0 .. n_steps-1:  max_val = org_max * (1 - i_s / n_grid);  min_val = org_min * (1 - i_s / n_grid)  (clip_sym:
+ *       org_max = |w|.amax, min_val = -max_val);  q_w = fake_quant(clamp(w, min_val, max_val));
+ *       err = mean_t ((x_g q_w_g^T) - (x_g w_g^T))^2;  keep the first step with the smallest err
+ * W [R, C], x [T_rows, C] (the sampled tokens, auto_clip.py:131-133) row-major in spec->dtype (bf16 / f16); rows
+ * tokens .. T_rows-1 of x must be zero (padding to a multiple of 8); `tokens` is the divisor of the mean.
+ * best_max / best_min: [R, C / group] in the tensor dtype (group_size <= 0: one group per row). spec: the weight
+ * quantizer (dynamic, LCB_OUT_FAKE, math_dtype == dtype). The per-step output is never materialised: the grouped
+ * tcgen05 product reduces the squared error over tokens in its epilogue.
+ * workspace: lcb_autoclip_workspace_bytes(R, C, T_rows, group_size).
+ */
+int lcb_autoclip_search(const void* W, const void* x, void* best_max, void* best_min, int64_t R, int64_t C, int64_t T_rows,
+                        int64_t tokens, int32_t group_size, int32_t n_grid, int32_t n_steps, int32_t clip_sym,
+                        const lcb_quant_spec* spec, void* workspace, void* stream);
+int64_t lcb_autoclip_workspace_bytes(int64_t R, int64_t C, int64_t T_rows, int64_t group_size);
 
 /* column absmax of a [rows, cols] matrix -> fp32 [cols] (running max: out = max(out, colmax)).
  * Replaces SmoothQuant.get_act_scale / get_weight_scale (smoothquant.py:27-51) and the |x| reductions

@@ -46,6 +46,9 @@ SIGNATURES = {
     'lcb_awq_candidates': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32,
                                           _c_i32, ctypes.POINTER(QuantSpec), _c_vp, _c_vp]),
     'lcb_awq_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i64, _c_i32]),
+    'lcb_autoclip_search': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32,
+                                           _c_i32, _c_i32, ctypes.POINTER(QuantSpec), _c_vp, _c_vp]),
+    'lcb_autoclip_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i64, _c_i64]),
     'lcb_col_absstat': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
 }
 

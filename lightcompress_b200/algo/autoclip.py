@@ -1,13 +1,13 @@
 """AutoClip v1 (auto_clip.py:44-215): per-(out-channel, group) search of the weight clipping range.
 
-Interim implementation: the reference's broadcast product `(x * w).sum(-1)` — which materialises a
-[256, 512, C] temporary per shrink step — becomes one batched GEMM per step over the groups ([ng, oc, gs] x [ng, gs, tok],
-a plain library bmm, fp32 accumulation, output in the tensor dtype) and the fake-quant runs in the fused kernel. A
-dedicated grouped tcgen05 kernel with a fused clamp + fake-quant + squared-error epilogue is the planned replacement.
-Numerics differ from the reference in summation order only (its products are rounded to the tensor dtype one by one),
-so near-tied (channel, group) pairs may pick a neighbouring shrink step; tests report the agreement rate."""
+The search runs in lcb_autoclip_search (csrc/autoclip.cu): per shrink step one fused clamp + fake-quant pass over W and
+one grouped tcgen05 product whose epilogue reduces the squared output error over the sampled tokens; the reference's
+[256, tok, C] broadcast product is never materialised. Roundings follow the reference op by op (output, difference,
+square and mean rounded to the tensor dtype); the products themselves are exact and summed in fp32 where the reference
+rounds each one first, so near-tied shrink steps can resolve differently (tests/test_autoclip_gpu.py reports it)."""
 import torch
 
+from .. import ops
 from . import dist as lcdist
 
 _SKIP = ('q_', 'k_', 'query', 'key', 'Wqkv')   # auto_clip.py:56
@@ -17,33 +17,13 @@ _SKIP = ('q_', 'k_', 'query', 'key', 'Wqkv')   # auto_clip.py:56
 def auto_clip_layer(w, x, wquantizer, clip_sym, n_grid=20, max_shrink=0.5, n_sample_token=None):
     """Returns (best_max_val, best_min_val), each [oc, n_group, 1] in w.dtype (auto_clip.py:84-191, clip_version v1)."""
     assert w.dim() == 2
-    oc, C = w.shape
-    gs = wquantizer.group_size if wquantizer.granularity == 'per_group' else C
-    ng = C // gs
-    W = w.reshape(oc, ng, gs)
+    C = w.shape[1]
     x = x.reshape(-1, C)
     if n_sample_token is None:
         n_sample_token = min(x.shape[0], 512)
     step = max(1, x.shape[0] // n_sample_token)
     x = x[0::step]
-    xg = x.reshape(x.shape[0], ng, gs).permute(1, 2, 0).contiguous()          # [ng, gs, tok]
-    org_out = torch.bmm(W.permute(1, 0, 2).contiguous(), xg)                  # [ng, oc, tok]
-    org_max = W.abs().amax(dim=-1, keepdim=True) if clip_sym else W.amax(dim=-1, keepdim=True)
-    org_min = W.amin(dim=-1, keepdim=True)
-    best_max, best_min = org_max.clone(), org_min.clone()
-    min_errs = torch.ones_like(org_max) * 1e9
-    for i_s in range(int(max_shrink * n_grid)):
-        max_val = org_max * (1 - i_s / n_grid)
-        min_val = -max_val if clip_sym else org_min * (1 - i_s / n_grid)
-        cur_w = torch.clamp(W, min_val, max_val)
-        q_w = wquantizer.fake_quant_weight_dynamic(cur_w.reshape(oc, C)).reshape(oc, ng, gs)
-        cur_out = torch.bmm(q_w.permute(1, 0, 2).contiguous(), xg)
-        err = (cur_out - org_out).pow(2).mean(dim=2).t().unsqueeze(-1)        # [oc, ng, 1]
-        better = err < min_errs
-        min_errs[better] = err[better]
-        best_max[better] = max_val[better]
-        best_min[better] = min_val[better]
-    return best_max, best_min
+    return ops.autoclip_search(w, x.to(w.dtype), wquantizer, clip_sym, n_grid, max_shrink)
 
 
 @torch.no_grad()

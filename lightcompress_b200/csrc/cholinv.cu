@@ -39,6 +39,29 @@ __device__ __forceinline__ void store_splits(const Splits& sp, int64_t idx, floa
   if (sp.ns > 2) sp.s[2][idx] = __float2bfloat16_rn(r1 - __bfloat162float(m));
 }
 
+// 128 x 128 fp32 block global -> shared, NT threads, loads issued in batches of 16 before any store (a plain copy loop
+// serialises on the load latency). dst index = f(r, c).
+template <int NT, typename F>
+__device__ __forceinline__ void load_block(const float* __restrict__ base, int64_t ld, F&& put) {
+  constexpr int PER = NB * NB / NT;
+  static_assert(PER % 16 == 0 || PER < 16, "batching");
+  constexpr int B = PER < 16 ? PER : 16;
+#pragma unroll 1
+  for (int b0 = 0; b0 < PER; b0 += B) {
+    float v[B];
+#pragma unroll
+    for (int u = 0; u < B; ++u) {
+      const int idx = (b0 + u) * NT + threadIdx.x;
+      v[u] = base[(int64_t)(idx >> 7) * ld + (idx & 127)];
+    }
+#pragma unroll
+    for (int u = 0; u < B; ++u) {
+      const int idx = (b0 + u) * NT + threadIdx.x;
+      put(idx >> 7, idx & 127, v[u]);
+    }
+  }
+}
+
 // ---- H[i, i] += percdamp * mean(diag H)   (gptq.py:165-167); one CTA -------------------------------------------------
 __global__ void __launch_bounds__(1024) chol_damp_kernel(float* __restrict__ H, int64_t n, int64_t ld, float percdamp) {
   __shared__ float red[32];
@@ -98,10 +121,7 @@ __global__ void __launch_bounds__(512) chol_diag_kernel(float* __restrict__ H, S
   float* Rp = X + (NB - PW) * XLD;       // [PW][XLD]       diagonal sub-block factor
   float* base = H + (int64_t)kb * NB * ld + (int64_t)kb * NB;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int idx = tid; idx < NB * NB; idx += 512) {
-    const int r = idx >> 7, c = idx & 127;
-    A[r * LDS_ + c] = base[(int64_t)r * ld + c];
-  }
+  load_block<512>(base, ld, [&](int r, int c, float v) { A[r * LDS_ + c] = v; });
   __syncthreads();
 #pragma unroll 1
   for (int p = NB / PW - 1; p >= 0; --p) {
@@ -200,10 +220,7 @@ __global__ void __launch_bounds__(256) chol_trsm_kernel(float* __restrict__ H, S
   extern __shared__ float smf[];
   float* RT = smf;  // [NB][LDS_]
   const float* diag = H + (int64_t)kb * NB * ld + (int64_t)kb * NB;
-  for (int idx = threadIdx.x; idx < NB * NB; idx += 256) {
-    const int i = idx >> 7, j = idx & 127;
-    RT[j * LDS_ + i] = diag[(int64_t)i * ld + j];
-  }
+  load_block<256>(diag, ld, [&](int i, int j, float v) { RT[j * LDS_ + i] = v; });
   float* rinv = smf + NB * LDS_;  // [NB] 1 / R[j][j]: the chain multiplies instead of dividing
   if (threadIdx.x < NB) rinv[threadIdx.x] = __fdiv_rn(1.f, diag[(int64_t)threadIdx.x * ld + threadIdx.x]);
   __syncthreads();
@@ -244,11 +261,10 @@ __global__ void __launch_bounds__(128) tri_inv_diag_kernel(const float* __restri
   float* U = smf + NB * LDS_;   // [NB][NB]  (U[k][c])
   const int kb = blockIdx.x;
   const float* base = H + (int64_t)kb * NB * ld + (int64_t)kb * NB;
-  for (int idx = threadIdx.x; idx < NB * NB; idx += 128) {
-    const int r = idx >> 7, c = idx & 127;
-    R[r * LDS_ + c] = base[(int64_t)r * ld + c];
-    U[idx] = 0.f;
-  }
+  load_block<128>(base, ld, [&](int r, int c, float v) {
+    R[r * LDS_ + c] = v;
+    U[r * NB + c] = 0.f;
+  });
   __syncthreads();
   const int c = threadIdx.x;
   const int cmax = (c | 31);  // warp-uniform upper bound of this warp's columns
@@ -279,8 +295,13 @@ __global__ void __launch_bounds__(RW_THREADS) tri_row_kernel(float* __restrict__
   float* Uii = smf;             // [NB][NB]
   float* Ts = smf + NB * NB;    // [NB][RW_COLS]
   const float* d = Dinv + (int64_t)ib * NB * NB;
-  for (int idx = threadIdx.x; idx < NB * NB / 4; idx += RW_THREADS)
-    reinterpret_cast<float4*>(Uii)[idx] = reinterpret_cast<const float4*>(d)[idx];
+  {
+    float4 v[NB * NB / 4 / RW_THREADS];
+#pragma unroll
+    for (int u = 0; u < NB * NB / 4 / RW_THREADS; ++u) v[u] = reinterpret_cast<const float4*>(d)[u * RW_THREADS + threadIdx.x];
+#pragma unroll
+    for (int u = 0; u < NB * NB / 4 / RW_THREADS; ++u) reinterpret_cast<float4*>(Uii)[u * RW_THREADS + threadIdx.x] = v[u];
+  }
   const int64_t row0 = (int64_t)ib * NB;
   if (blockIdx.x == gridDim.x - 1) {   // the diagonal block itself
     __syncthreads();
@@ -293,10 +314,20 @@ __global__ void __launch_bounds__(RW_THREADS) tri_row_kernel(float* __restrict__
     return;
   }
   const int64_t col0 = row0 + NB + (int64_t)blockIdx.x * RW_COLS;
-  for (int idx = threadIdx.x; idx < NB * RW_COLS; idx += RW_THREADS) {
-    const int k = idx >> 5, c = idx & 31;
-    Ts[idx] = T[(int64_t)k * ld + col0 + c];
-    T[(int64_t)k * ld + col0 + c] = 0.f;
+  {
+    constexpr int PER = NB * RW_COLS / RW_THREADS;
+    float v[PER];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int idx = u * RW_THREADS + threadIdx.x;
+      v[u] = T[(int64_t)(idx >> 5) * ld + col0 + (idx & 31)];
+    }
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int idx = u * RW_THREADS + threadIdx.x;
+      Ts[idx] = v[u];
+      T[(int64_t)(idx >> 5) * ld + col0 + (idx & 31)] = 0.f;
+    }
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

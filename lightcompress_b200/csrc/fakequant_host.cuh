@@ -313,6 +313,10 @@ extern "C" int lcb_fakequant(const void* in, void* out, void* scales, void* zero
     return LCB_E_INVALID;
   if (spec->kind == LCB_KIND_INT && spec->out_mode == LCB_OUT_FP8) return LCB_E_INVALID;
   if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  if (spec->clip_ratio != 1.0f && spec->clip_ratio != -1.0f) {   // AutoClip v1: dynamic 1-D units, math in the tensor dtype
+    if (!(fabsf(spec->clip_ratio) > 0.f && fabsf(spec->clip_ratio) <= 1.f)) return LCB_E_INVALID;
+    if (!dynamic || unit_rows != 1 || spec->math_dtype != spec->dtype) return LCB_E_UNSUPPORTED;
+  }
   if (rows == 0 || cols == 0) return LCB_OK;
   // ragged units are only defined for per_block (zero padding); 1-D groups must divide (quant.py:627-630)
   if (unit_rows == 1 && unit_cols < cols && cols % unit_cols != 0) return LCB_E_SHAPE;

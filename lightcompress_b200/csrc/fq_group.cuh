@@ -84,11 +84,7 @@ struct FastSpec {   // host-precomputed constants of the fast chains
 // qparams of one unit from its range; math dtype == storage dtype T (quant.py:545-559)
 template <typename T>
 __device__ __forceinline__ void qparams_unit(float mn, float mx, const SpecD& sp, const FastSpec& fs, UnitQ& u) {
-  if (sp.clip != 1.0f) {
-    mx = TI<T>::rd(__fmul_rn(mx, sp.clip));
-    mn = TI<T>::rd(__fmul_rn(mn, sp.clip));
-  }
-  float s, z = 0.f, r;
+  float s, z = 0.f, r;   // sp.clip was consumed by fq_finish_unit (the vectors and the range arrive clamped)
   const bool symlike = sp.sym || sp.kind != LCB_KIND_INT;
   // rd(max(a, 1e-5f)) == max(a, rd(1e-5f)) for a already in T
   const float a = symlike ? max_nan(max_nan(fabsf(mx), fabsf(mn)), fs.eps) : max_nan(TI<T>::rd(__fsub_rn(mx, mn)), fs.eps);
@@ -172,11 +168,29 @@ enum { CHAIN_ANY_OUT = -1 };  // template value: runtime out_mode, out-of-line g
 // qparams -> (rare) literal path or the compiled-in element chain -> stores, for the NV vectors one lane holds of a unit.
 // Lane's vector j sits at vector index v0 + j * vstride of the unit and at element offset e0 + j * vstride * VEC.
 template <typename T, int NV, int KINDC, int CHAIN>
-__device__ __forceinline__ void fq_finish_unit(const uint4 (&raw)[NV], float mn, float mx, int64_t unit, int64_t e0, int v0,
+__device__ __forceinline__ void fq_finish_unit(const uint4 (&raw_in)[NV], float mn, float mx, int64_t unit, int64_t e0, int v0,
                                                int vstride, int nvec, bool writer, void* __restrict__ out,
-                                               void* __restrict__ scales, void* __restrict__ zeros, const SpecD& sp,
+                                               void* __restrict__ scales, void* __restrict__ zeros, const SpecD& sp_in,
                                                const FastSpec& fs) {
   constexpr int VEC = TI<T>::VEC;
+  uint4 raw[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) raw[j] = raw_in[j];
+  SpecD sp = sp_in;
+  {  // AutoClip v1: clamp the unit to its shrunk range first; everything below then sees the clamped tensor
+    float lo, hi;
+    if (clip_bounds(mn, mx, sp.clip, TI<T>::ID, lo, hi)) {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        float f[VEC];
+        TI<T>::unpack(raw[j], f);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) f[i] = clamp_nan(f[i], lo, hi);
+        raw[j] = TI<T>::pack(f);
+      }
+    }
+    sp.clip = 1.0f;
+  }
   UnitQ u;
   qparams_unit<T>(mn, mx, sp, fs, u);
   if (u.exact) {  // unit-uniform, rare: literal chain, qparams recomputed literally as well

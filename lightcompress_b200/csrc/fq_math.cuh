@@ -21,7 +21,14 @@ struct UnitQ {
   float lo, hi; // qmin - z, qmax - z
   float s_out;  // s * output_scale_factor (rounded)
   int exact;    // 1 -> this unit must take the literal chain
+  float clo = -INFINITY, chi = INFINITY;  // AutoClip v1 clamp bounds of this unit (fq_elem_literal clamps x when clipped)
+  int clipped = 0;
 };
+
+// AutoClip v1 (auto_clip.py:112-117, 139-146, 258-260): max_val = org_max * ratio, min_val = org_min * ratio, or with
+// clip_sym (clip < 0) org_max = |w|.amax and min_val = -max_val; cur_w = clamp(w, min_val, max_val) is what the quantizer
+// sees, so its range is the clamped range (clamp is monotonic). Returns false when the spec does not clip.
+__device__ __forceinline__ bool clip_bounds(float& mn, float& mx, float clip, int md, float& lo, float& hi);
 
 struct SpecD {  // device copy of lcb_quant_spec + derived flags
   int dtype, math_dtype, qparam_dtype, kind, sym, round_zp, out_mode, fast_ok, qp_math;
@@ -34,14 +41,26 @@ __device__ __forceinline__ float clamp_nan(float v, float lo, float hi) {
 
 __device__ __forceinline__ bool finite_f(float v) { return fabsf(v) <= 3.402823466e38f; }
 
+__device__ __forceinline__ bool clip_bounds(float& mn, float& mx, float clip, int md, float& lo, float& hi) {
+  if (clip == 1.0f || clip == -1.0f) return false;
+  const float r = fabsf(clip);
+  if (clip < 0.f) {
+    hi = rd_rt(__fmul_rn(max_nan(fabsf(mx), fabsf(mn)), r), md);
+    lo = -hi;
+  } else {
+    hi = rd_rt(__fmul_rn(mx, r), md);
+    lo = rd_rt(__fmul_rn(mn, r), md);
+  }
+  mx = clamp_nan(mx, lo, hi);
+  mn = clamp_nan(mn, lo, hi);
+  return true;
+}
+
 // ---- qparams from a (min, max) range: quant.py:545-559 -------------------------------------------
 __device__ __forceinline__ void qparams_from_range(float mn, float mx, const SpecD& sp, UnitQ& u) {
   const int md = sp.math_dtype;
   const int mq = sp.qp_math;  // dtype of the qparam divisions (== md except per_tensor 0-dim promotion)
-  if (sp.clip != 1.0f) {  // AutoClip v1 shrink (auto_clip.py:139-141): max_val = org_max * (1 - i/n)
-    mx = rd_rt(__fmul_rn(mx, sp.clip), md);
-    mn = rd_rt(__fmul_rn(mn, sp.clip), md);
-  }
+  u.clipped = clip_bounds(mn, mx, sp.clip, md, u.clo, u.chi) ? 1 : 0;
   float s, z = 0.f;
   if (sp.sym || sp.kind != LCB_KIND_INT) {
     float a = max_nan(fabsf(mx), fabsf(mn));  // both already in math dtype: abs/max exact
@@ -82,6 +101,7 @@ __device__ __forceinline__ void finish_unit(const SpecD& sp, UnitQ& u) {
 // returns (.x) the fake-quant value, already rounded to the math dtype, and (.y) the integer / fp8 code value
 static __device__ __noinline__ float2 fq_elem_literal(float x, const UnitQ& u, const SpecD& sp) {
   const int md = sp.math_dtype;
+  if (u.clipped) x = clamp_nan(x, u.clo, u.chi);
   if (sp.kind == LCB_KIND_INT) {
     float q;
     if (sp.round_zp) {

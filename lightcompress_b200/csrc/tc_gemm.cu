@@ -87,6 +87,10 @@ int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tr
   p.kb_per_split = (kb_total + nsplit - 1) / nsplit;
   p.nsplit = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.n_seg = n_seg;
+  p.n_grp = 1;
+  p.kb_grp = 0;
+  p.org_grp_stride = 0;
+  p.rowsse = nullptr;
   p.tri_b = tri_b ? 1 : 0;
   p.idesc = tc::idesc_f16(fmt, BM, BN, a_kmajor ? 0 : 1, b_kmajor ? 0 : 1);
   p.org = nullptr;
@@ -147,6 +151,10 @@ int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org,
   p.nsplit = 1;  // the output is rounded before it is compared: no split-K
   p.kb_per_split = (int)((K + BK - 1) / BK);
   p.n_seg = 1;
+  p.n_grp = 1;
+  p.kb_grp = 0;
+  p.org_grp_stride = 0;
+  p.rowsse = nullptr;
   p.tri_b = 0;
   p.idesc = tc::idesc_f16(fmt, BM, BN, 0, 0);
   p.org = org;
@@ -166,6 +174,57 @@ int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org,
   }
   const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
   return launch_variant<true, true, false, false, EPI_MSE>(maps, p, grid, st);
+}
+
+int tc_grouped_rowsse_launch(int fmt, int store, const void* w, const void* x, void* org, double* rowsse, int64_t R,
+                             int64_t T, int64_t C, int64_t gs, cudaStream_t st) {
+  using namespace tcg;
+  if (R <= 0 || T <= 0) return LCB_OK;
+  if (C <= 0 || gs <= 0 || C % gs) return LCB_E_SHAPE;
+  if (gs % BK) return LCB_E_UNSUPPORTED;
+  if (R > (1 << 30) || T > (1 << 30) || C > (1 << 30)) return LCB_E_SHAPE;
+  if ((C % 8) || (T % 8) || (reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(w) & 15) ||
+      (reinterpret_cast<uintptr_t>(org) & 15))
+    return LCB_E_ALIGN;
+  if (!store && !rowsse) return LCB_E_INVALID;
+  Maps maps;
+  Params p;
+  p.M = (int)R;
+  p.N = (int)T;
+  p.K = (int)C;
+  p.nblk_i = (int)((R + BM - 1) / BM);
+  p.nblk_j = (int)((T + BN - 1) / BN);
+  p.n_tiles = p.nblk_i * p.nblk_j;
+  p.nsplit = 1;
+  p.n_grp = (int)(C / gs);
+  p.kb_grp = (int)(gs / BK);
+  p.kb_per_split = p.kb_grp;
+  p.n_seg = 1;
+  p.tri_b = 0;
+  p.idesc = tc::idesc_f16(fmt, BM, BN, 0, 0);
+  p.org = org;
+  p.ld_org = T;
+  p.org_grp_stride = R * T;
+  p.org_fmt = fmt;
+  p.loss = nullptr;
+  p.rowsse = rowsse;
+  const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  bool ok = make_tmap_2d(&maps.a[0], w, dt16, 2, R, C, C * 2, BM, BK) &&   // [R, C]: box 128 rows x 64 k
+            make_tmap_2d(&maps.b[0], x, dt16, 2, T, C, C * 2, BN, BK);     // [T, C]: box 256 rows x 64 k
+  if (!ok) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return LCB_E_CUDA;
+  }
+  for (int s = 1; s < MAX_SEG; ++s) {
+    maps.a[s] = maps.a[0];
+    maps.b[s] = maps.b[0];
+  }
+  maps.d = maps.a[0];  // unused by these epilogues
+  const int64_t n_items = (int64_t)p.n_tiles * p.n_grp;
+  if (n_items > (1ll << 30)) return LCB_E_SHAPE;
+  const int grid = (int)(n_items < kNumSMs ? n_items : kNumSMs);
+  if (store) return launch_variant<true, true, false, false, EPI_STORE16>(maps, p, grid, st);
+  return launch_variant<true, true, false, false, EPI_ROWSSE>(maps, p, grid, st);
 }
 
 }  // namespace lcb

@@ -29,7 +29,9 @@ constexpr int SMEM_BYTES = SMEM_MAIN + SMEM_EPI + 256 + 1024;  // + barriers + a
 constexpr int NTHREADS = 192;
 constexpr int MAX_SEG = 6;
 
-enum { EPI_REDUCE_ADD = 0, EPI_MSE = 1 };
+// EPI_STORE16: org[g][row][col] = rd16(acc) (no D). EPI_ROWSSE: rowsse[row * n_grp + g] += sum_col rd16(rd16(rd16(acc) -
+// org[g][row][col])^2) — the per-(output channel, group) squared error of AutoClip (auto_clip.py:150-156).
+enum { EPI_REDUCE_ADD = 0, EPI_MSE = 1, EPI_STORE16 = 2, EPI_ROWSSE = 3 };
 
 struct Params {
   int M, N, K;
@@ -39,6 +41,10 @@ struct Params {
   int nsplit;        // K splits per tile
   int kb_per_split;  // 64-deep K blocks per split (per segment)
   int n_seg;
+  int n_grp;         // grouped mode (n_grp > 1): group g contracts K blocks [g * kb_grp, (g + 1) * kb_grp) only — one
+  int kb_grp;        // independent [M, N] product per group of input channels (AutoClip's (x * w).sum(-1))
+  int64_t org_grp_stride;  // elements between consecutive groups of org
+  double* rowsse;
   int tri_b;         // B[k, n] == 0 for k > n (upper-triangular B): column block tj only needs k < (tj + 1) * BN
   uint32_t idesc;
   // EPI_MSE: loss[0] += sum over the tile of rd16(rd16(org) - rd16(acc))^2   (awq.py:134-145 on 16-bit tensors)
@@ -77,6 +83,22 @@ __device__ __forceinline__ int k_hi(const Params& p, int tj, int kb_total) {
   return p.tri_b ? min(kb_total, ((tj + 1) * BN + BK - 1) / BK) : kb_total;
 }
 
+struct Item {
+  int ti, tj, g, kb0, kb1;   // tile, group, K-block range [kb0, kb1) (empty: the item is skipped by every role)
+};
+template <bool SYRK>
+__device__ __forceinline__ Item decode_item(const Params& p, int item, int kb_total) {
+  Item it;
+  const int per_grp = p.n_tiles * p.nsplit;
+  it.g = item / per_grp;
+  const int r = item - it.g * per_grp;
+  tile_of<SYRK>(r / p.nsplit, p.nblk_j, it.ti, it.tj);
+  const int split = r % p.nsplit;
+  it.kb0 = it.g * p.kb_grp + split * p.kb_per_split;
+  it.kb1 = min(k_hi(p, it.tj, kb_total), it.kb0 + p.kb_per_split);
+  return it;
+}
+
 template <int FMT>
 __device__ __forceinline__ float rd16(float x) {
   if (FMT == 1) {
@@ -113,6 +135,49 @@ __device__ __forceinline__ float mse_row32(const uint32_t (&v)[32], const uint8_
   return sum;
 }
 
+// AutoClip: sum over 32 columns of rd16(d * d), d = rd16(rd16(acc) - org) (auto_clip.py:150: (cur_out - org_out).pow(2),
+// every op rounded to the tensor dtype; the mean over tokens accumulates these in fp32)
+template <int FMT>
+__device__ __forceinline__ float sse2_row32(const uint32_t (&v)[32], const uint8_t* org_row, int ncols) {
+  float sum = 0.f;
+#pragma unroll
+  for (int c8 = 0; c8 < 4; ++c8) {
+    if (c8 * 8 < ncols) {
+      const uint4 o = *reinterpret_cast<const uint4*>(org_row + c8 * 16);
+      const uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 og = unpack16x2<FMT>(ow[j]);
+        const float d0 = rd16<FMT>(__fsub_rn(rd16<FMT>(__uint_as_float(v[c8 * 8 + 2 * j])), og.x));
+        const float d1 = rd16<FMT>(__fsub_rn(rd16<FMT>(__uint_as_float(v[c8 * 8 + 2 * j + 1])), og.y));
+        sum = __fadd_rn(sum, rd16<FMT>(__fmul_rn(d0, d0)));
+        sum = __fadd_rn(sum, rd16<FMT>(__fmul_rn(d1, d1)));
+      }
+    }
+  }
+  return sum;
+}
+template <int FMT>
+__device__ __forceinline__ void store16_row32(const uint32_t (&v)[32], uint8_t* out_row, int ncols) {
+#pragma unroll
+  for (int c8 = 0; c8 < 4; ++c8) {
+    if (c8 * 8 < ncols) {
+      uint32_t w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a = __uint_as_float(v[c8 * 8 + 2 * j]), b = __uint_as_float(v[c8 * 8 + 2 * j + 1]);
+        if (FMT == 1) {
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w[j]) : "f"(b), "f"(a));
+        } else {
+          const __half2 h = __floats2half2_rn(a, b);
+          w[j] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+      }
+      *reinterpret_cast<uint4*>(out_row + c8 * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
 template <bool A_KMAJOR, bool B_KMAJOR, bool SYRK, bool NEG, int EPI>
 __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant__ Maps maps, const Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -147,7 +212,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int n_items = p.n_tiles * p.nsplit;
+  const int n_items = p.n_tiles * p.nsplit * p.n_grp;
   const int kb_total = (p.K + BK - 1) / BK;
 
   if (warp == 0) {
@@ -156,11 +221,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        int ti, tj;
-        tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
-        const int split = item % p.nsplit;
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(k_hi(p, tj, kb_total), kb0 + p.kb_per_split);
+        const Item it = decode_item<SYRK>(p, item, kb_total);
+        const int ti = it.ti, tj = it.tj, kb0 = it.kb0, kb1 = it.kb1;
         for (int seg = 0; seg < p.n_seg; ++seg) {
           for (int kb = kb0; kb < kb1; ++kb) {
             tc::mbar_wait(&empty[stage], phase ^ 1);
@@ -200,12 +262,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
     const uint64_t desc_mn = tc::smem_desc_sw128(BOX_BYTES, 1024);
     const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-      int ti, tj;
-      tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
-      const int split = item % p.nsplit;
-      const int kb0 = split * p.kb_per_split;
-      const int kb1 = min(k_hi(p, tj, kb_total), kb0 + p.kb_per_split);
-      const int n_kb = (kb1 - kb0) * p.n_seg;
+      const Item it = decode_item<SYRK>(p, item, kb_total);
+      const int n_kb = (it.kb1 - it.kb0) * p.n_seg;
       if (n_kb <= 0) continue;   // tri_b: this K split lies entirely below the triangle (all roles skip it alike)
       tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
       tc::tc_fence_after();
@@ -244,10 +302,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
     int buf = 0;
     double mse_sum = 0.0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-      int ti, tj;
-      tile_of<SYRK>(item / p.nsplit, p.nblk_j, ti, tj);
-      if (min(k_hi(p, tj, kb_total), (item % p.nsplit) * p.kb_per_split + p.kb_per_split) <= (item % p.nsplit) * p.kb_per_split)
-        continue;
+      const Item it = decode_item<SYRK>(p, item, kb_total);
+      const int ti = it.ti, tj = it.tj;
+      if (it.kb1 <= it.kb0) continue;
       tc::mbar_wait(&tfull[acc], acc_phase);
       tc::tc_fence_after();
       const int row0 = ti * BM + q * 32;
@@ -260,13 +317,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
         uint32_t v[32];
         tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
         tc::tmem_ld_wait();
-        if (EPI == EPI_MSE) {
-          // TMEM -> registers -> round to the 16-bit output dtype -> squared error against org_out
+        if (EPI == EPI_MSE || EPI == EPI_ROWSSE || EPI == EPI_STORE16) {
+          // TMEM -> registers -> round to the 16-bit output dtype -> squared error against org_out (or store)
           const int row = row0 + lane;
           if (row < p.M) {
-            const uint8_t* org_row = reinterpret_cast<const uint8_t*>(p.org) + ((int64_t)row * p.ld_org + col0) * 2;
+            uint8_t* org_row = reinterpret_cast<uint8_t*>(const_cast<void*>(p.org)) +
+                               ((int64_t)it.g * p.org_grp_stride + (int64_t)row * p.ld_org + col0) * 2;
             const int ncols = min(32, p.N - col0);
-            tile_sum += p.org_fmt == 1 ? mse_row32<1>(v, org_row, ncols) : mse_row32<0>(v, org_row, ncols);
+            if (EPI == EPI_MSE) tile_sum += p.org_fmt == 1 ? mse_row32<1>(v, org_row, ncols) : mse_row32<0>(v, org_row, ncols);
+            if (EPI == EPI_ROWSSE) tile_sum += p.org_fmt == 1 ? sse2_row32<1>(v, org_row, ncols) : sse2_row32<0>(v, org_row, ncols);
+            if (EPI == EPI_STORE16) {
+              if (p.org_fmt == 1) store16_row32<1>(v, org_row, ncols); else store16_row32<0>(v, org_row, ncols);
+            }
           }
         } else {
           // TMEM -> registers -> 128B-swizzled smem -> TMA reduce-add into D.
@@ -290,7 +352,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
           buf ^= 1;
         }
       }
-      mse_sum += (double)tile_sum;
+      if (EPI == EPI_ROWSSE) {   // lane = output channel: one atomic per (row, group, tile)
+        if (row0 + lane < p.M) atomicAdd(p.rowsse + (int64_t)(row0 + lane) * p.n_grp + it.g, (double)tile_sum);
+      } else {
+        mse_sum += (double)tile_sum;
+      }
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[acc]);
@@ -301,7 +367,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) mse_sum += __shfl_xor_sync(0xffffffffu, mse_sum, o);
       if (lane == 0 && mse_sum != 0.0) atomicAdd(p.loss, mse_sum);
-    } else {
+    } else if (EPI == EPI_REDUCE_ADD) {
       if (lane == 0) tc::bulk_wait_all();
     }
   }
@@ -332,5 +398,12 @@ int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tr
 // Awq.calculate_loss (awq.py:134-145) without writing the output. x [M, K], w [N, K], org [M, N], all 16-bit row-major.
 int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org, double* loss, int64_t M, int64_t N,
                          int64_t K, int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st);
+
+// Grouped product for AutoClip (auto_clip.py:133-156): for every group g of `gs` input channels,
+//   out_g[r, t] = sum_{c in g} w[r, c] * x[t, c]          w [R, C], x [T, C] 16-bit row-major, C = n_grp * gs, gs % 64 == 0
+// store != 0: org[g][r][t] = rd16(out_g)   (org is [n_grp, R, T], T % 8 == 0)
+// store == 0: rowsse[r * n_grp + g] += sum_t rd16(rd16(rd16(out_g[r, t]) - org[g][r][t])^2)
+int tc_grouped_rowsse_launch(int fmt, int store, const void* w, const void* x, void* org, double* rowsse, int64_t R,
+                             int64_t T, int64_t C, int64_t gs, cudaStream_t st);
 
 }  // namespace lcb

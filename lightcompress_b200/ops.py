@@ -195,3 +195,41 @@ def awq_candidates(W, x, org_out, cand_scales, wquantizer):
                                     gs, spec, ws.data_ptr(), _stream(W.device.index))
     _cabi.check(st, 'lcb_awq_candidates')
     return loss / float(T * R)
+
+
+def autoclip_search(W, x, wquantizer, clip_sym, n_grid=20, max_shrink=0.5):
+    """AutoClip v1 search of one linear (auto_clip.py:84-191): returns (best_max_val, best_min_val), each [R, n_group, 1]
+    in W.dtype. W [R, C] bf16 / f16; x [tokens, C] = the sampled tokens (auto_clip.py:131-133) in the same dtype."""
+    _need_cuda(W, x)
+    W = W.contiguous()
+    R, C = W.shape
+    x2 = x.reshape(-1, C)
+    if x2.dtype != W.dtype:
+        raise TypeError(f'autoclip_search: x is {x2.dtype}, W is {W.dtype}')
+    tokens = x2.shape[0]
+    T_rows = -(-tokens // 8) * 8
+    if T_rows != tokens:   # zero rows add nothing to the squared error; the mean still divides by `tokens`
+        xp = torch.zeros((T_rows, C), dtype=x2.dtype, device=x2.device)
+        xp[:tokens] = x2
+        x2 = xp
+    x2 = x2.contiguous()
+    g = wquantizer.granularity
+    if g == 'per_group':
+        gs = wquantizer.group_size
+    elif g == 'per_channel':
+        gs = 0
+    else:
+        raise NotImplementedError(f'autoclip_search: weight granularity {g}')
+    ng = C // gs if gs > 0 else 1
+    qmin, qmax = wquantizer._qrange()
+    spec = wquantizer._spec(W.dtype, W.dtype, W.dtype, _cabi.OUT_FAKE, qmin, qmax, 1.0, 1.0, _DT[W.dtype] + 1)
+    lib = _cabi.load()
+    best_max = torch.empty((R, ng, 1), dtype=W.dtype, device=W.device)
+    best_min = torch.empty((R, ng, 1), dtype=W.dtype, device=W.device)
+    ws = torch.empty(int(lib.lcb_autoclip_workspace_bytes(R, C, T_rows, gs)), dtype=torch.uint8, device=W.device)
+    with _on_device(W.device):
+        st = lib.lcb_autoclip_search(W.data_ptr(), x2.data_ptr(), best_max.data_ptr(), best_min.data_ptr(), R, C, T_rows,
+                                     tokens, gs, int(n_grid), int(max_shrink * n_grid), 1 if clip_sym else 0, spec,
+                                     ws.data_ptr(), _stream(W.device.index))
+    _cabi.check(st, 'lcb_autoclip_search')
+    return best_max, best_min

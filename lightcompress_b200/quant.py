@@ -411,6 +411,14 @@ class BaseQuantizer(object):
                 outs_all.extend(outs)
         return outs_all
 
+    def fake_quant_weight_clipped(self, weight, ratio, clip_sym=False):
+        """AutoClipper.fake_quantize_weight, clip_version 'v1' (auto_clip.py:258-260) at one shrink step:
+        fake_quant_weight_dynamic(clamp(w, org_min * ratio, org_max * ratio)) per unit (clip_sym: +/- |w|.amax * ratio),
+        the clamp fused into the quant kernel."""
+        ratio = float(ratio)
+        q, _, _ = self._dynamic(weight, _cabi.OUT_FAKE, weight.dtype, False, clip=(-ratio if clip_sym else ratio))
+        return q
+
     def fake_quant_weight_static(self, weight, args):
         """quant.py:785-831 / :1111-1140."""
         return self._fake_static(weight, args, True)

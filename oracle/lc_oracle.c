@@ -111,16 +111,25 @@ static uint8_t encode_fp8(float q, int kind) {
   return (uint8_t)(sign | ((ex + bias) << mb) | mant);
 }
 
-typedef struct { float s, z, s_out; } unitq;
+typedef struct { float s, z, s_out, clo, chi; int clipped; } unitq;
 
 /* quant.py:545-559 */
 static void qparams(float mn, float mx, const lco_spec* sp, unitq* u) {
   const int md = sp->math_dtype;
   /* per_tensor: 0-dim range / 0-dim fp32 divisor promotes to fp32 (torch 0-dim promotion) */
   const int mq = sp->qp_math_plus1 > 0 ? sp->qp_math_plus1 - 1 : md;
-  if (sp->clip_ratio != 1.0f) {        /* auto_clip.py:139-141 */
-    mx = rd(mx * sp->clip_ratio, md);
-    mn = rd(mn * sp->clip_ratio, md);
+  u->clipped = 0;
+  if (sp->clip_ratio != 1.0f && sp->clip_ratio != -1.0f) {
+    /* AutoClip v1 (auto_clip.py:112-117, 139-146, 258-260): max_val = org_max * ratio, min_val = org_min * ratio
+       (clip_ratio < 0 = clip_sym: org_max = |w|.amax, min_val = -max_val); cur_w = clamp(w, min_val, max_val) and the
+       quantizer then sees the clamped tensor, whose range is the clamped range (clamp is monotonic). */
+    const float r = fabsf(sp->clip_ratio);
+    float hi, lo;
+    if (sp->clip_ratio < 0.0f) { hi = rd(max_nan(fabsf(mx), fabsf(mn)) * r, md); lo = -hi; }
+    else { hi = rd(mx * r, md); lo = rd(mn * r, md); }
+    mx = clamp_nan(mx, lo, hi);
+    mn = clamp_nan(mn, lo, hi);
+    u->clo = lo; u->chi = hi; u->clipped = 1;
   }
   float s, z = 0.0f;
   if (sp->sym || sp->kind != KIND_INT) {
@@ -144,6 +153,7 @@ static void qparams(float mn, float mx, const lco_spec* sp, unitq* u) {
 /* quant.py:699-717 / 1061-1081; returns fake value (math dtype), *code = code value */
 static float elem(float x, const unitq* u, const lco_spec* sp, float* code) {
   const int md = sp->math_dtype;
+  if (u->clipped) x = clamp_nan(x, u->clo, u->chi);
   if (sp->kind == KIND_INT) {
     float q;
     if (sp->round_zp) {
@@ -209,6 +219,7 @@ int lco_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t 
       if (scales) store(scales, unit, u.s_out, sp->qparam_dtype);
       if (zeros && !sp->sym && sp->kind == KIND_INT) store(zeros, unit, u.z, sp->qparam_dtype);
     } else {
+      u.clipped = 0;
       u.s = load(scales, unit, sp->qparam_dtype);
       u.z = (zeros && !sp->sym && sp->kind == KIND_INT) ? load(zeros, unit, sp->qparam_dtype) : 0.0f;
       if (sp->kind != KIND_INT && u.s == 0.0f) u.s = 1.0f;

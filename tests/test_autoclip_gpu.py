@@ -1,0 +1,107 @@
+"""GPU parity of the AutoClip path against the pinned oracle (oracle/autoclip_oracle.py, itself bit-exact against the
+UNMODIFIED reference AutoClipper: tests/test_autoclip_oracle.py).
+
+ * clamped fake-quant (fake_quant_weight_clipped -> lcb_fakequant with clip_ratio): bit-exact against the reference's
+   golden q_w (auto_clip.py:258-260) and against the oracle on random tensors;
+ * lcb_autoclip_search: the selected (best_max, best_min) must equal the oracle's for nearly every (channel, group);
+   the reference rounds every product x*w to the tensor dtype before summing, the tensor cores sum exact products, so a
+   disagreement is accepted only where the oracle's own errors of the two steps are within 5 % (a near-tie)."""
+import gzip
+import io
+import os
+
+import pytest
+import torch
+
+from lightcompress_b200 import ops
+from lightcompress_b200 import quant as Q
+from oracle import autoclip_oracle as aco
+from oracle import quant_oracle as qo
+from tests.golden.make_autoclip_golden import inputs
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'autoclip_golden.pt.gz')
+with gzip.open(PATH, 'rb') as f:
+    GOLD = torch.load(io.BytesIO(f.read()), weights_only=False)
+IDS = [f"oc{r['case']['oc']}-C{r['case']['C']}-{r['case']['dtype']}-sym{int(r['case']['clip_sym'])}" for r in GOLD]
+
+
+def spec_of(c):
+    qmin, qmax = (-(2.0 ** (c['bit'] - 1)), 2.0 ** (c['bit'] - 1) - 1) if c['sym'] else (0.0, 2.0 ** c['bit'] - 1)
+    return dict(kind=0, sym=c['sym'], qmin=qmin, qmax=qmax)
+
+
+@pytest.mark.parametrize('rec', GOLD, ids=IDS)
+def test_clipped_fake_quant_matches_reference_golden(rec):
+    c = rec['case']
+    W, _ = inputs(c)
+    wq = Q.IntegerQuantizer(c['bit'], c['sym'], 'per_group', group_size=c['gs'])
+    for i_s, ref in rec['q_w'].items():
+        got = wq.fake_quant_weight_clipped(W.to(DEV), 1 - i_s / 20, c['clip_sym']).cpu()
+        assert torch.equal(got.view(torch.int16), ref.view(torch.int16)), f'i_s={i_s}'
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('gran,gs,cols', [('per_group', 128, 1024), ('per_group', 64, 512), ('per_channel', 0, 4096),
+                                          ('per_channel', 0, 14336), ('per_channel', 0, 333)])
+@pytest.mark.parametrize('sym,clip_sym', [(False, False), (True, True), (False, True)])
+def test_clipped_fake_quant_matches_oracle(dtype, gran, gs, cols, sym, clip_sym):
+    g = torch.Generator().manual_seed(cols + gs)
+    W = (torch.randn(24, cols, generator=g) * 0.02)
+    W[3, :64] = W[3, :64].abs() + 0.01
+    W[5, :64] = -W[5, :64].abs() - 0.01
+    W = W.to(dtype)
+    kw = {'group_size': gs} if gran == 'per_group' else {}
+    wq = Q.IntegerQuantizer(4, sym, gran, **kw)
+    spec = dict(kind=0, sym=sym, qmin=-8.0 if sym else 0.0, qmax=7.0 if sym else 15.0)
+    for ratio in (0.95, 0.7, 0.55):
+        got = wq.fake_quant_weight_clipped(W.to(DEV), ratio, clip_sym).cpu()
+        ref, _, _ = qo.fakequant(W, 24, cols, 1, gs if gs else cols, clip=(-ratio if clip_sym else ratio), **spec)
+        assert torch.equal(got.view(torch.int16), ref.view(torch.int16)), ratio
+
+
+def _check_search(W, x, c, tok):
+    spec = spec_of(c)
+    bmax_o, bmin_o, errs = aco.auto_clip_layer(W, x, spec, c['gs'], c['clip_sym'], n_sample_token=tok)
+    wq = Q.IntegerQuantizer(c['bit'], c['sym'], 'per_group', group_size=c['gs'])
+    bmax, bmin = ops.autoclip_search(W.to(DEV), x.reshape(-1, x.shape[-1]).to(DEV), wq, c['clip_sym'])
+    bmax, bmin = bmax.cpu(), bmin.cpu()
+    assert bmax.shape == bmax_o.shape and bmin.shape == bmin_o.shape
+    same = (bmax.view(torch.int16) == bmax_o.view(torch.int16)) & (bmin.view(torch.int16) == bmin_o.view(torch.int16))
+    agree = float(same.float().mean())
+    # disagreements must be near-ties of the oracle's own error curve
+    errs = errs.float()                                    # [steps, oc, ng]
+    org_max = (W.reshape(W.shape[0], -1, c['gs']).abs() if c['clip_sym'] else W.reshape(W.shape[0], -1, c['gs'])).amax(-1)
+    ratio = (bmax.squeeze(-1).float() / org_max.float()).clamp(0.5, 1.0)
+    step = torch.round((1 - ratio) * 20).long().clamp(0, errs.shape[0] - 1)
+    e_sel = errs.gather(0, step.unsqueeze(0)).squeeze(0)
+    e_min = errs.min(0).values
+    bad = (~same.squeeze(-1)) & (e_sel > 1.05 * e_min + 1e-12)
+    return agree, int(bad.sum()), same.numel()
+
+
+@pytest.mark.parametrize('rec', GOLD, ids=IDS)
+def test_autoclip_search_matches_oracle(rec):
+    c = rec['case']
+    W, x = inputs(c)
+    agree, bad, n = _check_search(W, x, c, c['tok'])
+    assert agree >= 0.85, f'agreement {agree:.3f}'
+    assert bad <= max(1, n // 100), f'{bad} of {n} picks are not near-ties (agreement {agree:.3f})'
+
+
+def test_autoclip_search_ragged_tokens_and_llama_shape():
+    c = dict(oc=256, C=1024, tok=75, dtype='bfloat16', seed=31, bit=4, sym=False, gs=128, clip_sym=False)
+    W, x = inputs(c)
+    agree, bad, n = _check_search(W, x, c, c['tok'])    # 75 tokens: padded to 80 rows, mean over 75
+    assert agree >= 0.85 and bad <= max(1, n // 100), (agree, bad)
+
+
+def test_autoclip_rejects_unsupported():
+    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=32)
+    W = torch.randn(64, 256, device=DEV).to(torch.bfloat16)
+    x = torch.randn(16, 256, device=DEV).to(torch.bfloat16)
+    with pytest.raises(NotImplementedError):
+        ops.autoclip_search(W, x, wq, False)            # group of 32 < one 64-deep K block: no kernel, no fallback
+    with pytest.raises(RuntimeError):
+        ops.autoclip_search(W.cpu(), x.cpu(), Q.IntegerQuantizer(4, False, 'per_group', group_size=128), False)

@@ -33,11 +33,15 @@ def ev_time(fn, rep=1):
 
 
 def main():
-    dev = torch.device('cuda:0')
     quick = '--quick' in sys.argv
     nb = 128
     if '--batches' in sys.argv:
         nb = int(sys.argv[sys.argv.index('--batches') + 1])
+    run(torch.device('cuda:0'), nb, quick, emit=True)
+
+
+def run(dev, nb=128, quick=False, emit=False):
+    """Returns {'hessian_s', 'cholesky_s', 'update_s', 'calib_s_per_block', 'batches'} for one Llama-3-8B block."""
     T = 2048
     total = {'hessian_s': 0.0, 'cholesky_s': 0.0, 'update_s': 0.0}
     rows = []
@@ -80,7 +84,8 @@ def main():
                'cholinv_ms': round(t_c * 1e3, 2), 'torch_cholesky_chain_ms': round(t_c_torch * 1e3, 2), 'update_ms': round(t_u * 1e3, 3), 'update_wall_ms': round(wall * 1e3, 3),
                'update_gemm_equiv_TFLOPs': round(float(R) * C * C / t_u / 1e12, 2)}
         rows.append(row)
-        print(json.dumps(row), flush=True)
+        if emit:
+            print(json.dumps(row), flush=True)
         total['hessian_s'] += mult * nb * t_h4
         total['cholesky_s'] += mult * t_c
         total['update_s'] += mult * t_u
@@ -90,7 +95,9 @@ def main():
             break
     total['calib_s_per_block'] = sum(total.values())
     total['batches'] = nb
-    print(json.dumps({'llama3_8b_block': total}), flush=True)
+    if emit:
+        print(json.dumps({'llama3_8b_block': total}), flush=True)
+    return total
 
 
 if __name__ == '__main__':
