@@ -161,6 +161,15 @@ __device__ __forceinline__ uint4 quant_vec_fast_f32(const uint4& raw, const Unit
   return TI<T>::pack(val);
 }
 
+template <typename T>
+__device__ __noinline__ uint4 clamp_vec_noinline(uint4 raw, float lo, float hi) {
+  float f[TI<T>::VEC];
+  TI<T>::unpack(raw, f);
+#pragma unroll
+  for (int i = 0; i < TI<T>::VEC; ++i) f[i] = clamp_nan(f[i], lo, hi);   // exact: values and bounds are T-representable
+  return TI<T>::pack(f);
+}
+
 enum { CHAIN_ANY_OUT = -1 };  // template value: runtime out_mode, out-of-line generic chain
 
 // CHAIN: element chain compiled in. CHAIN_ANY_OUT serves every out_mode through quant_store_vec_generic; the others
@@ -176,29 +185,24 @@ __device__ __forceinline__ void fq_finish_unit(const uint4 (&raw_in)[NV], float 
   uint4 raw[NV];
 #pragma unroll
   for (int j = 0; j < NV; ++j) raw[j] = raw_in[j];
-  SpecD sp = sp_in;
-  {  // AutoClip v1: clamp the unit to its shrunk range first; everything below then sees the clamped tensor
+  const SpecD& sp = sp_in;
+  float mnc = mn, mxc = mx;
+  {  // AutoClip v1 (rare, uniform): clamp the unit to its shrunk range; the fast chains then see the clamped tensor.
+     // The literal path below gets the original vectors and range (qparams_from_range / fq_elem_literal clip themselves).
     float lo, hi;
-    if (clip_bounds(mn, mx, sp.clip, TI<T>::ID, lo, hi)) {
+    if (clip_bounds(mnc, mxc, sp.clip, TI<T>::ID, lo, hi)) {
 #pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        float f[VEC];
-        TI<T>::unpack(raw[j], f);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) f[i] = clamp_nan(f[i], lo, hi);
-        raw[j] = TI<T>::pack(f);
-      }
+      for (int j = 0; j < NV; ++j) raw[j] = clamp_vec_noinline<T>(raw[j], lo, hi);
     }
-    sp.clip = 1.0f;
   }
   UnitQ u;
-  qparams_unit<T>(mn, mx, sp, fs, u);
+  qparams_unit<T>(mnc, mxc, sp, fs, u);
   if (u.exact) {  // unit-uniform, rare: literal chain, qparams recomputed literally as well
     if (writer) write_qparams_literal(mn, mx, sp, scales, zeros, unit);
     if (sp.out_mode != LCB_OUT_NONE) {
 #pragma unroll
       for (int j = 0; j < NV; ++j)
-        if (v0 + j * vstride < nvec) quant_store_vec_literal<T>(raw[j], mn, mx, sp, out, e0 + (int64_t)j * vstride * VEC);
+        if (v0 + j * vstride < nvec) quant_store_vec_literal<T>(raw_in[j], mn, mx, sp, out, e0 + (int64_t)j * vstride * VEC);
     }
     return;
   }
