@@ -144,6 +144,33 @@ def _sq_act_scale(orig):
     return get_act_scale
 
 
+# ---- AutoClip (auto_clip.py) ----------------------------------------------------------------------------------------------
+def _autoclip_layer(orig):
+    def auto_clip_layer(self, block_idx, layer_name, w, inputs, n_grid=20, max_shrink=0.5, n_sample_token=512, eps=0.0):
+        wq = self.wquantizer
+        gs = wq.group_size if wq.granularity == 'per_group' else w.shape[1]
+        ok = (self.clip_version == 'v1' and self.w_only and len(inputs) == 1 and not self.padding_mask and w.dim() == 2
+              and type(wq).__name__ == 'IntegerQuantizer' and wq.granularity in ('per_group', 'per_channel')
+              and w.dtype in (torch.bfloat16, torch.float16) and inputs[0].dtype == w.dtype
+              and w.shape[1] % gs == 0 and gs % 64 == 0 and w.shape[0] % 64 == 0)
+        if not ok:
+            return orig(self, block_idx, layer_name, w, inputs, n_grid, max_shrink, n_sample_token, eps)
+        from .autoclip import auto_clip_layer as lcb_layer
+        x = inputs[0].to(w.device)
+        return lcb_layer(w.data if hasattr(w, 'data') else w, x, wq, self.clip_sym, n_grid, max_shrink, n_sample_token)
+    return auto_clip_layer
+
+
+def patch_autoclipper(cls):
+    """cls: llmc.compression.quantization.auto_clip.AutoClipper. Routes auto_clip_layer (v1, w_only) to
+    lcb_autoclip_search; anything else keeps the reference path. Returns True when newly patched."""
+    if getattr(cls, '_lcb_patched', False):
+        return False
+    cls.auto_clip_layer = _autoclip_layer(cls.auto_clip_layer)
+    cls._lcb_patched = True
+    return True
+
+
 def patch_reference(registry):
     """registry: llmc.utils.registry_factory.ALGO_REGISTRY (or any dict name -> class). Returns the patched names."""
     done = []

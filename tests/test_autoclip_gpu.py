@@ -105,3 +105,27 @@ def test_autoclip_rejects_unsupported():
         ops.autoclip_search(W, x, wq, False)            # group of 32 < one 64-deep K block: no kernel, no fallback
     with pytest.raises(RuntimeError):
         ops.autoclip_search(W.cpu(), x.cpu(), Q.IntegerQuantizer(4, False, 'per_group', group_size=128), False)
+
+
+class _RefLikeAutoClipper(object):
+    """Attribute contract of auto_clip.py:21-42; the hot method raises unless patched."""
+
+    def __init__(self, wquantizer, clip_sym):
+        self.wquantizer, self.aquantizer = wquantizer, None
+        self.clip_version, self.clip_sym, self.w_only, self.padding_mask = 'v1', clip_sym, True, None
+
+    def auto_clip_layer(self, block_idx, layer_name, w, inputs, n_grid=20, max_shrink=0.5, n_sample_token=512, eps=0.0):
+        raise AssertionError('reference path taken')
+
+
+def test_patch_autoclipper_contract():
+    from lightcompress_b200.algo import patch_autoclipper
+    assert patch_autoclipper(_RefLikeAutoClipper) and not patch_autoclipper(_RefLikeAutoClipper)
+    c = GOLD[0]['case']
+    W, x = inputs(c)
+    wq = Q.IntegerQuantizer(c['bit'], c['sym'], 'per_group', group_size=c['gs'])
+    ac = _RefLikeAutoClipper(wq, c['clip_sym'])
+    bmax, bmin = ac.auto_clip_layer(0, 'fc', W.to(DEV), [x.to(DEV)], n_sample_token=c['tok'])
+    assert bmax.shape == GOLD[0]['best_max'].shape and bmax.dtype == W.dtype
+    same = (bmax.cpu().view(torch.int16) == GOLD[0]['best_max'].view(torch.int16))
+    assert float(same.float().mean()) >= 0.85
