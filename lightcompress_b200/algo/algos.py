@@ -5,7 +5,7 @@ import torch.nn as nn
 from .. import ops
 from . import awq as lcawq
 from .blockwise import ALGO_REGISTRY, BaseBlockwiseQuantization
-from .gptq import GPTQLayer
+from .gptq import GPTQLayer, HessianState
 
 
 @ALGO_REGISTRY
@@ -24,19 +24,41 @@ class GPTQ(BaseBlockwiseQuantization):
         self.layers_cache = {}
         self.qparams = {}     # module -> (scales [R*C/g, 1], zeros) for deploy (update_model_qparams, gptq.py:398-409)
 
-    def _new_layer(self, m):
-        return GPTQLayer(m.weight, self.wquantizer, self.blocksize, self.percdamp, self.actorder, self.static_groups)
+    def _new_layer(self, m, hessian=None):
+        return GPTQLayer(m.weight, self.wquantizer, self.blocksize, self.percdamp, self.actorder, self.static_groups,
+                         hessian=hessian)
 
     def block_init(self, block):                       # gptq.py:318-322
         self.named_layers = self.model.get_block_linears(block)
-        self.layers_cache = {n: self._new_layer(m) for n, m in self.named_layers.items()}
+        self.layers_cache, self.hessian_owner = {}, {}
+        subsets = self.model.get_subsets_in_block(block)
+        for i, subset in enumerate(subsets):
+            self.subset_init(subset)
+            if self.true_sequential and i > 0:
+                # the reference accumulates these in the first forward too and throws them away when the subset is
+                # re-hooked after its predecessors were quantized (gptq.py:311-315, base_bq.py:505-526): skip the work
+                for n in subset['layers']:
+                    self.hessian_owner[n] = False
+        for n, m in self.named_layers.items():
+            if n not in self.layers_cache:
+                self.layers_cache[n] = self._new_layer(m)
+                self.hessian_owner[n] = True
 
     def subset_init(self, subset):                     # gptq.py:311-315: the next subset's Hessians start over
+        # The linears of one subset read the same input (subset['input'], models/llama.py:30-75), so their Hessians and
+        # inverse factors are identical: one HessianState per (subset, in_features) is accumulated by its first linear
+        # and factorised once. `share_hessian: False` in `special` restores one state per linear.
+        shared = {}
         for n, m in subset['layers'].items():
-            self.layers_cache[n] = self._new_layer(m)
+            key = m.weight.shape[1] if self.special.get('share_hessian', True) else n
+            first = key not in shared
+            if first:
+                shared[key] = HessianState(m.weight.shape[1], m.weight.device)
+            self.layers_cache[n] = self._new_layer(m, shared[key])
+            self.hessian_owner[n] = first
 
     def cache_input_hook(self, m, x, y, name, feat_dict):   # gptq.py:247-251: accumulate, do not keep the input
-        if name in self.layers_cache:
+        if name in self.layers_cache and self.hessian_owner.get(name, True):
             self.layers_cache[name].add_batch(x[0].detach())
 
     @torch.no_grad()

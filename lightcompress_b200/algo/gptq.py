@@ -11,25 +11,18 @@ from .. import ops
 from . import dist as lcdist
 
 
-class GPTQLayer(object):
-    def __init__(self, weight, wquantizer, blocksize=128, percdamp=0.01, actorder=False, static_groups=False):
-        if not weight.is_cuda:
-            raise RuntimeError('GPTQLayer: weight must live on a CUDA device (no CPU path)')
-        self.weight = weight
-        self.wquantizer = wquantizer
-        self.blocksize = blocksize
-        self.percdamp = percdamp
-        self.actorder = actorder
-        self.static_groups = static_groups
-        self.rows, self.columns = weight.shape[0], weight.shape[1]
-        # layer_init (gptq.py:297-309): H zeros, nsamples 0. Here H is the UN-NORMALISED sum until finalize().
-        self.S = torch.zeros((self.columns, self.columns), dtype=torch.float32, device=weight.device)
+class HessianState(object):
+    """Running Hessian of one layer INPUT and its damped inverse factor. Linears that see the same input (q/k/v, gate/up:
+    one `subset` of the reference, models/llama.py) may share one state: the reference accumulates and factorises an
+    identical H once per linear (gptq.py:254-295, 128-176); sharing is the same arithmetic done once."""
+
+    def __init__(self, columns, device):
+        self.columns = columns
+        # layer_init (gptq.py:297-309): H zeros, nsamples 0. Here S is the UN-NORMALISED sum until finalize().
+        self.S = torch.zeros((columns, columns), dtype=torch.float32, device=device)
         self.nsamples = 0
         self.H = None
-        self.scales = self.zeros = None
-        self.losses = None
-        self.perm = self.invperm = None
-        self.chol_splits = 3   # bf16 pieces per fp32 operand in the factorisation GEMMs (3 = fp32-class accuracy)
+        self._factor = None     # (key, dead, perm, Hinv)
 
     @torch.no_grad()
     def add_batch(self, inp):
@@ -42,36 +35,76 @@ class GPTQLayer(object):
     @torch.no_grad()
     def finalize(self):
         """One all-reduce of (S, nsamples) over the ranks, then H = (2 / n) * sym(S)."""
-        n = lcdist.allreduce_hessian(self.S, self.nsamples)
-        self.nsamples = n
-        self.H = ops.hessian_finalize(self.S, n)
-        self.S = None
+        if self.H is None:
+            n = lcdist.allreduce_hessian(self.S, self.nsamples)
+            self.nsamples = n
+            self.H = ops.hessian_finalize(self.S, n)
+            self.S = None
         return self.H
+
+    @torch.no_grad()
+    def factor(self, percdamp, actorder, splits):
+        """gptq.py:143-174 without the weight: dead columns, act-order permutation, damping, Cholesky-inverse upper
+        factor (ops.cholinv_upper: SURVEY.md §8f N1; raises torch.linalg.LinAlgError like torch.linalg.cholesky).
+        Returns (dead mask, perm | None, Hinv); computed once per (percdamp, actorder)."""
+        key = (float(percdamp), bool(actorder), int(splits))
+        if self._factor is not None and self._factor[0] == key:
+            return self._factor[1:]
+        H = self.finalize()
+        dead = torch.diag(H) == 0
+        H[dead, dead] = 1
+        perm = None
+        if actorder:
+            perm = torch.argsort(torch.diag(H), descending=True)
+            H = H[perm][:, perm]
+        Hinv = ops.cholinv_upper(H.contiguous(), percdamp, splits=splits)
+        self.H = None
+        self._factor = (key, dead, perm, Hinv)
+        return dead, perm, Hinv
+
+
+class GPTQLayer(object):
+    def __init__(self, weight, wquantizer, blocksize=128, percdamp=0.01, actorder=False, static_groups=False, hessian=None):
+        if not weight.is_cuda:
+            raise RuntimeError('GPTQLayer: weight must live on a CUDA device (no CPU path)')
+        self.weight = weight
+        self.wquantizer = wquantizer
+        self.blocksize = blocksize
+        self.percdamp = percdamp
+        self.actorder = actorder
+        self.static_groups = static_groups
+        self.rows, self.columns = weight.shape[0], weight.shape[1]
+        self.hessian = hessian if hessian is not None else HessianState(self.columns, weight.device)
+        assert self.hessian.columns == self.columns
+        self.scales = self.zeros = None
+        self.losses = None
+        self.perm = self.invperm = None
+        self.chol_splits = 3   # bf16 pieces per fp32 operand in the factorisation GEMMs (3 = fp32-class accuracy)
+
+    # the Hessian-side state, kept reachable under the reference's names
+    S = property(lambda self: self.hessian.S)
+    H = property(lambda self: self.hessian.H)
+    nsamples = property(lambda self: self.hessian.nsamples)
+
+    def add_batch(self, inp):
+        self.hessian.add_batch(inp)
+
+    def finalize(self):
+        return self.hessian.finalize()
 
     def _qrange(self):
         return self.wquantizer._qrange()
 
     @torch.no_grad()
     def process_hessian_and_weights(self):
-        """gptq.py:128-176: dead columns, optional act-order permutation, damping, Cholesky inverse upper factor.
-        Damping and the three factorisations (gptq.py:165-174) are one call of ops.cholinv_upper (blocked reverse
-        Cholesky + triangular inverse on tcgen05); it raises torch.linalg.LinAlgError like
-        torch.linalg.cholesky when the damped Hessian is not positive definite."""
-        if self.H is None:
-            self.finalize()
-        H = self.H
+        """gptq.py:128-176: dead columns, optional act-order permutation, damping, Cholesky inverse upper factor."""
+        dead, self.perm, Hinv = self.hessian.factor(self.percdamp, self.actorder, self.chol_splits)
         W = self.weight.data.clone().float()
-        dead = torch.diag(H) == 0
-        H[dead, dead] = 1
         W[:, dead] = 0
         if self.actorder:
-            self.perm = torch.argsort(torch.diag(H), descending=True)
             W = W[:, self.perm].contiguous()
-            H = H[self.perm][:, self.perm]
             self.invperm = torch.argsort(self.perm)
-        H = ops.cholinv_upper(H.contiguous(), self.percdamp, splits=self.chol_splits)
-        self.H = None
-        return W, H
+        return W, Hinv
 
     @torch.no_grad()
     def quantize(self, static_scales=None, static_zeros=None):
