@@ -47,6 +47,8 @@ extern "C" {
 #define LCB_OUT_FP8 4    /* fp8 byte (e4m3fn / e5m2) (FloatQuantizer.real_quant_*)     */
 #define LCB_OUT_NONE 5   /* nothing: qparams only  (get_tensor_qparams)                */
 #define LCB_OUT_CODE_T 6 /* integer code kept in the math dtype (IntegerQuantizer.quant) */
+#define LCB_OUT_DEQUANT 7 /* `in` holds codes in the math dtype; out = (q - z) * s (IntegerQuantizer.dequant, quant.py:710-712);
+                             static calls only */
 
 /*
  * Quantizer description. Mirrors the ctor kwargs of BaseQuantizer/IntegerQuantizer/
@@ -98,6 +100,22 @@ int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t 
                   void* workspace, void* stream);
 
 int64_t lcb_fakequant_workspace_bytes(void);
+
+/*
+ * Range of every quantization unit (same unit grid as lcb_fakequant): mins / maxs receive amin / amax over the unit in
+ * `range_dtype` (the tensor dtype; LCB_F32 with abs_range != 0 = per_block, which ranges |x|.float() and counts the zero
+ * padding of ragged edge blocks, quant.py:137-138, 637-638). Replaces get_minmax_range (quant.py:132-143).
+ */
+int lcb_minmax(const void* in, void* mins, void* maxs, int64_t rows, int64_t cols, int64_t unit_rows, int64_t unit_cols,
+               int32_t dtype, int32_t range_dtype, int32_t abs_range, void* stream);
+
+/*
+ * scales / zeros of n units from given (min, max) ranges: get_qparams (quant.py:545-559) for ranges that were modified
+ * after the search (learnable bounds `sigmoid(f) * min / max`, quant.py:205-219; AutoClip v2, static calibration).
+ * mins / maxs in spec->math_dtype, scales / zeros in spec->qparam_dtype; zeros may be NULL when spec->sym.
+ */
+int lcb_qparams_from_range(const void* mins, const void* maxs, void* scales, void* zeros, int64_t n,
+                           const lcb_quant_spec* spec, void* stream);
 
 /*
  * Dynamic fake-quant (LCB_OUT_FAKE, IntegerQuantizer, units of 1 x unit_cols with unit_cols * sizeof(dtype) <= 1 KiB)

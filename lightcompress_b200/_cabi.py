@@ -10,7 +10,7 @@ from . import _build
 
 LCB_F32, LCB_F16, LCB_BF16 = 0, 1, 2
 KIND_INT, KIND_FP8_E4M3, KIND_FP8_E5M2 = 0, 1, 2
-OUT_FAKE, OUT_I8, OUT_U8, OUT_I32, OUT_FP8, OUT_NONE, OUT_CODE_T = range(7)
+OUT_FAKE, OUT_I8, OUT_U8, OUT_I32, OUT_FP8, OUT_NONE, OUT_CODE_T, OUT_DEQUANT = range(8)
 
 _c_i64, _c_i32, _c_vp, _c_f = ctypes.c_int64, ctypes.c_int32, ctypes.c_void_p, ctypes.c_float
 
@@ -30,6 +30,8 @@ SIGNATURES = {
     'lcb_fakequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64,
                                      ctypes.POINTER(QuantSpec), ctypes.c_int, _c_vp, _c_vp]),
     'lcb_fakequant_workspace_bytes': (_c_i64, []),
+    'lcb_minmax': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp]),
+    'lcb_qparams_from_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_fakequant_multi': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i32, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp, _c_vp]),

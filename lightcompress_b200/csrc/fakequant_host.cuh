@@ -173,7 +173,7 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
 
   if (!dynamic) {
     if (!scales) return LCB_E_INVALID;
-    if (vec_ok && (math_is_T || sp.math_dtype == LCB_F32)) {
+    if (vec_ok && (math_is_T || sp.math_dtype == LCB_F32) && sp.out_mode != LCB_OUT_DEQUANT) {
       LCB_KIND_SWITCH(return launch_static<T, KINDC>(in, out, scales, zeros, rows, cols, ur, uc, sp, st));
     }
     int64_t units = ((rows + ur - 1) / ur) * ((cols + uc - 1) / uc);
@@ -307,9 +307,11 @@ extern "C" int lcb_fakequant(const void* in, void* out, void* scales, void* zero
   if (spec->dtype < LCB_F32 || spec->dtype > LCB_BF16 || spec->math_dtype < LCB_F32 || spec->math_dtype > LCB_BF16 ||
       spec->qparam_dtype < LCB_F32 || spec->qparam_dtype > LCB_BF16)
     return LCB_E_UNSUPPORTED;
-  if (spec->out_mode < LCB_OUT_FAKE || spec->out_mode > LCB_OUT_CODE_T) return LCB_E_UNSUPPORTED;
+  if (spec->out_mode < LCB_OUT_FAKE || spec->out_mode > LCB_OUT_DEQUANT) return LCB_E_UNSUPPORTED;
+  if (spec->out_mode == LCB_OUT_DEQUANT && dynamic) return LCB_E_INVALID;
   if (spec->kind != LCB_KIND_INT && !(spec->out_mode == LCB_OUT_FAKE || spec->out_mode == LCB_OUT_FP8 ||
-                                      spec->out_mode == LCB_OUT_NONE || spec->out_mode == LCB_OUT_CODE_T))
+                                      spec->out_mode == LCB_OUT_NONE || spec->out_mode == LCB_OUT_CODE_T ||
+                                      spec->out_mode == LCB_OUT_DEQUANT))
     return LCB_E_INVALID;
   if (spec->kind == LCB_KIND_INT && spec->out_mode == LCB_OUT_FP8) return LCB_E_INVALID;
   if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;

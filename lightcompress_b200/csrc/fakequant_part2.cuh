@@ -105,6 +105,7 @@ __global__ void __launch_bounds__(256)
 template <typename T>
 __device__ __forceinline__ void store_scalar(void* out, int64_t e, float val, float code, const SpecD& sp) {
   switch (sp.out_mode) {
+    case LCB_OUT_DEQUANT:
     case LCB_OUT_FAKE: TI<T>::store1(reinterpret_cast<T*>(out) + e, val); break;
     case LCB_OUT_CODE_T: TI<T>::store1(reinterpret_cast<T*>(out) + e, code); break;
     case LCB_OUT_I8: reinterpret_cast<int8_t*>(out)[e] = (int8_t)(int)code; break;
@@ -219,3 +220,87 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace lcb
 #include "fakequant_host.cuh"
+
+namespace lcb {
+// ---- get_minmax_range (quant.py:132-143): warp per unit -------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+    minmax_units_kernel(const T* __restrict__ in, void* __restrict__ mins, void* __restrict__ maxs, int64_t rows, int64_t cols,
+                        int64_t ur, int64_t uc, int range_dtype, int abs_range) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t nru = (rows + ur - 1) / ur, ncu = (cols + uc - 1) / uc;
+  for (int64_t unit = warp; unit < nru * ncu; unit += nwarps) {
+    const int64_t r0 = (unit / ncu) * ur, c0 = (unit % ncu) * uc;
+    const int64_t nr = min(ur, rows - r0), nc = min(uc, cols - c0);
+    float mx = -INFINITY, mn = INFINITY;
+    for (int64_t i = lane; i < nr * nc; i += 32) {
+      float x = TI<T>::load1(in + (r0 + i / nc) * cols + c0 + i % nc);
+      if (abs_range) x = fabsf(x);
+      mx = max_nan(mx, x);
+      mn = min_nan(mn, x);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    }
+    if (abs_range && (nr < ur || nc < uc)) mn = min_nan(mn, 0.f);  // zero padding (quant.py:637-638)
+    if (lane == 0) {
+      store_rt(mins, unit, mn, range_dtype);
+      store_rt(maxs, unit, mx, range_dtype);
+    }
+  }
+}
+
+// ---- get_qparams (quant.py:545-559) on given ranges: thread per unit, literal arithmetic --------------------------------
+__global__ void __launch_bounds__(256)
+    qparams_from_range_kernel(const void* __restrict__ mins, const void* __restrict__ maxs, void* __restrict__ scales,
+                              void* __restrict__ zeros, int64_t n, SpecD sp) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  sp.fast_ok = 0;
+  UnitQ u;
+  qparams_from_range(load_rt(mins, i, sp.math_dtype), load_rt(maxs, i, sp.math_dtype), sp, u);
+  finish_unit(sp, u);
+  write_qparams(scales, zeros, i, u, sp);
+}
+}  // namespace lcb
+
+extern "C" int lcb_minmax(const void* in, void* mins, void* maxs, int64_t rows, int64_t cols, int64_t unit_rows,
+                          int64_t unit_cols, int32_t dtype, int32_t range_dtype, int32_t abs_range, void* stream) {
+  using namespace lcb;
+  if (!in || !mins || !maxs || rows < 0 || cols < 0 || unit_rows < 1 || unit_cols < 1) return LCB_E_INVALID;
+  if (dtype < LCB_F32 || dtype > LCB_BF16 || range_dtype < LCB_F32 || range_dtype > LCB_BF16) return LCB_E_UNSUPPORTED;
+  if (rows == 0 || cols == 0) return LCB_OK;
+  if (unit_rows == 1 && unit_cols < cols && cols % unit_cols != 0) return LCB_E_SHAPE;
+  const int64_t ur = unit_rows > rows ? rows : unit_rows, uc = unit_cols > cols ? cols : unit_cols;
+  const int64_t units = ((rows + ur - 1) / ur) * ((cols + uc - 1) / uc);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = grid_for((units + 7) / 8, 8);
+  if (dtype == LCB_F32)
+    minmax_units_kernel<float><<<grid, 256, 0, st>>>((const float*)in, mins, maxs, rows, cols, ur, uc, range_dtype, abs_range);
+  else if (dtype == LCB_F16)
+    minmax_units_kernel<__half><<<grid, 256, 0, st>>>((const __half*)in, mins, maxs, rows, cols, ur, uc, range_dtype, abs_range);
+  else
+    minmax_units_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)in, mins, maxs, rows, cols, ur, uc, range_dtype,
+                                                             abs_range);
+  LCB_CUDA_CHECK_LAUNCH("minmax_units");
+  return LCB_OK;
+}
+
+extern "C" int lcb_qparams_from_range(const void* mins, const void* maxs, void* scales, void* zeros, int64_t n,
+                                      const lcb_quant_spec* spec, void* stream) {
+  using namespace lcb;
+  if (!mins || !maxs || !scales || !spec || n < 0) return LCB_E_INVALID;
+  if (spec->kind < LCB_KIND_INT || spec->kind > LCB_KIND_FP8_E5M2) return LCB_E_UNSUPPORTED;
+  if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  if (n == 0) return LCB_OK;
+  SpecD sp = make_specd(spec);
+  sp.out_mode = LCB_OUT_NONE;
+  sp.clip = 1.0f;
+  qparams_from_range_kernel<<<(int)((n + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(mins, maxs, scales, zeros, n, sp);
+  LCB_CUDA_CHECK_LAUNCH("qparams_from_range");
+  return LCB_OK;
+}

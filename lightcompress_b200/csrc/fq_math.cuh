@@ -102,6 +102,10 @@ __device__ __forceinline__ void finish_unit(const SpecD& sp, UnitQ& u) {
 static __device__ __noinline__ float2 fq_elem_literal(float x, const UnitQ& u, const SpecD& sp) {
   const int md = sp.math_dtype;
   if (u.clipped) x = clamp_nan(x, u.clo, u.chi);
+  if (sp.out_mode == LCB_OUT_DEQUANT) {   // x is a code: (q - z) * s   (quant.py:710-712 / 1076-1078)
+    const float t4 = sp.kind == LCB_KIND_INT ? rd_rt(__fsub_rn(x, u.z), md) : x;
+    return make_float2(rd_rt(__fmul_rn(t4, u.s_out), md), x);
+  }
   if (sp.kind == LCB_KIND_INT) {
     float q;
     if (sp.round_zp) {

@@ -279,14 +279,79 @@ class BaseQuantizer(object):
     # ---- reference API ------------------------------------------------------------------------------
     def get_tensor_qparams(self, tensor, args={}):
         """quant.py:690-697 / :1043-1059 → (reshaped_tensor, scales, zeros, qmax, qmin)."""
+        dev = tensor.device
+        if self.calib_algo == 'learnable':   # range -> sigmoid bounds -> qparams (quant.py:119-130, 205-219)
+            t = self.reshape_tensor(tensor)
+            rng = self.get_learnable_range(tensor, **{k: v for k, v in args.items()
+                                                      if k in ('lowbound_factor', 'upbound_factor')})
+            scales, zeros, qmax, qmin = self.get_qparams(rng, dev)
+            return t, scales, zeros, qmax, qmin
         _, scales, zeros, = self._dynamic(tensor, _cabi.OUT_NONE, None, True)
         if zeros is None:
             zeros = torch.tensor(0.0)
-        dev = tensor.device
         return self.reshape_tensor(tensor), scales, zeros, self.qmax.to(dev), self.qmin.to(dev)
 
     def get_minmax_range(self, tensor):
-        raise NotImplementedError('use get_tensor_qparams (range + qparams are fused in one kernel)')
+        """quant.py:132-143: (min_val, max_val) of every unit — per_block: of |t|.float() (fp32, zero padding counted);
+        otherwise amin / amax in the tensor dtype, shaped [units, 1] (per_tensor: 0-dim). Accepts the tensor in its
+        original or in its reshape_tensor() layout (lcb_minmax)."""
+        _require_cuda(tensor, 'get_minmax_range')
+        x = tensor.contiguous()
+        if self.granularity == 'per_block' and x.dim() == 4:
+            raise NotImplementedError('4-D per_block views: pass the 2-D weight')
+        u = self._units(x)
+        per_block = self.granularity == 'per_block'
+        rd = torch.float32 if per_block else x.dtype
+        mins = torch.empty(u.qshape, dtype=rd, device=x.device)
+        maxs = torch.empty(u.qshape, dtype=rd, device=x.device)
+        lib = _cabi.load()
+        with _on_device(x.device):
+            st = lib.lcb_minmax(x.data_ptr(), mins.data_ptr(), maxs.data_ptr(), u.rows, u.cols, u.ur, u.uc, _DT[x.dtype],
+                                _DT[rd], 1 if per_block else 0, _stream(x.device.index))
+        _cabi.check(st, 'lcb_minmax')
+        return mins, maxs
+
+    def get_learnable_range(self, tensor, lowbound_factor=None, upbound_factor=None):
+        """quant.py:205-219: the min/max search on the GPU kernel, the sigmoid bounds on the [units, 1] results."""
+        min_val, max_val = self.get_minmax_range(tensor)
+        if self.sym:
+            if upbound_factor is not None:
+                abs_max = torch.max(max_val.abs(), min_val.abs()).clamp(min=1e-5)
+                abs_max = torch.sigmoid(upbound_factor) * abs_max
+                min_val, max_val = -abs_max, abs_max
+        elif upbound_factor is not None and lowbound_factor is not None:
+            min_val = torch.sigmoid(lowbound_factor) * min_val
+            max_val = torch.sigmoid(upbound_factor) * max_val
+        return min_val, max_val
+
+    def get_tensor_range(self, tensor, args={}):
+        """quant.py:119-130."""
+        if self.calib_algo == 'learnable':
+            return self.get_learnable_range(tensor, **args)
+        if self.calib_algo == 'mse':
+            raise NotImplementedError('calib_algo=mse is not on the CUDA hot path')
+        return self.get_minmax_range(tensor)
+
+    def get_qparams(self, tensor_range, device):
+        """quant.py:545-559 on given ranges (lcb_qparams_from_range) → (scales, zeros, qmax, qmin)."""
+        min_val, max_val = tensor_range[0], tensor_range[1]
+        _require_cuda(min_val, 'get_qparams')
+        md = _promote(min_val.dtype, max_val.dtype)
+        mn, mx = min_val.to(md).contiguous(), max_val.to(md).contiguous()
+        qd = md
+        if mn.dim() == 0 and (self._kind() != _cabi.KIND_INT or not self.sym):
+            qd = torch.float32      # 0-dim range / 0-dim float divisor promotes (quant.py:552-556)
+        qmin, qmax = self._qrange()
+        spec = self._spec(md, md, qd, _cabi.OUT_NONE, qmin, qmax, 1.0, 1.0, _DT[qd] + 1)
+        scales = torch.empty(mn.shape, dtype=qd, device=mn.device)
+        asym = not self.sym and self._kind() == _cabi.KIND_INT
+        zeros = torch.empty(mn.shape, dtype=qd, device=mn.device) if asym else None
+        lib = _cabi.load()
+        with _on_device(mn.device):
+            st = lib.lcb_qparams_from_range(mn.data_ptr(), mx.data_ptr(), scales.data_ptr(),
+                                            zeros.data_ptr() if asym else None, mn.numel(), spec, _stream(mn.device.index))
+        _cabi.check(st, 'lcb_qparams_from_range')
+        return scales, (zeros if asym else torch.tensor(0.0)), self.qmax.to(device), self.qmin.to(device)
 
     def _bcast_units(self, tensor, scales):
         """units for direct quant()/dequant()/quant_dequant() calls on already reshaped tensors."""
@@ -340,6 +405,9 @@ class BaseQuantizer(object):
                 mix = tensor.clone()
                 mix.index_copy_(dim, torch.as_tensor(args['int_indices'], device=tensor.device), q)
                 return mix
+            if self.calib_algo == 'learnable':   # AWQ clip v2 deploy (base_bq.py:46-65): bounds from the module buffers
+                _, sc, zp, qmax, qmin = self.get_tensor_qparams(tensor, args)
+                return self._static(tensor, sc, zp, qmax, qmin, _cabi.OUT_FAKE, tensor.dtype)
             if is_weight and 'dim' in args and 'ic' in args['dim']:
                 q, _, _ = self._dynamic(tensor.T, _cabi.OUT_FAKE, tensor.dtype, False)
                 return q.T
@@ -464,7 +532,10 @@ class IntegerQuantizer(BaseQuantizer):
         self.qmax = torch.tensor(hi)
 
     def dequant(self, tensor, scales, zeros):
-        raise NotImplementedError('dequant alone is not a hot-path entry; use quant_dequant / fake_quant_*')
+        """quant.py:710-712: (codes - zeros) * scales on a reshaped [units, unit_len] tensor of codes."""
+        md = _promote(tensor.dtype, *([scales.dtype] if torch.is_tensor(scales) and scales.dim() > 0 else []))
+        x = tensor if md == tensor.dtype else tensor.to(md)
+        return self._static(x, scales, zeros, None, None, _cabi.OUT_DEQUANT, x.dtype, units=self._bcast_units(x, scales))
 
     def _code_dtype(self):
         # quant.py:929-936: bit 8 -> int8 (uint8 when qmin == 0); anything else -> unpacked int32
