@@ -241,6 +241,18 @@ int lcb_autoclip_search(const void* W, const void* x, void* best_max, void* best
                         const lcb_quant_spec* spec, void* workspace, void* stream);
 int64_t lcb_autoclip_workspace_bytes(int64_t R, int64_t C, int64_t T_rows, int64_t group_size);
 
+/*
+ * Real-quant export packers (the reference packs with numpy on the host / a Python loop per column).
+ * lcb_pack_rows: VllmRealQuantLinear.pack (module_utils.py:931-955): codes [rows, cols] (int8 or int32, code_bytes = 1 | 4)
+ *   -> out int32 [rows, ceil(cols / (32 / bit))], code + 2^(bit-1) as unsigned in bits [bit i, bit i + bit) of word col / pf.
+ * lcb_awq_gemm_pack: AutoawqRealQuantLinear.gemm_pack (module_utils.py:1099-1158), 4 bit: W [R, C] (dtype), scales fp16
+ *   [C / group, R], zeros int32 [C / group, R] -> qweight int32 [C, R / 8], qzeros int32 [C / group, R / 8], nibble
+ *   order 0 2 4 6 1 3 5 7; intweight = round((w + zeros * scales) / scales) in torch's promoted dtype.
+ */
+int lcb_pack_rows(const void* codes, int32_t* out, int64_t rows, int64_t cols, int32_t code_bytes, int32_t bit, void* stream);
+int lcb_awq_gemm_pack(const void* W, const void* scales, const int32_t* zeros, int32_t* qweight, int32_t* qzeros, int64_t R,
+                      int64_t C, int32_t group_size, int32_t dtype, void* stream);
+
 /* column absmax of a [rows, cols] matrix -> fp32 [cols] (running max: out = max(out, colmax)).
  * Replaces SmoothQuant.get_act_scale / get_weight_scale (smoothquant.py:27-51) and the |x| reductions
  * of Awq.get_act_scale (awq.py:74-85) when mean != 0 (then it is a column |x| sum). */
