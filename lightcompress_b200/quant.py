@@ -212,7 +212,7 @@ class BaseQuantizer(object):
             c = self.__dict__['_qrange_cache'] = (self.qmin, self.qmax, float(self.qmin), float(self.qmax))
         return c[2], c[3]
 
-    def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0):
+    def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0, out=None):
         """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
         _require_cuda(tensor, 'dynamic quant')
         if self.calib_algo not in ('minmax',):
@@ -229,6 +229,8 @@ class BaseQuantizer(object):
         spec = self._spec(x.dtype, md, qd, out_mode, qmin, qmax, osf, clip, _DT[qd] + 1)
         if out_mode == _cabi.OUT_NONE:
             out = None
+        elif out is not None:
+            assert out.is_contiguous() and out.shape == x.shape and out.dtype == out_dtype and out.device == x.device
         elif out_dtype == x.dtype:
             out = torch.empty_like(x)
         else:
