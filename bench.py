@@ -150,6 +150,66 @@ def extras(torch, dev, tf_peak):
     return res
 
 
+def sharded_extras(torch, dist, dev, world, rank):
+    """N > 1, every rank participates: the sharded tensor paths of SURVEY.md §8e at Llama-3-8B shapes.
+    Hessian: the 128 x 2048 calibration tokens of one linear input are split over the ranks, every rank accumulates its
+    shard into its own S (tcgen05 SYRK), ONE all-reduce of S over NCCL, then the finalize kernel — checked against the
+    batch count. AWQ: the 20 grid candidates of a 4096 x 4096 linear are split over the ranks (n = rank mod world), the
+    argmin is reduced. Times are device times, max over ranks."""
+    from lightcompress_b200 import ops
+    from lightcompress_b200.algo import dist as lcdist
+    from lightcompress_b200.quant import IntegerQuantizer
+    res = {}
+
+    def timed(fn):
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([a.elapsed_time(b)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), out
+
+    T, batches = 2048, 128
+    for C in (4096, 14336):
+        g = torch.Generator(device=dev).manual_seed(100 + rank)
+        xs = [torch.randn(T, C, device=dev, generator=g).to(torch.bfloat16) for _ in range(2)]
+        mine = len(range(rank, batches, world))
+
+        def hess():
+            S = torch.zeros(C, C, device=dev)
+            for i in range(mine):
+                ops.hessian_accum(S, xs[i & 1])
+            n = lcdist.allreduce_hessian(S, mine)
+            return ops.hessian_finalize(S, n), n
+        hess()
+        ms, (H, n) = timed(hess)
+        res[f'hessian_C{C}'] = {'ms': ms, 'batches_total': int(n), 'batches_per_rank': mine,
+                                'gemm_equiv_TFLOPs_aggregate': 2.0 * T * batches * C * C / (ms * 1e-3) / 1e12}
+        assert int(n) == batches
+        del H, xs
+        torch.cuda.empty_cache()
+    C, T = 4096, 8192
+    g = torch.Generator(device=dev).manual_seed(7)      # identical data on every rank
+    x = torch.randn(T, C, device=dev, generator=g).to(torch.bfloat16)
+    W = (torch.randn(C, C, device=dev, generator=g) * 0.02).to(torch.bfloat16)
+    org = torch.nn.functional.linear(x, W)
+    cand = (torch.rand(20, C, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    wq = IntegerQuantizer(4, False, 'per_group', group_size=128)
+    idx = lcdist.shard_candidates(20)
+
+    def awq():
+        losses = ops.awq_candidates(W, x, org, cand[idx], wq)
+        return lcdist.argmin_across_ranks([float(v) for v in losses.tolist()], idx, dev)
+    awq()
+    ms, (best_l, best_i) = timed(awq)
+    res['awq_20_candidates'] = {'ms': ms, 'candidates_per_rank': len(idx), 'best_index': int(best_i), 'T': T, 'R': C, 'C': C}
+    return res
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
@@ -298,6 +358,10 @@ def main():
         del ws, hin, hout
         torch.cuda.empty_cache()
         out['extras'].update(extras(torch, dev, tf_peak))
+    if world > 1 and not args.no_extras:
+        del ws, hin, hout
+        torch.cuda.empty_cache()
+        out['sharded'] = sharded_extras(torch, dist, dev, world, rank)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         out['cpu_baseline'] = cpu_baseline()[0]
     if rank == 0:
