@@ -202,6 +202,15 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
   if (vec_ok && sp.math_dtype == LCB_F32 && ur == 128 && uc == 128 && sp.sym) {
     int64_t tiles = ((rows + 127) / 128) * ((cols + 127) / 128);
     if (tiles > 0x7fffffff) return LCB_E_SHAPE;
+    if (kindc == 1 && sp.osf == 1.0f && (sp.out_mode == LCB_OUT_FAKE || sp.out_mode == LCB_OUT_FP8)) {
+      const bool e5 = sp.kind == LCB_KIND_FP8_E5M2, codes = sp.out_mode == LCB_OUT_FP8;
+      if (!e5 && !codes) fq_block2d_fp8_kernel<T, 0, 0><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
+      else if (!e5 && codes) fq_block2d_fp8_kernel<T, 0, 1><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
+      else if (e5 && !codes) fq_block2d_fp8_kernel<T, 1, 0><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
+      else fq_block2d_fp8_kernel<T, 1, 1><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
+      LCB_CUDA_CHECK_LAUNCH("fq_block2d_fp8");
+      return LCB_OK;
+    }
     LCB_KIND_SWITCH(fq_block2d_kernel<T, KINDC><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp));
     LCB_CUDA_CHECK_LAUNCH("fq_block2d");
     return LCB_OK;

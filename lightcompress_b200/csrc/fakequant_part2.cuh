@@ -100,6 +100,114 @@ __global__ void __launch_bounds__(256)
 }
 
 // ------------------------------------------------------------------------------------------------
+// per_block 128x128, FP8 (DeepSeek-style block-wise weight quant, quant.py:1061-1081 with fp32 math): compile-time format
+// and output, packed conversions. Per pair of elements: 2 x Markstein division (3 FP32 ops each), "+ 0" (-0 -> +0),
+// ONE cvt.rn.satfinite.e4m3x2.f32 (or e5m2x2), then either the two bytes are the real-quant code (LCB_OUT_FP8) or ONE
+// cvt.rn.f16x2.e4m3x2 brings them back for the dequant product (LCB_OUT_FAKE).
+// ------------------------------------------------------------------------------------------------
+template <int E5M2>
+__device__ __forceinline__ uint32_t f32x2_to_fp8x2(float lo, float hi) {   // byte 0 = fp8(lo), byte 1 = fp8(hi)
+  uint16_t r;
+  if (E5M2) asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+template <int E5M2>
+__device__ __forceinline__ float2 fp8x2_to_f32x2(uint32_t b) {
+  uint32_t h2;
+  const uint16_t s = (uint16_t)b;
+  if (E5M2) asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(h2) : "h"(s));
+  else asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"(s));
+  return __half22float2(*reinterpret_cast<const __half2*>(&h2));
+}
+template <typename T>
+__device__ __noinline__ void block_vec_slow(uint4 raw, UnitQ u, SpecD sp, void* out, int64_t e0) {
+  float f[TI<T>::VEC];
+  TI<T>::unpack(raw, f);
+  quant_store_vec<T, float, 1>(f, u, sp, out, e0);
+}
+
+template <typename T, int E5M2, int OUT_CODES>
+__global__ void __launch_bounds__(256)
+    fq_block2d_fp8_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, int64_t rows,
+                          int64_t cols, SpecD sp) {
+  constexpr int VEC = TI<T>::VEC;
+  constexpr int BS = 128;
+  constexpr int VPR = BS / VEC;        // vectors per tile row
+  constexpr int RPP = 256 / VPR;       // rows per pass
+  constexpr int NP = BS / RPP;         // passes
+  __shared__ float red[64];
+  const int64_t ncb = (cols + BS - 1) / BS;
+  const int64_t bi = blockIdx.x / ncb, bj = blockIdx.x % ncb;
+  const int vr = threadIdx.x / VPR, vc = threadIdx.x % VPR;
+  const int64_t col = bj * BS + vc * VEC;
+  uint4 raw[NP];
+  bool ok[NP];
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    const int64_t row = bi * BS + p * RPP + vr;
+    ok[p] = (row < rows) && (col < cols);
+    raw[p] = ok[p] ? ld_stream(in + row * cols + col) : make_uint4(0u, 0u, 0u, 0u);
+  }
+  float mx = 0.f;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    float f[VEC];
+    TI<T>::unpack(raw[p], f);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) mx = max_nan(mx, fabsf(f[i]));
+  }
+  float mn = mx;
+  block_minmax(mx, mn, red);
+  UnitQ u;
+  qparams_from_range(mx, mx, sp, u);
+  finish_unit(sp, u);
+  if (!finite_f(mx)) u.exact = 1;
+  if (threadIdx.x == 0 && scales) store_rt(scales, blockIdx.x, u.s_out, sp.qparam_dtype);
+  if (u.exact) {   // CTA-uniform, rare (non-finite range): the literal chain
+#pragma unroll 1
+    for (int p = 0; p < NP; ++p)
+      if (ok[p]) block_vec_slow<T>(raw[p], u, sp, out, (bi * BS + p * RPP + vr) * cols + col);
+    return;
+  }
+  const float s = u.s, r = u.r, so = u.s_out;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    if (!ok[p]) continue;
+    const int64_t e0 = (bi * BS + p * RPP + vr) * cols + col;
+    float f[VEC];
+    TI<T>::unpack(raw[p], f);
+    uint32_t b2[VEC / 2];
+#pragma unroll
+    for (int i = 0; i < VEC; i += 2) {
+      float q[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float q0 = __fmul_rn(f[i + k], r);
+        q[k] = __fadd_rn(__fmaf_rn(__fmaf_rn(-s, q0, f[i + k]), r, q0), 0.0f);   // RN(x / s), -0 -> +0
+      }
+      b2[i / 2] = f32x2_to_fp8x2<E5M2>(q[0], q[1]);
+    }
+    if (OUT_CODES) {
+      uint32_t w[VEC / 4];
+#pragma unroll
+      for (int i = 0; i < VEC / 4; ++i) w[i] = b2[2 * i] | (b2[2 * i + 1] << 16);
+      if (VEC == 8) *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(out) + e0) = make_uint2(w[0], w[VEC / 4 - 1]);
+      else *reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(out) + e0) = w[0];
+    } else {
+      float val[VEC];
+#pragma unroll
+      for (int i = 0; i < VEC; i += 2) {
+        const float2 v = fp8x2_to_f32x2<E5M2>(b2[i / 2]);
+        val[i] = __fmul_rn(v.x, so);
+        val[i + 1] = __fmul_rn(v.y, so);
+      }
+      st_stream(reinterpret_cast<T*>(out) + e0, TI<T>::pack(val));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // generic: warp per 2-D unit, scalar accesses, literal arithmetic. Any shape, any alignment, any spec.
 // ------------------------------------------------------------------------------------------------
 template <typename T>

@@ -42,7 +42,10 @@ def main():
         ('int4 sym g128 fp16', lambda: IntegerQuantizer(4, True, 'per_group', group_size=128), 'w16', 4096),
     ]
     sizes = [2 ** 22, 2 ** 24, 2 ** 26, 2 ** 28] if quick else [2 ** 20, 2 ** 22, 2 ** 24, 2 ** 26, 2 ** 28, 2 ** 30]
+    only = [a[7:] for a in sys.argv if a.startswith('--only=')]
     for name, mk, kind, cols in cases:
+        if only and not any(o in name for o in only):
+            continue
         q = mk()
         for numel in sizes:
             rows = max(1, numel // cols)
