@@ -105,9 +105,10 @@ int64_t lcb_fakequant_workspace_bytes(void);
  * Range of every quantization unit (same unit grid as lcb_fakequant): mins / maxs receive amin / amax over the unit in
  * `range_dtype` (the tensor dtype; LCB_F32 with abs_range != 0 = per_block, which ranges |x|.float() and counts the zero
  * padding of ragged edge blocks, quant.py:137-138, 637-638). Replaces get_minmax_range (quant.py:132-143).
+ * workspace: NULL or lcb_fakequant_workspace_bytes() bytes (lets a whole-tensor range use every SM).
  */
 int lcb_minmax(const void* in, void* mins, void* maxs, int64_t rows, int64_t cols, int64_t unit_rows, int64_t unit_cols,
-               int32_t dtype, int32_t range_dtype, int32_t abs_range, void* stream);
+               int32_t dtype, int32_t range_dtype, int32_t abs_range, void* workspace, void* stream);
 
 /*
  * scales / zeros of n units from given (min, max) ranges: get_qparams (quant.py:545-559) for ranges that were modified

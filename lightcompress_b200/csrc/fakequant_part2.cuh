@@ -362,6 +362,21 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// whole-tensor range, second stage: reduces the per-CTA (max, min) pairs of minmax_partial_kernel
+__global__ void __launch_bounds__(256) minmax_finalize_range_kernel(const float* ws, int nparts, void* mins, void* maxs, int range_dtype) {
+  __shared__ float red[64];
+  float mx = -INFINITY, mn = INFINITY;
+  for (int i = threadIdx.x; i < nparts; i += blockDim.x) {
+    mx = max_nan(mx, ws[2 * i]);
+    mn = min_nan(mn, ws[2 * i + 1]);
+  }
+  block_minmax(mx, mn, red);
+  if (threadIdx.x == 0) {
+    store_rt(mins, 0, mn, range_dtype);
+    store_rt(maxs, 0, mx, range_dtype);
+  }
+}
+
 // ---- get_qparams (quant.py:545-559) on given ranges: thread per unit, literal arithmetic --------------------------------
 __global__ void __launch_bounds__(256)
     qparams_from_range_kernel(const void* __restrict__ mins, const void* __restrict__ maxs, void* __restrict__ scales,
@@ -376,8 +391,19 @@ __global__ void __launch_bounds__(256)
 }
 }  // namespace lcb
 
+template <typename T>
+static int minmax_whole(const void* in, void* mins, void* maxs, int64_t numel, int range_dtype, float* ws, cudaStream_t st) {
+  using namespace lcb;
+  const int parts = grid_for((numel / TI<T>::VEC + 1023) / 1024, 8);
+  minmax_partial_kernel<T><<<parts, 256, 0, st>>>((const T*)in, numel, ws);
+  minmax_finalize_range_kernel<<<1, 256, 0, st>>>(ws, parts, mins, maxs, range_dtype);
+  LCB_CUDA_CHECK_LAUNCH("minmax_whole");
+  return LCB_OK;
+}
+
 extern "C" int lcb_minmax(const void* in, void* mins, void* maxs, int64_t rows, int64_t cols, int64_t unit_rows,
-                          int64_t unit_cols, int32_t dtype, int32_t range_dtype, int32_t abs_range, void* stream) {
+                          int64_t unit_cols, int32_t dtype, int32_t range_dtype, int32_t abs_range, void* workspace,
+                          void* stream) {
   using namespace lcb;
   if (!in || !mins || !maxs || rows < 0 || cols < 0 || unit_rows < 1 || unit_cols < 1) return LCB_E_INVALID;
   if (dtype < LCB_F32 || dtype > LCB_BF16 || range_dtype < LCB_F32 || range_dtype > LCB_BF16) return LCB_E_UNSUPPORTED;
@@ -386,6 +412,14 @@ extern "C" int lcb_minmax(const void* in, void* mins, void* maxs, int64_t rows, 
   const int64_t ur = unit_rows > rows ? rows : unit_rows, uc = unit_cols > cols ? cols : unit_cols;
   const int64_t units = ((rows + ur - 1) / ur) * ((cols + uc - 1) / uc);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int64_t numel = rows * cols;
+  const int vec = dtype == LCB_F32 ? 4 : 8;
+  if (units == 1 && !abs_range && workspace && numel >= 4096 && numel % vec == 0 && aligned16(in)) {   // per_tensor
+    float* ws = reinterpret_cast<float*>(workspace);
+    if (dtype == LCB_F32) return minmax_whole<float>(in, mins, maxs, numel, range_dtype, ws, st);
+    if (dtype == LCB_F16) return minmax_whole<__half>(in, mins, maxs, numel, range_dtype, ws, st);
+    return minmax_whole<__nv_bfloat16>(in, mins, maxs, numel, range_dtype, ws, st);
+  }
   const int grid = grid_for((units + 7) / 8, 8);
   if (dtype == LCB_F32)
     minmax_units_kernel<float><<<grid, 256, 0, st>>>((const float*)in, mins, maxs, rows, cols, ur, uc, range_dtype, abs_range);

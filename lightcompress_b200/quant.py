@@ -215,8 +215,8 @@ class BaseQuantizer(object):
     def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0, out=None):
         """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
         _require_cuda(tensor, 'dynamic quant')
-        if self.calib_algo not in ('minmax',):
-            raise NotImplementedError(f'calib_algo={self.calib_algo!r} is not on the CUDA hot path (minmax only)')
+        if self.calib_algo in ('mse', 'hqq'):   # every other value ranges by min/max here, as get_tensor_range does (quant.py:119-130)
+            raise NotImplementedError(f'calib_algo={self.calib_algo!r} is not on the CUDA hot path')
         x = tensor.contiguous()
         u = self._units(x)
         md = self._math_dtype_dynamic(x.dtype)
@@ -307,9 +307,13 @@ class BaseQuantizer(object):
         mins = torch.empty(u.qshape, dtype=rd, device=x.device)
         maxs = torch.empty(u.qshape, dtype=rd, device=x.device)
         lib = _cabi.load()
+        ws = None
+        if u.n_units == 1:
+            ws = torch.empty(int(lib.lcb_fakequant_workspace_bytes()), dtype=torch.uint8, device=x.device)
         with _on_device(x.device):
             st = lib.lcb_minmax(x.data_ptr(), mins.data_ptr(), maxs.data_ptr(), u.rows, u.cols, u.ur, u.uc, _DT[x.dtype],
-                                _DT[rd], 1 if per_block else 0, _stream(x.device.index))
+                                _DT[rd], 1 if per_block else 0, ws.data_ptr() if ws is not None else None,
+                                _stream(x.device.index))
         _cabi.check(st, 'lcb_minmax')
         return mins, maxs
 
@@ -334,10 +338,75 @@ class BaseQuantizer(object):
             raise NotImplementedError('calib_algo=mse is not on the CUDA hot path')
         return self.get_minmax_range(tensor)
 
+    # ---- static activation calibration (quant.py:103-117, 221-264, 524-586): host glue over the GPU range kernel -------
+    def reshape_batch_tensors(self, act_tensors):
+        assert len(act_tensors) > 0, (
+            'Calibration data is insufficient. Please provide more data to ensure '
+            'all experts in the MOE receive an adequate number of tokens.')
+        if isinstance(act_tensors[0], tuple):
+            act_tensors = [torch.stack(tl) for tl in zip(*act_tensors)]
+        elif len(act_tensors) == 1:
+            act_tensors[0] = [act_tensors[0][i] for i in range(act_tensors[0].size(0))]
+        else:
+            act_tensors = [act_tensors]
+        return act_tensors
+
+    def get_minmax_stats(self, act_tensors):
+        stats = {}
+        for idx, tensors in enumerate(act_tensors):
+            mins, maxs = [], []
+            for tensor in tensors:
+                mn, mx = self.get_minmax_range(tensor)
+                mins.append(mn.reshape(-1)[:1].float())
+                maxs.append(mx.reshape(-1)[:1].float())
+            # the reference builds these with torch.tensor([min_val]) one .item() at a time; one transfer here
+            stats[idx] = {'min': torch.cat(mins).cpu(), 'max': torch.cat(maxs).cpu()}
+        return stats
+
+    def get_static_minmax_range(self, act_tensors):
+        stats = self.get_minmax_stats(self.reshape_batch_tensors(act_tensors))
+        return [r['min'].mean() for r in stats.values()], [r['max'].mean() for r in stats.values()]
+
+    def get_static_moving_minmax_range(self, act_tensors, alpha):
+        mins, maxs = [], []
+        for tensors in self.reshape_batch_tensors(act_tensors):
+            mmin = mmax = None
+            for tensor in tensors:
+                mn, mx = self.get_minmax_range(tensor)
+                if mmin is None:
+                    mmin, mmax = mn, mx
+                else:
+                    mmin = mmin + alpha * (mn - mmin)
+                    mmax = mmax + alpha * (mx - mmax)
+            mins.append(mmin)
+            maxs.append(mmax)
+        return mins, maxs
+
+    def get_batch_tensors_qparams(self, act_tensors, alpha=0.01, args={}):
+        if self.calib_algo == 'static_minmax':
+            min_vals, max_vals = self.get_static_minmax_range(act_tensors)
+        elif self.calib_algo == 'static_moving_minmax':
+            min_vals, max_vals = self.get_static_moving_minmax_range(act_tensors, alpha)
+        elif self.calib_algo == 'static_hist':
+            raise NotImplementedError('calib_algo=static_hist (histogram search) is not on the CUDA hot path')
+        else:
+            raise ValueError(f'Unsupported calibration algorithm: {self.calib_algo}')
+        out = ([], [], [], [])
+        for mn, mx in zip(min_vals, max_vals):
+            sc, zp, qmax, qmin = self.get_qparams((mn, mx), mn.device)
+            for lst, v in zip(out, (sc, zp, qmin, qmax)):
+                lst.append(v)
+        return out
+
     def get_qparams(self, tensor_range, device):
         """quant.py:545-559 on given ranges (lcb_qparams_from_range) → (scales, zeros, qmax, qmin)."""
         min_val, max_val = tensor_range[0], tensor_range[1]
-        _require_cuda(min_val, 'get_qparams')
+        if not min_val.is_cuda:
+            # static calibration (quant.py:253-264, 561-586) averages per-batch ranges on the host: scalars travel to the
+            # GPU for the arithmetic and come back to where the reference leaves them
+            dev = torch.device('cuda', torch.cuda.current_device())
+            sc, zp, qmax, qmin = self.get_qparams((min_val.to(dev), max_val.to(dev)), dev)
+            return sc.to(min_val.device), zp.to(min_val.device), qmax.to(device), qmin.to(device)
         md = _promote(min_val.dtype, max_val.dtype)
         mn, mx = min_val.to(md).contiguous(), max_val.to(md).contiguous()
         qd = md

@@ -60,9 +60,28 @@ def run(c):
     return rec
 
 
+STATIC = [dict(bit=8, sym=True, algo='static_minmax', dtype='bfloat16', seed=321),
+          dict(bit=8, sym=False, algo='static_minmax', dtype='float16', seed=322),
+          dict(bit=8, sym=False, algo='static_moving_minmax', dtype='bfloat16', seed=323)]
+
+
+def static_acts(c):
+    return [make_input((1, 48, 256), getattr(torch, c['dtype']), c['seed'] + i, 'act') for i in range(3)]
+
+
+def run_static(c):
+    from llmc.compression.quantization import quant as refq
+    q = refq.IntegerQuantizer(c['bit'], c['sym'], 'per_tensor', calib_algo=c['algo'])
+    with torch.no_grad():
+        sc, zp, qmin, qmax = q.get_batch_tensors_qparams(static_acts(c), alpha=0.01)
+        x = static_acts(c)[0]
+        fake = q.fake_quant_act_static(x.clone(), {'scales': sc[0], 'zeros': zp[0], 'qmax': qmax[0], 'qmin': qmin[0]})
+    return dict(case=c, scales=sc, zeros=zp, fake=fake)
+
+
 def main():
     sys.path.insert(0, '/root/reference')
-    recs = [run(c) for c in CASES]
+    recs = [run(c) for c in CASES] + [run_static(c) for c in STATIC]
     buf = io.BytesIO()
     torch.save(recs, buf)
     with gzip.open(OUT, 'wb') as f:

@@ -9,13 +9,15 @@ import torch
 
 from lightcompress_b200 import quant as Q
 from tests.golden.make_golden import make_input
-from tests.golden.make_range_golden import factors
+from tests.golden.make_range_golden import factors, static_acts
 
 pytestmark = pytest.mark.gpu
 DEV = 'cuda:0'
 PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'range_golden.pt.gz')
 with gzip.open(PATH, 'rb') as f:
     GOLD = torch.load(io.BytesIO(f.read()), weights_only=False)
+STATIC = [r for r in GOLD if 'algo' in r['case']]
+GOLD = [r for r in GOLD if 'algo' not in r['case']]
 IDS = [f"{r['case']['gran']}-b{r['case']['bit']}-{'sym' if r['case']['sym'] else 'asym'}-{r['case']['dtype']}" for r in GOLD]
 
 
@@ -62,3 +64,17 @@ def test_quant_dequant_and_learnable_match_reference(rec):
         out = ql.fake_quant_weight_dynamic(x, {'lowbound_factor': lo.to(DEV), 'upbound_factor': up.to(DEV)})
         assert out.dtype == dtype
         assert _same(out, rec[f'learnable_{fdt}']), f'learnable bounds ({fdt} factors) differ'
+
+
+@pytest.mark.parametrize('rec', STATIC, ids=[f"{r['case']['algo']}-{'sym' if r['case']['sym'] else 'asym'}" for r in STATIC])
+def test_static_activation_calibration_matches_reference(rec):
+    c = rec['case']
+    q = Q.IntegerQuantizer(c['bit'], c['sym'], 'per_tensor', calib_algo=c['algo'])
+    acts = [a.to(DEV) for a in static_acts(c)]
+    sc, zp, qmin, qmax = q.get_batch_tensors_qparams(acts, alpha=0.01)
+    assert len(sc) == len(rec['scales']) == 1
+    assert _same(sc[0], rec['scales'][0]), (sc[0], rec['scales'][0])
+    if not c['sym']:
+        assert _same(zp[0], rec['zeros'][0])
+    fake = q.fake_quant_act_static(acts[0], {'scales': sc[0], 'zeros': zp[0], 'qmax': qmax[0], 'qmin': qmin[0]})
+    assert _same(fake, rec['fake'])
