@@ -446,6 +446,10 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
   const int n_seg = splits == 2 ? 3 : 6;
 
   // ---- phase 1: A = R R^T, R upper, from the last block column to the first ----
+  // Two-level trailing update (same sums, a quarter of the fp32 read-modify-write traffic): inside a super-block of
+  // SUPER panels a factored panel is retired only from the super-block's remaining columns (K = 128, narrow); when the
+  // super-block is done, its SUPER * 128 columns are retired from everything to the left in one SYRK (K = 512).
+  constexpr int SUPER = 4;
   for (int k = nb - 1; k >= 0; --k) {
     chol_diag_kernel<<<1, 512, SM_DIAG, st>>>(A, sp, lda, k, info);
     LCB_CUDA_CHECK_LAUNCH("chol_diag");
@@ -455,12 +459,24 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
     LCB_CUDA_CHECK_LAUNCH("chol_trsm");
     const void* aa[6];
     const void* bb[6];
-    for (int s = 0; s < n_seg; ++s) {
-      aa[s] = sp.s[pa[s]] + n1;   // rows 0 .. n1-1, columns n1 .. n1+127
-      bb[s] = sp.s[pb[s]] + n1;
+    const int64_t s0 = (int64_t)(k / SUPER) * SUPER * NB;   // first column of this super-block
+    if (n1 > s0) {   // near: H[0:n1, s0:n1] -= R[0:n1, k] R[s0:n1, k]^T
+      for (int s = 0; s < n_seg; ++s) {
+        aa[s] = sp.s[pa[s]] + n1;                // rows 0 .. n1-1, columns n1 .. n1+127
+        bb[s] = sp.s[pb[s]] + s0 * lda + n1;     // rows s0 .. n1-1 of the same block column
+      }
+      const int rc = tc_gemm_launch_ex(true, true, false, true, false, 1, aa, bb, n_seg, A + s0, n1, n1 - s0, NB, lda, lda, lda, st);
+      if (rc != LCB_OK) return rc;
     }
-    const int rc = tc_gemm_launch_ex(true, true, true, true, false, 1, aa, bb, n_seg, A, n1, n1, NB, lda, lda, lda, st);
-    if (rc != LCB_OK) return rc;
+    if (n1 == s0) {   // far: the finished super-block [s0, s1) leaves everything to its left
+      const int64_t s1 = std::min<int64_t>(s0 + (int64_t)SUPER * NB, np);
+      for (int s = 0; s < n_seg; ++s) {
+        aa[s] = sp.s[pa[s]] + s0;                // rows 0 .. s0-1, columns s0 .. s1-1
+        bb[s] = sp.s[pb[s]] + s0;
+      }
+      const int rc = tc_gemm_launch_ex(true, true, true, true, false, 1, aa, bb, n_seg, A, s0, s0, s1 - s0, lda, lda, lda, st);
+      if (rc != LCB_OK) return rc;
+    }
   }
   // ---- phase 2: U = R^-1 by block rows from the bottom, in place ----
   tri_inv_diag_kernel<<<nb, 128, SM_INV, st>>>(A, Dinv, lda);

@@ -59,19 +59,20 @@ __global__ void __launch_bounds__(256)
 // ---- IntegerQuantizer.quant_dequant of one fp32 value (quant.py:699-717), math dtype fp32 ------------------------------
 // x / s is RN(x / s): by a Markstein step on r = RN(1 / s) when (s, x) are inside the window where that step is exact
 // (tests/test_fq_math_identity.py), by the IEEE division otherwise. `fast` is per (row, group).
+__device__ __noinline__ float div_ieee(float x, float s) { return __fdiv_rn(x, s); }   // cold: kept out of the step body
 __device__ __forceinline__ float div_exact(float x, float s, float r, bool fast) {
   if (fast && (fabsf(x) >= 1e-30f || x == 0.f) && fabsf(x) <= 1e30f) {
     const float q0 = __fmul_rn(x, r);
     return __fmaf_rn(__fmaf_rn(-s, q0, x), r, q0);
   }
-  return __fdiv_rn(x, s);
+  return div_ieee(x, s);
 }
 __device__ __forceinline__ float qdq_f32(float x, float s, float r, bool fast, float z, const GSpec& g) {
   float q;
   if (g.round_zp) {
     q = clamp_nan(__fadd_rn(rintf(div_exact(x, s, r, fast)), z), g.qmin, g.qmax);
   } else {
-    q = clamp_nan(rintf(__fadd_rn(__fdiv_rn(x, max_nan(s, 1e-9f)), z)), g.qmin, g.qmax);
+    q = clamp_nan(rintf(__fadd_rn(div_ieee(x, max_nan(s, 1e-9f)), z)), g.qmin, g.qmax);
   }
   return __fmul_rn(__fsub_rn(q, z), s);
 }
@@ -79,7 +80,33 @@ __device__ __forceinline__ float qdq_f32(float x, float s, float r, bool fast, f
 constexpr int LPR = 8;    // lanes per weight row
 constexpr int NK = 16;    // columns per lane (block of up to 128 columns)
 constexpr int BSMAX = LPR * NK;
-constexpr int BLOCK_SMEM = BSMAX * BSMAX * 4 + BSMAX * 8;  // Hinv1 + per-step 1/d + per-step group index
+// Hinv1 in shared memory, laid out for the update loop: row i holds, for every lane l, the NK values Hinv1[i][kk * LPR + l]
+// (kk = 0 .. NK-1) contiguously, lane blocks HLANE floats apart (20: the 8 lanes of a row hit distinct bank groups with
+// 128-bit loads). One step then reads its remaining columns with (NK - k) / 4 LDS.128 instead of NK - k scalar loads.
+constexpr int HLANE = NK + 4, HROW = LPR * HLANE;
+constexpr int BLOCK_SMEM = BSMAX * HROW * 4 + BSMAX * 12;  // Hinv1 + diag + 1/diag + per-step group index
+
+// group switch (rare, CTA-uniform): scale / zero / reciprocal of the new group; out of line to keep the step body small
+struct GroupQ {
+  float s, z, rs;
+  int fast;
+};
+__device__ __noinline__ GroupQ load_group(const float* gscales, const float* gzeros, int64_t off, int sym) {
+  GroupQ q;
+  q.s = gscales[off];
+  q.z = (gzeros && !sym) ? gzeros[off] : 0.f;
+  q.fast = (q.s >= 1e-20f) && (q.s <= 1e20f);
+  q.rs = q.fast ? __frcp_rn(q.s) : 1.f;
+  return q;
+}
+__device__ __noinline__ GroupQ make_group(float s, float z) {
+  GroupQ q;
+  q.s = s;
+  q.z = z;
+  q.fast = (s >= 1e-20f) && (s <= 1e20f);
+  q.rs = q.fast ? __frcp_rn(s) : 1.f;
+  return q;
+}
 
 // grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BLOCK_SMEM
 // FUSED_QP: the quantization groups of this block start inside it, are aligned to multiples of 8 columns and end inside
@@ -92,16 +119,35 @@ __global__ void __launch_bounds__(256)
                       float* __restrict__ gscales, float* __restrict__ gzeros,
                       const int32_t* __restrict__ col_group, int64_t R, int64_t C, int i1, int count, int err_col0,
                       int err_ld, int group_size, GSpec gsp, SpecD sp) {
-  extern __shared__ float Hs[];  // [BSMAX][BSMAX], rows/cols >= count are zero
-  float* rdiag = Hs + BSMAX * BSMAX;                      // RN(1 / Hinv1[i, i])
+  extern __shared__ float Hs[];  // [BSMAX][HROW] (see HLANE), rows/cols >= count are zero
+  float* dg = Hs + BSMAX * HROW;                          // Hinv1[i, i]
+  float* rdiag = dg + BSMAX;                              // RN(1 / Hinv1[i, i])
   int* gidx = reinterpret_cast<int*>(rdiag + BSMAX);      // group of column i1 + i
-  for (int idx = threadIdx.x; idx < BSMAX * BSMAX; idx += blockDim.x) {
-    const int r = idx / BSMAX, c = idx % BSMAX;
-    Hs[idx] = (r < count && c < count) ? Hinv[(int64_t)(i1 + r) * C + i1 + c] : 0.f;
+  {  // Hinv1 tile -> shared memory: 16 loads in flight per thread before the first store (a plain copy loop pays the L2
+     // latency once per element)
+    constexpr int PER = BSMAX * BSMAX / 256, B = 16;
+    const float* hbase = Hinv + (int64_t)i1 * C + i1;
+#pragma unroll 1
+    for (int b0 = 0; b0 < PER; b0 += B) {
+      float v[B];
+#pragma unroll
+      for (int u = 0; u < B; ++u) {
+        const int idx = (b0 + u) * 256 + threadIdx.x;
+        const int r = idx / BSMAX, c = idx % BSMAX;
+        v[u] = (r < count && c < count) ? hbase[(int64_t)r * C + c] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < B; ++u) {
+        const int idx = (b0 + u) * 256 + threadIdx.x;
+        const int r = idx / BSMAX, c = idx % BSMAX;
+        Hs[r * HROW + (c % LPR) * HLANE + c / LPR] = v[u];
+      }
+    }
   }
   if (threadIdx.x < BSMAX) {
     const int i = threadIdx.x;
     const float d = i < count ? Hinv[(int64_t)(i1 + i) * C + i1 + i] : 1.f;
+    dg[i] = d;
     rdiag[i] = (fabsf(d) >= 1e-20f && fabsf(d) <= 1e20f) ? __frcp_rn(d) : 0.f;  // 0: take the IEEE division
     const int col = i1 + (i < count ? i : count - 1);
     gidx[i] = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
@@ -154,6 +200,7 @@ __global__ void __launch_bounds__(256)
     }
   }
   int cur_g = -1;
+  const int g_first = gidx[0];
   float s = 1.f, z = 0.f, rs = 1.f;
   bool fast = false;
 #pragma unroll
@@ -164,21 +211,23 @@ __global__ void __launch_bounds__(256)
       if (i >= count) break;  // uniform
       const float w = __shfl_sync(0xffffffffu, reg[k], (lane & ~(LPR - 1)) | l0);
       const int g = gidx[i];
-      if (g != cur_g) {  // uniform across the CTA
+      if (g != cur_g) {  // uniform across the CTA, rare
         cur_g = g;
+        GroupQ gq;
         if (FUSED_QP) {
-          const int gi = i / group_size;
-          s = gi == 0 ? sq[0] : gi == 1 ? sq[1] : gi == 2 ? sq[2] : sq[3];
-          z = gi == 0 ? zq[0] : gi == 1 ? zq[1] : gi == 2 ? zq[2] : zq[3];
+          const int gi = g - g_first;   // groups of a fused block are consecutive
+          gq = make_group(gi == 0 ? sq[0] : gi == 1 ? sq[1] : gi == 2 ? sq[2] : sq[3],
+                          gi == 0 ? zq[0] : gi == 1 ? zq[1] : gi == 2 ? zq[2] : zq[3]);
         } else {
-          s = gscales[(int64_t)g * R + row];
-          z = (gzeros && !gsp.sym) ? gzeros[(int64_t)g * R + row] : 0.f;
+          gq = load_group(gscales, gzeros, (int64_t)g * R + row, gsp.sym);
         }
-        fast = (s >= 1e-20f) && (s <= 1e20f);
-        rs = fast ? __frcp_rn(s) : 1.f;
+        s = gq.s;
+        z = gq.z;
+        rs = gq.rs;
+        fast = gq.fast != 0;
       }
       const float q = qdq_f32(w, s, rs, fast, z, gsp);
-      const float d = Hs[i * BSMAX + i];
+      const float d = dg[i];
       const float rd = rdiag[i];
       const float diff = __fsub_rn(w, q);
       const float err = div_exact(diff, d, rd, rd != 0.f);   // (w - q) / d
@@ -187,10 +236,18 @@ __global__ void __launch_bounds__(256)
         diffv[k] = diff;
         errv[k] = err;
       }
-      const float* hrow = Hs + i * BSMAX + l;
+      // W1[:, j] -= err * Hinv1[i, j] for the columns j > i this lane owns: separate multiply and subtract (the
+      // reference's outer product + sub). 128-bit loads of the lane's contiguous Hinv1 slice.
+      const float4* h4 = reinterpret_cast<const float4*>(Hs + i * HROW + l * HLANE);
 #pragma unroll
-      for (int kk = k; kk < NK; ++kk) {
-        if (kk > k || l > l0) reg[kk] = __fsub_rn(reg[kk], __fmul_rn(err, hrow[kk * LPR]));
+      for (int c4 = k / 4; c4 < NK / 4; ++c4) {
+        const float4 h = h4[c4];
+        const float hv[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int kk = c4 * 4 + t;
+          if (kk > k || (kk == k && l > l0)) reg[kk] = __fsub_rn(reg[kk], __fmul_rn(err, hv[t]));
+        }
       }
     }
   }
@@ -199,7 +256,7 @@ __global__ void __launch_bounds__(256)
   for (int k = 0; k < NK; ++k) {
     const int j = k * LPR + l;
     if (j < count) {
-      const float d = Hs[j * BSMAX + j];
+      const float d = dg[j];
       Out[row * C + i1 + j] = tmpv[k];
       Losses[row * C + i1 + j] = __fdiv_rn(__fmul_rn(diffv[k], diffv[k]), __fmul_rn(2.f, __fmul_rn(d, d)));  // (w-q)^2 / (2 d^2)
       const __nv_bfloat16 h = __float2bfloat16_rn(errv[k]);

@@ -123,6 +123,7 @@ int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tr
   const int grid = n_items < kNumSMs ? n_items : kNumSMs;
   if (b_kmajor) {
     if (a_kmajor && syrk && neg) return launch_variant<true, true, true, true, EPI_REDUCE_ADD>(maps, p, grid, st);
+    if (a_kmajor && !syrk && neg) return launch_variant<true, true, false, true, EPI_REDUCE_ADD>(maps, p, grid, st);
     return LCB_E_UNSUPPORTED;
   }
   if (!a_kmajor && syrk && !neg) return launch_variant<false, false, true, false, EPI_REDUCE_ADD>(maps, p, grid, st);
