@@ -277,18 +277,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    sampler.start()   # nvidia-smi needs ~100 ms per sample: it runs from the warm-up to the end of the e2e leg
     for _ in range(max(args.warmup, 3)):
         step()
-    sampler = ClockSampler(local)
     sync()
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     sync()
-    clocks = sampler.stop()
     ms = e0.elapsed_time(e1) / args.steps
     t = torch.tensor([ms], device=dev)
     if world > 1:
@@ -319,6 +318,7 @@ def main():
     e1.record()
     sync()
     pipe.synchronize()
+    clocks = sampler.stop()
     t = torch.tensor([e0.elapsed_time(e1) / e2e_steps], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -108,51 +108,18 @@ __device__ __noinline__ GroupQ make_group(float s, float z) {
   return q;
 }
 
-// grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BLOCK_SMEM
-// FUSED_QP: the quantization groups of this block start inside it, are aligned to multiples of 8 columns and end inside
-// it, so their (min, max) are taken from the block's own (not yet updated) register copy — exactly the outer W the
-// reference searches (gptq.py:215-223) — and no separate qparams kernel runs.
-template <bool FUSED_QP>
-__global__ void __launch_bounds__(256)
-    gptq_block_kernel(const float* __restrict__ W, const float* __restrict__ Hinv, float* __restrict__ Out,
-                      float* __restrict__ Losses, __nv_bfloat16* __restrict__ err_hi, __nv_bfloat16* __restrict__ err_lo,
-                      float* __restrict__ gscales, float* __restrict__ gzeros,
-                      const int32_t* __restrict__ col_group, int64_t R, int64_t C, int i1, int count, int err_col0,
-                      int err_ld, int group_size, GSpec gsp, SpecD sp) {
-  extern __shared__ float Hs[];  // [BSMAX][HROW] (see HLANE), rows/cols >= count are zero
-  float* dg = Hs + BSMAX * HROW;                          // Hinv1[i, i]
-  float* rdiag = dg + BSMAX;                              // RN(1 / Hinv1[i, i])
-  int* gidx = reinterpret_cast<int*>(rdiag + BSMAX);      // group of column i1 + i
-  {  // Hinv1 tile -> shared memory: 16 loads in flight per thread before the first store (a plain copy loop pays the L2
-     // latency once per element)
-    constexpr int PER = BSMAX * BSMAX / 256, B = 16;
-    const float* hbase = Hinv + (int64_t)i1 * C + i1;
-#pragma unroll 1
-    for (int b0 = 0; b0 < PER; b0 += B) {
-      float v[B];
-#pragma unroll
-      for (int u = 0; u < B; ++u) {
-        const int idx = (b0 + u) * 256 + threadIdx.x;
-        const int r = idx / BSMAX, c = idx % BSMAX;
-        v[u] = (r < count && c < count) ? hbase[(int64_t)r * C + c] : 0.f;
-      }
-#pragma unroll
-      for (int u = 0; u < B; ++u) {
-        const int idx = (b0 + u) * 256 + threadIdx.x;
-        const int r = idx / BSMAX, c = idx % BSMAX;
-        Hs[r * HROW + (c % LPR) * HLANE + c / LPR] = v[u];
-      }
-    }
-  }
-  if (threadIdx.x < BSMAX) {
-    const int i = threadIdx.x;
-    const float d = i < count ? Hinv[(int64_t)(i1 + i) * C + i1 + i] : 1.f;
-    dg[i] = d;
-    rdiag[i] = (fabsf(d) >= 1e-20f && fabsf(d) <= 1e20f) ? __frcp_rn(d) : 0.f;  // 0: take the IEEE division
-    const int col = i1 + (i < count ? i : count - 1);
-    gidx[i] = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
-  }
-  __syncthreads();
+// The rows of one warp (4 rows x 8 lanes) through the 128 column steps of a block.
+// SPEC = true : speculative pass. Both divisions are Markstein steps without guards; a flag records whether any operand
+//               left the window in which that step equals the IEEE division (or a scale / diagonal had no usable
+//               reciprocal). If the flag is set anywhere in the warp nothing is stored and `true` is returned.
+// SPEC = false: the literal pass (guards + IEEE fallbacks), always stores.
+template <bool FUSED_QP, bool SPEC>
+__device__ __forceinline__ bool gptq_rows(const float* __restrict__ W, float* __restrict__ Out, float* __restrict__ Losses,
+                                          __nv_bfloat16* __restrict__ err_hi, __nv_bfloat16* __restrict__ err_lo,
+                                          float* __restrict__ gscales, float* __restrict__ gzeros, int64_t R, int64_t C,
+                                          int i1, int count, int err_col0, int err_ld, int group_size, const GSpec& gsp,
+                                          const SpecD& sp, const float* Hs, const float* dg, const float* rdiag,
+                                          const int* gidx) {
   const int lane = threadIdx.x & 31;
   const int l = lane & (LPR - 1);
   const int64_t row_raw = (int64_t)blockIdx.x * 32 + (threadIdx.x / LPR);
@@ -203,6 +170,7 @@ __global__ void __launch_bounds__(256)
   const int g_first = gidx[0];
   float s = 1.f, z = 0.f, rs = 1.f;
   bool fast = false;
+  bool bad = false;
 #pragma unroll
   for (int k = 0; k < NK; ++k) {
 #pragma unroll 1
@@ -225,12 +193,26 @@ __global__ void __launch_bounds__(256)
         z = gq.z;
         rs = gq.rs;
         fast = gq.fast != 0;
+        if (SPEC) bad |= !fast;
       }
-      const float q = qdq_f32(w, s, rs, fast, z, gsp);
       const float d = dg[i];
       const float rd = rdiag[i];
-      const float diff = __fsub_rn(w, q);
-      const float err = div_exact(diff, d, rd, rd != 0.f);   // (w - q) / d
+      float q, diff, err;
+      if (SPEC) {
+        const float q0 = __fmul_rn(w, rs);
+        float t = __fmaf_rn(__fmaf_rn(-s, q0, w), rs, q0);                       // RN(w / s) inside the window
+        t = clamp_nan(__fadd_rn(rintf(t), z), gsp.qmin, gsp.qmax);
+        q = __fmul_rn(__fsub_rn(t, z), s);
+        diff = __fsub_rn(w, q);
+        const float e0 = __fmul_rn(diff, rd);
+        err = __fmaf_rn(__fmaf_rn(-d, e0, diff), rd, e0);                          // RN(diff / d) inside the window
+        const float aw = fabsf(w), ad = fabsf(diff);
+        bad |= !((aw >= 1e-30f || w == 0.f) && aw <= 1e30f) | !((ad >= 1e-30f || diff == 0.f) && ad <= 1e30f) | (rd == 0.f);
+      } else {
+        q = qdq_f32(w, s, rs, fast, z, gsp);
+        diff = __fsub_rn(w, q);
+        err = div_exact(diff, d, rd, rd != 0.f);   // (w - q) / d
+      }
       if (l == l0) {
         tmpv[k] = w;
         diffv[k] = diff;
@@ -251,7 +233,8 @@ __global__ void __launch_bounds__(256)
       }
     }
   }
-  if (!row_ok) return;
+  if (SPEC && __any_sync(0xffffffffu, bad)) return true;
+  if (!row_ok) return false;
 #pragma unroll
   for (int k = 0; k < NK; ++k) {
     const int j = k * LPR + l;
@@ -264,6 +247,61 @@ __global__ void __launch_bounds__(256)
       err_lo[row * err_ld + err_col0 + j] = __float2bfloat16_rn(__fsub_rn(errv[k], __bfloat162float(h)));
     }
   }
+  return false;
+}
+
+// grid: ceil(R / 32) CTAs of 256 threads (32 rows); dynamic smem: BLOCK_SMEM
+// FUSED_QP: the quantization groups of this block start inside it, are aligned to multiples of 8 columns and end inside
+// it, so their (min, max) are taken from the block's own (not yet updated) register copy — exactly the outer W the
+// reference searches (gptq.py:215-223) — and no separate qparams kernel runs.
+template <bool FUSED_QP>
+__global__ void __launch_bounds__(256)
+    gptq_block_kernel(const float* __restrict__ W, const float* __restrict__ Hinv, float* __restrict__ Out,
+                      float* __restrict__ Losses, __nv_bfloat16* __restrict__ err_hi, __nv_bfloat16* __restrict__ err_lo,
+                      float* __restrict__ gscales, float* __restrict__ gzeros,
+                      const int32_t* __restrict__ col_group, int64_t R, int64_t C, int i1, int count, int err_col0,
+                      int err_ld, int group_size, GSpec gsp, SpecD sp) {
+  extern __shared__ float Hs[];  // [BSMAX][HROW] (see HLANE), rows/cols >= count are zero
+  float* dg = Hs + BSMAX * HROW;                          // Hinv1[i, i]
+  float* rdiag = dg + BSMAX;                              // RN(1 / Hinv1[i, i])
+  int* gidx = reinterpret_cast<int*>(rdiag + BSMAX);      // group of column i1 + i
+  {  // Hinv1 tile -> shared memory: 16 loads in flight per thread before the first store (a plain copy loop pays the L2
+     // latency once per element)
+    constexpr int PER = BSMAX * BSMAX / 256, B = 16;
+    const float* hbase = Hinv + (int64_t)i1 * C + i1;
+#pragma unroll 1
+    for (int b0 = 0; b0 < PER; b0 += B) {
+      float v[B];
+#pragma unroll
+      for (int u = 0; u < B; ++u) {
+        const int idx = (b0 + u) * 256 + threadIdx.x;
+        const int r = idx / BSMAX, c = idx % BSMAX;
+        v[u] = (r < count && c < count) ? hbase[(int64_t)r * C + c] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < B; ++u) {
+        const int idx = (b0 + u) * 256 + threadIdx.x;
+        const int r = idx / BSMAX, c = idx % BSMAX;
+        Hs[r * HROW + (c % LPR) * HLANE + c / LPR] = v[u];
+      }
+    }
+  }
+  if (threadIdx.x < BSMAX) {
+    const int i = threadIdx.x;
+    const float d = i < count ? Hinv[(int64_t)(i1 + i) * C + i1 + i] : 1.f;
+    dg[i] = d;
+    rdiag[i] = (fabsf(d) >= 1e-20f && fabsf(d) <= 1e20f) ? __frcp_rn(d) : 0.f;  // 0: take the IEEE division
+    const int col = i1 + (i < count ? i : count - 1);
+    gidx[i] = col_group ? col_group[col] : (group_size > 0 ? col / group_size : 0);
+  }
+  __syncthreads();
+  bool redo = true;
+  if (gsp.round_zp)   // speculative pass: branch-free arithmetic, valid when every operand stays inside the exactness windows
+    redo = gptq_rows<FUSED_QP, true>(W, Out, Losses, err_hi, err_lo, gscales, gzeros, R, C, i1, count, err_col0, err_ld,
+                                     group_size, gsp, sp, Hs, dg, rdiag, gidx);
+  if (redo)           // warp-uniform, rare: the literal pass (IEEE divisions where a window is left)
+    gptq_rows<FUSED_QP, false>(W, Out, Losses, err_hi, err_lo, gscales, gzeros, R, C, i1, count, err_col0, err_ld,
+                               group_size, gsp, sp, Hs, dg, rdiag, gidx);
 }
 
 __global__ void __launch_bounds__(256) split_f32_2d_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ hi,
