@@ -66,3 +66,20 @@ def test_weight_transform_static_per_channel():
                                                   static_scales=sc_o.to(DEV))
     assert torch.equal(tmp.cpu()[:, :bs], tmp_o[:, :bs])
     assert _rel(tmp.cpu(), tmp_o) < 1e-3
+
+
+def test_weight_transform_outside_exactness_window_takes_literal_pass():
+    # operands below 1e-30 leave the window of the speculative (Markstein) pass: the warp re-runs the literal pass, and the
+    # first block must still be bit-identical to the reference arithmetic
+    R, C, bs = 64, 256, 128
+    W, Hinv = _problem(R, C, 2 * C, seed=9)
+    W[3, 5] = 1e-33
+    W[10, 40] = -3e-35
+    W[20, :128] = 0.0          # an all-zero group (scale clamps to 1e-5 / 15)
+    spec = dict(kind=0, sym=False, qmin=0.0, qmax=15.0)
+    tmp_o, loss_o, sc_o, zp_o = go.weight_transform(W.clone(), Hinv, bs, 128, spec)
+    tmp, losses, sc, zp = ops.gptq_weight_transform(W.clone().to(DEV), Hinv.to(DEV), bs, 128, 0.0, 15.0, False)
+    assert torch.equal(tmp.cpu()[:, :bs], tmp_o[:, :bs])
+    assert torch.equal(losses.cpu()[:, :bs], loss_o[:, :bs])
+    assert torch.equal(sc.cpu()[:1], sc_o[:1]) and torch.equal(zp.cpu()[:1], zp_o[:1])
+    assert _rel(tmp.cpu(), tmp_o) < 1e-3
