@@ -35,6 +35,18 @@ def _worker(rank, world, port, q):
     out['best'] = lcdist.argmin_across_ranks([losses_all[i] for i in cands], cands, torch.device('cpu'))
     t = torch.tensor([float(rank), 5.0 - rank])
     out['max'] = lcdist.allreduce_max(t)
+    # expert sharding: weight i on rank i mod world, results gathered on every rank (fp8 codes travel as bytes)
+    from lightcompress_b200.algo import rtn_real_quantize_sharded
+    weights = {f'experts.{i}.w': torch.full((4, 8), float(i + 1)) for i in range(5)}
+    calls = []
+
+    def fake_quantize(w):
+        calls.append(float(w[0, 0]))
+        return (w / 8).to(torch.float8_e4m3fn), w.amax(dim=1, keepdim=True), None
+    res = rtn_real_quantize_sharded(weights, None, quantize=fake_quantize)
+    out['expert_calls'] = calls
+    out['experts'] = {n: (c.float(), s, z) for n, (c, s, z) in res.items()}
+    out['local_only'] = sorted(rtn_real_quantize_sharded(weights, None, quantize=fake_quantize, gather=False))
     q.put((rank, out))
     dist.barrier()
     dist.destroy_process_group()
@@ -60,6 +72,13 @@ def test_result_only_collectives_world2():
         assert res[r]['cands'] == list(range(r, 20, 2))
         assert res[r]['best'] == (0.0, 7)          # tie between 7 (rank 1) and 11 (rank 1)... lowest index wins
         assert torch.equal(res[r]['max'], torch.tensor([1.0, 5.0]))
+        assert res[r]['expert_calls'][:3 - r] == [float(i + 1) for i in range(r, 5, 2)]     # only its own experts
+        assert sorted(res[r]['experts']) == [f'experts.{i}.w' for i in range(5)]
+        for i in range(5):
+            c, s_, z = res[r]['experts'][f'experts.{i}.w']
+            assert torch.equal(c, torch.full((4, 8), (i + 1) / 8.0)) and z is None
+            assert torch.equal(s_, torch.full((4, 1), float(i + 1)))
+        assert res[r]['local_only'] == [f'experts.{i}.w' for i in range(r, 5, 2)]
 
 
 def test_single_process_is_identity():
