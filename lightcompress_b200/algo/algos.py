@@ -57,9 +57,16 @@ class GPTQ(BaseBlockwiseQuantization):
             self.layers_cache[n] = self._new_layer(m, shared[key])
             self.hessian_owner[n] = first
 
+    graph_safe_hooks = True   # the hook launches one kernel into a persistent buffer and keeps no tensor
+
     def cache_input_hook(self, m, x, y, name, feat_dict):   # gptq.py:247-251: accumulate, do not keep the input
         if name in self.layers_cache and self.hessian_owner.get(name, True):
-            self.layers_cache[name].add_batch(x[0].detach())
+            if self._capturing:   # block_forward is recording a CUDA graph: the batch is counted once per replay
+                st = self.layers_cache[name].hessian
+                b = st.add_batch(x[0].detach(), count=False)
+                self._on_replay.append(lambda st=st, b=b: setattr(st, 'nsamples', st.nsamples + b))
+            else:
+                self.layers_cache[name].add_batch(x[0].detach())
 
     @torch.no_grad()
     def subset_transform(self, subset, input_feat, subset_kwargs):   # gptq.py:97-126

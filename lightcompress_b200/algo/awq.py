@@ -84,8 +84,9 @@ def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, 
         for m, w0 in zip(layers, saved):
             m.weight.data = wquantizer.fake_quant_weight_dynamic(ops.scale_cols(w0, scales))
         out = fwd(ops.scale_cols(x, scales, div=True))
-        losses.append((org_out - out).float().pow(2).mean().item())
+        losses.append((org_out - out).float().pow(2).mean())   # stays on the device: one sync after the loop
         for m, w0 in zip(layers, saved):
             m.weight.data = w0
+    losses = torch.stack(losses).tolist() if losses else []
     _, best = lcdist.argmin_across_ranks(losses, mine, x.device)
     return get_scales(x_mean, w_max, best / n_grid, version), best, losses

@@ -25,12 +25,15 @@ class HessianState(object):
         self._factor = None     # (key, dead, perm, Hinv)
 
     @torch.no_grad()
-    def add_batch(self, inp):
-        """gptq.py:254-295 for Linear layers: `nsamples` counts batches (inp.shape[0]), not tokens."""
+    def add_batch(self, inp, count=True):
+        """gptq.py:254-295 for Linear layers: `nsamples` counts batches (inp.shape[0]), not tokens.
+        count=False: launch only (CUDA-graph capture of the block forward); the caller adds the batch count per replay."""
         if inp.dim() == 2:
             inp = inp.unsqueeze(0)
-        self.nsamples += inp.shape[0]
+        if count:
+            self.nsamples += inp.shape[0]
         ops.hessian_accum(self.S, inp)
+        return inp.shape[0]
 
     @torch.no_grad()
     def finalize(self):
@@ -86,8 +89,8 @@ class GPTQLayer(object):
     H = property(lambda self: self.hessian.H)
     nsamples = property(lambda self: self.hessian.nsamples)
 
-    def add_batch(self, inp):
-        self.hessian.add_batch(inp)
+    def add_batch(self, inp, count=True):
+        return self.hessian.add_batch(inp, count)
 
     def finalize(self):
         return self.hessian.finalize()

@@ -124,6 +124,36 @@ def test_gptq_shared_hessian_equals_per_linear():
     assert float((outs[True] == outs[False]).float().mean()) > 0.99
 
 
+def test_gptq_graph_replayed_forward_equals_eager(monkeypatch):
+    # the recorded-and-replayed block forward (CUDA graph, hooks included) must do what the per-sample eager loop does:
+    # same Hessian sample count, same quantized weights (up to the run-to-run order of the Hessian reduce-adds)
+    from lightcompress_b200.algo import blockwise as bw
+    from lightcompress_b200.algo import gptq as lcgptq
+    model = _tiny_llama(seed=7)
+    data = _calib(n=6, seed=8)
+    used, counts = [], []
+    orig = bw.BaseBlockwiseQuantization._block_forward_graph
+    monkeypatch.setattr(bw.BaseBlockwiseQuantization, '_block_forward_graph',
+                        lambda self, *a, **k: (used.append(1), orig(self, *a, **k))[1])
+    fin = lcgptq.HessianState.finalize
+    monkeypatch.setattr(lcgptq.HessianState, 'finalize',
+                        lambda self: (counts.append(self.nsamples) if self.H is None else None, fin(self))[1])
+    outs = {}
+    for graph in (True, False):
+        q = copy.deepcopy(model)
+        cfg = {'weight': W4, 'special': {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
+                                         'true_sequential': True, 'cuda_graph': graph}}
+        n_used = len(used)
+        a = _run('GPTQ', cfg, q, data)
+        assert (len(used) > n_used) == graph
+        outs[graph] = torch.cat([m.weight.data.float().flatten() for blk in a.blocks
+                                 for m in a.model.get_block_linears(blk).values()])
+    assert counts and all(c == 6 for c in counts), counts
+    rel = float((outs[True] - outs[False]).norm() / outs[False].norm())
+    assert rel < 1e-3, rel
+    assert float((outs[True] == outs[False]).float().mean()) > 0.99
+
+
 def test_gptq_beats_rtn_on_calibration_data():
     model = _tiny_llama(seed=3)
     data = _calib(n=8, seed=4)

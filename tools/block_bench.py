@@ -1,0 +1,75 @@
+"""End-to-end calibration seconds per block through the ALGO_REGISTRY plug-ins, on ONE random-init decoder block with
+Llama-3-8B dimensions (hidden 4096, inter 14336, 32 heads / 8 KV heads) — BASELINE.json's "GPTQ/AWQ calib s/block".
+
+    python tools/block_bench.py [gptq] [awq] [--samples N]
+
+GPTQ: 128 samples x 2048 tokens, w4a16 g128, true_sequential (configs/quantization/methods/GPTQ/gptq_w_only.yml).
+AWQ : 128 samples x 512 tokens, w4a16 g128, trans v2 + weight_clip (awq_w_only.yml).
+The time covers everything `block_opt` does for the block: the hooked forward(s), Hessians / searches, factorisations,
+updates, scale application, clipping — including the attention / MLP module forwards the searches need (torch ops).
+"""
+import json
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from lightcompress_b200 import algo  # noqa: E402
+
+W4 = {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128}
+
+
+def one_block_llama(dev, seed=0):
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(seed)
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=4096, intermediate_size=14336, num_hidden_layers=1,
+                      num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=4096)
+    with torch.device(dev):
+        m = LlamaForCausalLM(cfg).to(torch.bfloat16).eval()
+    return m
+
+
+def run(method, dev, samples, seq, special):
+    model = one_block_llama(dev)
+    g = torch.Generator().manual_seed(1)
+    data = [{'input_ids': torch.randint(0, 1024, (1, seq), generator=g).to(dev)} for _ in range(samples)]
+    ad = algo.adapters.LlamaAdapter(model)
+    inp = ad.collect_first_block_input(data)
+    a = algo.ALGO_REGISTRY[method](ad, {'weight': dict(W4), 'special': special}, inp, None, {'calib': {'seq_len': seq}})
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    a.run_block_loop()
+    torch.cuda.synchronize()
+    t = time.perf_counter() - t0
+    w = model.model.layers[0].mlp.down_proj.weight
+    assert torch.isfinite(w.float()).all()
+    del a, ad, model, data, inp
+    torch.cuda.empty_cache()
+    return t
+
+
+def main(argv=None, emit=True):
+    argv = sys.argv[1:] if argv is None else argv
+    dev = torch.device('cuda:0')
+    samples = int(argv[argv.index('--samples') + 1]) if '--samples' in argv else 128
+    which = [a for a in argv if a in ('gptq', 'awq')] or ['gptq', 'awq']
+    res = {}
+    if 'gptq' in which:
+        sp = {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
+        run('GPTQ', dev, 2, 2048, sp)      # warm-up: attributes, allocator, cuBLAS handles of the module forwards
+        res['gptq_s_per_block'] = run('GPTQ', dev, samples, 2048, sp)
+        res['gptq_config'] = f'{samples} x 2048 tokens, w4a16 g128, true_sequential, shared Hessians'
+    if 'awq' in which:
+        sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
+        run('Awq', dev, 2, 512, sp)
+        res['awq_s_per_block'] = run('Awq', dev, samples, 512, sp)
+        res['awq_config'] = f'{samples} x 512 tokens, w4a16 g128, trans v2 + AutoClip'
+    if emit:
+        print(json.dumps(res), flush=True)
+    return res
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,48 @@
+"""Wall time per phase (synchronised) of one end-to-end GPTQ / Awq block calibration."""
+import os
+import sys
+import time
+from collections import defaultdict
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import block_bench as bb  # noqa: E402
+from lightcompress_b200.algo import blockwise as bw  # noqa: E402
+
+acc = defaultdict(float)
+
+
+def timed(cls, name):
+    f = getattr(cls, name)
+
+    def g(*a, **k):
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        r = f(*a, **k)
+        torch.cuda.synchronize()
+        acc[name] += time.perf_counter() - t
+        return r
+    setattr(cls, name, g)
+
+
+method = sys.argv[1] if len(sys.argv) > 1 else 'gptq'
+dev = torch.device('cuda:0')
+from lightcompress_b200.algo import algos  # noqa: E402
+for c, n in ((bw.BaseBlockwiseQuantization, 'block_forward'), (algos.GPTQ, 'subset_transform'),
+             (algos.Awq, 'subset_transform'), (bw.BaseBlockwiseQuantization, 'rehook_next_subset')):
+    timed(c, n)
+if method == 'awq':
+    from lightcompress_b200.algo import autoclip
+    timed(autoclip, 'auto_clip_block')
+if method == 'gptq':
+    sp = {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
+    bb.run('GPTQ', dev, 2, 2048, sp)
+    acc.clear()
+    t = bb.run('GPTQ', dev, 128, 2048, sp)
+else:
+    sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
+    bb.run('Awq', dev, 2, 512, sp)
+    acc.clear()
+    t = bb.run('Awq', dev, 128, 512, sp)
+print('wall', t, dict(acc))
