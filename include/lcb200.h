@@ -119,6 +119,20 @@ int lcb_qparams_from_range(const void* mins, const void* maxs, void* scales, voi
                            const lcb_quant_spec* spec, void* stream);
 
 /*
+ * calib_algo = 'mse': the shrink-grid range search of BaseQuantizer.get_mse_range (quant.py:145-203) on a contiguous
+ * [n_units, unit_len] tensor of spec->dtype (the reshape_tensor() layout of per_group / per_channel / per_token /
+ * per_head; the reference itself only handles 2-D row units here). For i in [0, n_steps) — n_steps =
+ * int(maxshrink * mse_grid) — the candidate range is (1 - i / mse_grid) * (min, max) of the range kept so far (the
+ * reference writes the kept range through the tensors the next candidate is derived from, quant.py:164, 193-195), its
+ * error sum |quant_dequant(x) - x| ** norm in fp32, kept when strictly smaller. mins / maxs: fp32 [n_units]
+ * (the search runs on tensor.float(), quant.py:151). Uses spec->kind / sym / round_zp / qmin / qmax / dtype only.
+ * unit_len * 4 bytes must fit the shared memory of one CTA (unit_len <= 51200). LCB_KIND_INT only: on a shrunk range the
+ * fp8 grid overflows and the result is defined by qtorch.float_quantize, which cannot be pinned offline.
+ */
+int lcb_mse_range(const void* in, void* mins, void* maxs, int64_t n_units, int64_t unit_len, const lcb_quant_spec* spec,
+                  int32_t n_steps, double mse_grid, float norm, void* stream);
+
+/*
  * Dynamic fake-quant (LCB_OUT_FAKE, IntegerQuantizer, units of 1 x unit_cols with unit_cols * sizeof(dtype) <= 1 KiB)
  * of up to 16 tensors in ONE launch — e.g. the 7 linear weights of a transformer block at deploy time
  * (base_bq.py:899-1006 calls w_qdq once per linear). ins / outs / rows / cols are HOST arrays of n entries; every

@@ -32,6 +32,8 @@ SIGNATURES = {
     'lcb_fakequant_workspace_bytes': (_c_i64, []),
     'lcb_minmax': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp, _c_vp]),
     'lcb_qparams_from_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
+    'lcb_mse_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, ctypes.POINTER(QuantSpec), _c_i32,
+                                     ctypes.c_double, ctypes.c_float, _c_vp]),
     'lcb_fakequant_multi': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i32, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp, _c_vp]),

@@ -119,6 +119,9 @@ class GPTQLayer(object):
         qmin, qmax = self._qrange()
         gs = wq.group_size if wq.granularity == 'per_group' else 0
         col_group = None
+        if gs > 0 and not self.static_groups and static_scales is None and wq.calib_algo != 'minmax':
+            raise NotImplementedError('GPTQ with on-the-fly group qparams fuses the min/max search into the column kernel; '
+                                      f"calib_algo={wq.calib_algo!r} needs static_groups=True or per_channel")
         if gs > 0 and self.static_groups:
             if static_scales is None:   # search_group_qparams (gptq.py:380-395): qparams of the original weight
                 _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data.float())

@@ -215,8 +215,11 @@ class BaseQuantizer(object):
     def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0, out=None):
         """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
         _require_cuda(tensor, 'dynamic quant')
-        if self.calib_algo in ('mse', 'hqq'):   # every other value ranges by min/max here, as get_tensor_range does (quant.py:119-130)
+        if self.calib_algo == 'hqq':   # every other value ranges by min/max here, as get_tensor_range does (quant.py:119-130)
             raise NotImplementedError(f'calib_algo={self.calib_algo!r} is not on the CUDA hot path')
+        if self.calib_algo == 'mse':
+            assert clip == 1.0
+            return self._dynamic_mse(tensor, out_mode, out_dtype, want_qparams, osf)
         x = tensor.contiguous()
         u = self._units(x)
         md = self._math_dtype_dynamic(x.dtype)
@@ -243,6 +246,21 @@ class BaseQuantizer(object):
         with _on_device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, True, out, scales, zeros)
         return out, scales, zeros
+
+    def _dynamic_mse(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0):
+        """calib_algo='mse': searched fp32 range (lcb_mse_range) -> fp32 qparams -> the static kernel, whose math dtype
+        promotes to fp32 exactly as the reference's quant_dequant does with fp32 scales (quant.py:690-717)."""
+        x = tensor.contiguous()
+        u = self._units(x)
+        rng = self.get_mse_range(x)
+        scales, zeros, qmax, qmin = self.get_qparams(rng, x.device)
+        asym = not self.sym and self._kind() == _cabi.KIND_INT
+        out = None
+        if out_mode != _cabi.OUT_NONE:
+            out = self._static(x, scales, zeros if asym else None, qmax, qmin, out_mode, out_dtype, osf, units=u)
+        if not want_qparams:
+            return out, None, None
+        return out, scales.reshape(u.qshape), (zeros.reshape(u.qshape) if asym else None)
 
     def _static(self, tensor, scales, zeros, qmax, qmin, out_mode, out_dtype, osf=1.0, units=None):
         _require_cuda(tensor, 'static quant')
@@ -335,8 +353,37 @@ class BaseQuantizer(object):
         if self.calib_algo == 'learnable':
             return self.get_learnable_range(tensor, **args)
         if self.calib_algo == 'mse':
-            raise NotImplementedError('calib_algo=mse is not on the CUDA hot path')
+            return self.get_mse_range(tensor)
         return self.get_minmax_range(tensor)
+
+    def get_mse_range(self, tensor, norm=2.4, bs=256):
+        """quant.py:145-203 on the GPU (lcb_mse_range): fp32 (min_val, max_val) [units, 1] of the shrink-grid search.
+        Accepts the tensor in its original or in its reshape_tensor() layout. Units are rows (per_group / per_channel /
+        per_token / per_head) of a 2-D tensor, the only layouts the reference's search handles."""
+        _require_cuda(tensor, 'get_mse_range')
+        if self.granularity in ('per_tensor', 'per_block'):
+            raise NotImplementedError(f'calib_algo=mse with granularity={self.granularity}: the reference search indexes '
+                                      '[units, 1] ranges (quant.py:157-161)')
+        if self._kind() != _cabi.KIND_INT:
+            raise NotImplementedError('calib_algo=mse with FloatQuantizer: a shrunk range overflows the fp8 grid and the '
+                                      'outcome is defined by qtorch.float_quantize (not pinned); IntegerQuantizer only')
+        if tensor.dim() != 2:
+            raise RuntimeError('get_mse_range handles 2-D tensors (the error sum runs over dim 1, quant.py:187)')
+        x = tensor.contiguous()
+        u = self._units(x)
+        assert self.mse_b_num >= 1 and u.n_units % self.mse_b_num == 0, \
+            'Batch number must be divisible by tensor.shape[0],'
+        mins = torch.empty((u.n_units, 1), dtype=torch.float32, device=x.device)
+        maxs = torch.empty((u.n_units, 1), dtype=torch.float32, device=x.device)
+        qmin, qmax = self._qrange()
+        spec = self._spec(x.dtype, torch.float32, torch.float32, _cabi.OUT_FAKE, qmin, qmax)
+        lib = _cabi.load()
+        with _on_device(x.device):
+            st = lib.lcb_mse_range(x.data_ptr(), mins.data_ptr(), maxs.data_ptr(), u.n_units, u.uc, spec,
+                                   int(self.maxshrink * self.mse_grid), float(self.mse_grid), float(norm),
+                                   _stream(x.device.index))
+        _cabi.check(st, 'lcb_mse_range')
+        return mins, maxs
 
     # ---- static activation calibration (quant.py:103-117, 221-264, 524-586): host glue over the GPU range kernel -------
     def reshape_batch_tensors(self, act_tensors):
