@@ -15,6 +15,26 @@ def _free_port():
     return p
 
 
+def _plain(o):
+    if isinstance(o, torch.Tensor):
+        return ('__t__', o.numpy().copy())
+    if isinstance(o, dict):
+        return {k: _plain(v) for k, v in o.items()}
+    if isinstance(o, (list, tuple)):
+        return type(o)(_plain(v) for v in o)
+    return o
+
+
+def _unplain(o):
+    if isinstance(o, tuple) and len(o) == 2 and isinstance(o[0], str) and o[0] == '__t__':
+        return torch.from_numpy(o[1])
+    if isinstance(o, dict):
+        return {k: _unplain(v) for k, v in o.items()}
+    if isinstance(o, (list, tuple)):
+        return type(o)(_unplain(v) for v in o)
+    return o
+
+
 def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group('gloo', rank=rank, world_size=world)
@@ -47,7 +67,7 @@ def _worker(rank, world, port, q):
     out['expert_calls'] = calls
     out['experts'] = {n: (c.float(), s, z) for n, (c, s, z) in res.items()}
     out['local_only'] = sorted(rtn_real_quantize_sharded(weights, None, quantize=fake_quantize, gather=False))
-    q.put((rank, out))
+    q.put((rank, _plain(out)))      # numpy, not torch storages: no fd hand-over that races with this process exiting
     dist.barrier()
     dist.destroy_process_group()
 
@@ -59,7 +79,7 @@ def test_result_only_collectives_world2():
     ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in ps:
         p.start()
-    res = dict(q.get(timeout=120) for _ in ps)
+    res = {r: _unplain(o) for r, o in (q.get(timeout=120) for _ in ps)}
     for p in ps:
         p.join(timeout=60)
         assert p.exitcode == 0
