@@ -151,6 +151,26 @@ int lcb_fp8_block_dequant(const void* codes, const float* scales, void* out, int
                           void* stream);
 
 /*
+ * act_quant (kernel.py:7-54, the Triton kernel of LlmcFp8Linear's activation side, module_utils.py:41-43): x is a
+ * contiguous tensor of n_groups * group elements (bf16 / f16 / f32); for every group of `group` consecutive elements
+ * s = max|x| / 448 (fp32) and y = e4m3(x / s) (fp32 division, RNE cast). An all-zero group yields s = 0 and NaN codes
+ * (0 / 0), as the reference does. group in {8, 16, 32, 64, 128, 256}. y: uint8 [n_groups * group], scales fp32 [n_groups].
+ */
+int lcb_act_quant_fp8(const void* x, void* y, float* scales, int64_t n_groups, int64_t group, int32_t dtype,
+                      void* stream);
+
+/*
+ * fp8_gemm (kernel.py:140-242) with the bias add of block_wise_fp8_forward_func (module_utils.py:41-46):
+ *   c[m, n] = out_dtype( sum_kb  dot(a[m, kb], b[n, kb]) * a_s[m, kb] * b_s[n / 128, kb] )  (+ bias[n], rounded again)
+ * a: e4m3 [M, K] row-major, a_s fp32 [M, ceil(K/128)]; b: e4m3 [N, K] row-major (a Linear weight), b_s fp32
+ * [ceil(N/128), ceil(K/128)]; c: [M, N] of out_dtype; bias NULL or [N] of bias_dtype. The K block is 128 as in the
+ * reference kernel (BLOCK_SIZE_K = 128, b_s indexed by offs_n // 128). fp32 accumulation: each K block is contracted by
+ * the tensor pipe into TMEM and promoted with one FMA by (a_s * b_s). K % 16 == 0 and 16-byte aligned a / b (TMA).
+ */
+int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias, int64_t M,
+                 int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* stream);
+
+/*
  * GPTQ Hessian accumulation  S += X^T X   (upper 128x128 blocks of S only; SYRK)
  * X is the layer input flattened to [tokens, C] row-major (the reference transposes a view of it, gptq.py:265-267),
  * f32 / f16 / bf16. S is fp32 [C, C] row-major, zero-initialised by the caller, and holds the UN-NORMALISED running

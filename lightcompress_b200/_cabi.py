@@ -36,6 +36,8 @@ SIGNATURES = {
                                      ctypes.c_double, ctypes.c_float, _c_vp]),
     'lcb_fakequant_multi': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i32, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
+    'lcb_act_quant_fp8': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp]),
+    'lcb_fp8_gemm': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp, _c_vp]),
     'lcb_hessian_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i32]),
     'lcb_hessian_finalize': (ctypes.c_int, [_c_vp, _c_i64, ctypes.c_double, _c_vp]),

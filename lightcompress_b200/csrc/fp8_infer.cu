@@ -1,0 +1,411 @@
+// fp8_infer.cu — the block-wise FP8 inference step next to the quantization path:
+//   lcb_act_quant_fp8  = act_quant  (kernel.py:7-54):    per-128 activation groups -> e4m3 codes + fp32 scales, HBM bound
+//   lcb_fp8_gemm       = fp8_gemm   (kernel.py:140-242) (+ the bias add of block_wise_fp8_forward_func,
+//                        module_utils.py:41-46): C = sum_kb (A8[:, kb] . B8[:, kb]^T) * a_s[:, kb] * b_s[n / 128, kb]
+//
+// The GEMM is a persistent warp-specialised tcgen05 kernel. fp32 block scales cannot ride the hardware's block-scaled MMA
+// (that takes UE8M0 / UE4M3 scale factors), so every 128-deep K block is contracted into a FRESH TMEM accumulator stage by
+// tcgen05.mma.kind::f8f6f4 and promoted by the epilogue warps: acc_reg = fma(tmem, a_s * b_s, acc_reg) — the tensor
+// pipe runs K block k + 1 while the CUDA cores promote K block k (2 TMEM stages of 256 columns).
+//   warp 0    : TMA producer, 4-stage ring of (A 128 x 128 B, B 256 x 128 B) e4m3 tiles, 128-byte swizzle, K-major both
+//   warp 1    : MMA issuer (one thread): 4 x (M = 128, N = 256, K = 32) per K block, accumulate flag cleared on the first
+//   warps 4-11: promotion + epilogue: thread = output row (TMEM lane) x 128-column half, 128 fp32 accumulators in
+//               registers (setmaxnreg: 232 for these two warpgroups, 40 for the producer / issuer warpgroup)
+#include "tc.cuh"
+
+namespace lcb {
+namespace f8 {
+
+// ----------------------------------------------------------------------------------------------------------------------
+// act_quant: y = (x / s).to(e4m3), s = max|x| / 448 over each group of `G` consecutive elements (kernel.py:7-29)
+// 8 elements per lane, LANES = G / 8 lanes per group, UNROLL independent groups per lane in flight.
+// ----------------------------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float* f) {
+  if (sizeof(T) == 4) {
+    const uint4 a = ld_stream(p), b = ld_stream(reinterpret_cast<const uint8_t*>(p) + 16);
+    f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y); f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
+    f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y); f[6] = __uint_as_float(b.z); f[7] = __uint_as_float(b.w);
+  } else {
+    const uint4 a = ld_stream(p);
+    TI<T>::unpack(a, f);
+  }
+}
+
+__device__ __forceinline__ uint32_t cvt_e4m3x2(float lo, float hi) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+template <typename T, int LANES, int UNROLL>
+__global__ void __launch_bounds__(256) act_quant_kernel(const T* __restrict__ x, uint8_t* __restrict__ y,
+                                                        float* __restrict__ s_out, int64_t n_groups) {
+  // "slot" = one 8-element chunk; slot v belongs to group v / LANES. A warp covers 32 consecutive slots per step.
+  const int64_t n_slots = n_groups * LANES;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // every lane of a warp runs the same number of iterations (shuffles): loop on the warp's first slot
+  for (int64_t base = tid - (threadIdx.x & 31); base < n_slots; base += stride * UNROLL) {
+    float f[UNROLL][8];
+    bool live[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t v = base + u * stride + (threadIdx.x & 31);
+      live[u] = v < n_slots;
+      if (live[u]) {
+        load8<T>(x + v * 8, f[u]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t v = base + u * stride + (threadIdx.x & 31);
+      float a = fabsf(f[u][0]);
+#pragma unroll
+      for (int i = 1; i < 8; ++i) a = max_nan(a, fabsf(f[u][i]));
+#pragma unroll
+      for (int o = LANES / 2; o > 0; o >>= 1) a = max_nan(a, __shfl_xor_sync(0xffffffffu, a, o));
+      // s = RN(a / 448): Markstein step on RN(1 / 448) inside the normal range (tests/test_fp8_infer_oracle.py proves it
+      // over every bf16 value and 2e7 random fp32 values), IEEE division otherwise
+      float s;
+      const bool fast = a >= 1e-17f && a <= 1e22f;
+      if (fast) {
+        const float r448 = 1.0f / 448.0f;
+        const float q0 = __fmul_rn(a, r448);
+        s = __fmaf_rn(__fmaf_rn(-448.0f, q0, a), r448, q0);
+      } else {
+        s = __fdiv_rn(a, 448.0f);
+      }
+      uint32_t w[2];
+      if (fast) {   // then 1e-20 < s < 1e20: the Markstein residual of x / s is exact
+        // RN(x / s) by a Markstein step on the correctly rounded reciprocal (fq_math.cuh; tests/test_fq_math_identity.py)
+        const float r = __frcp_rn(s);
+        float qv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float q0 = __fmul_rn(f[u][i], r);
+          qv[i] = __fmaf_rn(__fmaf_rn(-s, q0, f[u][i]), r, q0);
+        }
+        w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
+        w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
+      } else {  // s == 0 (all-zero group: 0 / 0 = NaN like the reference), denormal / huge / NaN scales: IEEE division
+        float qv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) qv[i] = __fdiv_rn(f[u][i], s);
+        w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
+        w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
+      }
+      if (live[u]) {
+        *reinterpret_cast<uint2*>(y + v * 8) = make_uint2(w[0], w[1]);
+        if ((v % LANES) == 0) s_out[v / LANES] = s;
+      }
+    }
+  }
+}
+
+template <typename T, int LANES>
+int launch_act_quant(const void* x, void* y, float* s, int64_t n_groups, cudaStream_t st) {
+  constexpr int UNROLL = 4;
+  const int64_t n_slots = n_groups * LANES;
+  int64_t blocks = (n_slots + 256 * UNROLL - 1) / (256 * UNROLL);
+  const int64_t cap = (int64_t)kNumSMs * 8;
+  const int grid = (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+  act_quant_kernel<T, LANES, UNROLL><<<grid, 256, 0, st>>>(reinterpret_cast<const T*>(x), reinterpret_cast<uint8_t*>(y), s, n_groups);
+  LCB_CUDA_CHECK_LAUNCH("act_quant_fp8");
+  return LCB_OK;
+}
+
+template <typename T>
+int dispatch_act_quant(const void* x, void* y, float* s, int64_t n_groups, int64_t group, cudaStream_t st) {
+  switch (group) {
+    case 8: return launch_act_quant<T, 1>(x, y, s, n_groups, st);
+    case 16: return launch_act_quant<T, 2>(x, y, s, n_groups, st);
+    case 32: return launch_act_quant<T, 4>(x, y, s, n_groups, st);
+    case 64: return launch_act_quant<T, 8>(x, y, s, n_groups, st);
+    case 128: return launch_act_quant<T, 16>(x, y, s, n_groups, st);
+    case 256: return launch_act_quant<T, 32>(x, y, s, n_groups, st);
+    default: return LCB_E_UNSUPPORTED;
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------------------
+// fp8_gemm
+// ----------------------------------------------------------------------------------------------------------------------
+constexpr int BM = 128, BN = 256, BKB = 128;          // BKB: K block in elements == bytes == one 128B swizzle row
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BKB, B_BYTES = BN * BKB, STAGE_BYTES = A_BYTES + B_BYTES;   // 48 KB
+constexpr int NACC = 512 / BN;                        // TMEM accumulator stages
+constexpr int EPI_WARPS = 8;                          // two per TMEM lane quarter: one waits on tcgen05.ld, one runs FMAs
+constexpr int EPI_COLS = BN / (EPI_WARPS / 4);        // accumulator columns per epilogue thread
+constexpr int FIRST_EPI_WARP = 4;
+constexpr int NTHREADS = (FIRST_EPI_WARP + EPI_WARPS) * 32;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 + 1024;
+
+struct Params {
+  int M, N, K;
+  int nblk_i, nblk_j, n_tiles, nkb, nsb;   // nsb = ceil(N / 128) rows of b_s
+  const float* a_s;   // [M, nkb]
+  const float* b_s;   // [ceil(N / 128), nkb]
+  void* c;            // [M, N], leading dimension ldc
+  int64_t ldc;
+  const void* bias;   // NULL or [N]
+  int bias_dtype;
+  uint32_t idesc;
+};
+struct Maps {
+  CUtensorMap a, b;
+};
+
+__device__ __forceinline__ void mma_f8_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// kind::f8f6f4 instruction descriptor: D fp32 (bit 4), A / B e4m3 (0) or e5m2 (1), both K-major
+__host__ __device__ constexpr uint32_t idesc_f8(int afmt, int bfmt, int M_, int N_) {
+  return (1u << 4) | ((uint32_t)afmt << 7) | ((uint32_t)bfmt << 10) | ((uint32_t)(N_ >> 3) << 17) | ((uint32_t)(M_ >> 4) << 24);
+}
+
+template <typename TO>
+__global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_constant__ Maps maps, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tfull = empty + STAGES;
+  uint64_t* tempty = tfull + NACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + NACC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tc::tma_prefetch_desc(&maps.a);
+    tc::tma_prefetch_desc(&maps.b);
+    for (int s = 0; s < STAGES; ++s) {
+      tc::mbar_init(&full[s], 1);
+      tc::mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < NACC; ++a) {
+      tc::mbar_init(&tfull[a], 1);
+      tc::mbar_init(&tempty[a], EPI_WARPS);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int nkb = p.nkb;
+
+  if (warp < FIRST_EPI_WARP) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+        // consecutive CTAs share the B (weight) column block: tile index runs over row blocks fastest
+        const int ti = t % p.nblk_i, tj = t / p.nblk_i;
+        for (int kb = 0; kb < nkb; ++kb) {
+          tc::mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          tc::mbar_expect_tx(&full[stage], STAGE_BYTES);
+          tc::tma_load_2d(sa, &maps.a, &full[stage], kb * BKB, ti * BM);
+          tc::tma_load_2d(sa + A_BYTES, &maps.b, &full[stage], kb * BKB, tj * BN);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);   // K-major SWIZZLE_128B: 8-row groups 1024 B apart
+    for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc::mbar_wait(&full[stage], phase);
+        tc::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+          const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
+#pragma unroll
+          for (int k = 0; k < BKB / 32; ++k)   // K = 32 e4m3 per instruction = 32 B along the swizzled row
+            mma_f8_ss(d_tmem, tc::smem_desc_at(desc_k, sa + k * 32), tc::smem_desc_at(desc_k, sb + k * 32), p.idesc, k != 0 ? 1u : 0u);
+          tc::mma_commit(&empty[stage]);
+          tc::mma_commit(&tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+        if (++acc == NACC) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    // ===== promotion + epilogue =====
+    const int q = warp & 3;   // TMEM lane quarter of this warp
+    const int ch = ((warp - FIRST_EPI_WARP) >> 2) * EPI_COLS;   // first accumulator column of this warp
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float accv[EPI_COLS];
+    for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+      const int ti = t % p.nblk_i, tj = t / p.nblk_i;
+      const int row = ti * BM + q * 32 + lane;
+      const float* asp = p.a_s + (int64_t)min(row, p.M - 1) * nkb;
+      // weight scale block of this warp's 128 columns (clamped for the half tile past the ragged edge: nothing is stored)
+      const float* bsp = p.b_s + (int64_t)min((tj * BN + ch) >> 7, p.nsb - 1) * nkb;
+#pragma unroll
+      for (int j = 0; j < EPI_COLS; ++j) accv[j] = 0.f;
+      float sc = __fmul_rn(asp[0], bsp[0]);
+#pragma unroll 1
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int kn = min(kb + 1, nkb - 1);
+        const float sc_next = __fmul_rn(__ldg(asp + kn), __ldg(bsp + kn));
+        tc::mbar_wait(&tfull[acc], acc_phase);
+        tc::tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + ch);
+#pragma unroll
+        for (int c = 0; c < EPI_COLS / 64; ++c) {
+          uint32_t v0[32], v1[32];
+          tc::tmem_ld_32x32(taddr + c * 64, v0);
+          tc::tmem_ld_32x32(taddr + c * 64 + 32, v1);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) accv[c * 64 + j] = __fmaf_rn(__uint_as_float(v0[j]), sc, accv[c * 64 + j]);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) accv[c * 64 + 32 + j] = __fmaf_rn(__uint_as_float(v1[j]), sc, accv[c * 64 + 32 + j]);
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&tempty[acc]);
+        if (++acc == NACC) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+        sc = sc_next;
+      }
+      // ---- store: round to the output dtype, then the bias add of block_wise_fp8_forward_func (y += bias) ----
+      if (row < p.M) {
+        const int col0 = tj * BN + ch;
+        TO* crow = reinterpret_cast<TO*>(p.c) + (int64_t)row * p.ldc + col0;
+        constexpr int V = TI<TO>::VEC;
+        const bool vec_ok = (p.ldc % V == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
+#pragma unroll
+        for (int c = 0; c < EPI_COLS; c += V) {
+          float o[V];
+#pragma unroll
+          for (int i = 0; i < V; ++i) o[i] = TI<TO>::rd(accv[c + i]);
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+              if (col0 + c + i < p.N) o[i] = TI<TO>::rd(__fadd_rn(o[i], load_rt(p.bias, col0 + c + i, p.bias_dtype)));
+          }
+          if (vec_ok && col0 + c + V <= p.N) {
+            *reinterpret_cast<uint4*>(crow + c) = TI<TO>::pack(o);
+          } else {
+#pragma unroll
+            for (int i = 0; i < V; ++i)
+              if (col0 + c + i < p.N) TI<TO>::store1(crow + c + i, o[i]);
+          }
+        }
+      }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <typename TO>
+int launch_gemm(const Maps& maps, const Params& p, int grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(fp8_gemm_kernel<TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) {
+      set_last_error("cudaFuncSetAttribute(fp8_gemm)", cudaGetLastError());
+      return LCB_E_CUDA;
+    }
+    attr_set = true;
+  }
+  fp8_gemm_kernel<TO><<<grid, NTHREADS, SMEM_BYTES, st>>>(maps, p);
+  LCB_CUDA_CHECK_LAUNCH("fp8_gemm");
+  return LCB_OK;
+}
+
+}  // namespace f8
+}  // namespace lcb
+
+extern "C" int lcb_act_quant_fp8(const void* x, void* y, float* scales, int64_t n_groups, int64_t group, int32_t dtype,
+                                 void* stream) {
+  using namespace lcb;
+  if (n_groups == 0) return LCB_OK;
+  if (!x || !y || !scales || n_groups < 0) return LCB_E_INVALID;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || (reinterpret_cast<uintptr_t>(y) & 7)) return LCB_E_ALIGN;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == LCB_BF16) return f8::dispatch_act_quant<__nv_bfloat16>(x, y, scales, n_groups, group, st);
+  if (dtype == LCB_F16) return f8::dispatch_act_quant<__half>(x, y, scales, n_groups, group, st);
+  if (dtype == LCB_F32) return f8::dispatch_act_quant<float>(x, y, scales, n_groups, group, st);
+  return LCB_E_UNSUPPORTED;
+}
+
+extern "C" int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias,
+                            int64_t M, int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* stream) {
+  using namespace lcb;
+  using namespace lcb::f8;
+  if (M == 0 || N == 0) return LCB_OK;
+  if (!a || !a_s || !b || !b_s || !c || M < 0 || N < 0 || K <= 0) return LCB_E_INVALID;
+  if (M > (1 << 30) || N > (1 << 30) || K > (1 << 30)) return LCB_E_SHAPE;
+  if ((K % 16) || (reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15)) return LCB_E_ALIGN;   // TMA pitch
+  if (bias && bias_dtype != LCB_F32 && bias_dtype != LCB_F16 && bias_dtype != LCB_BF16) return LCB_E_UNSUPPORTED;
+  Maps maps;
+  Params p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K = (int)K;
+  p.nblk_i = (int)((M + BM - 1) / BM);
+  p.nblk_j = (int)((N + BN - 1) / BN);
+  p.n_tiles = p.nblk_i * p.nblk_j;
+  p.nkb = (int)((K + BKB - 1) / BKB);
+  p.nsb = (int)((N + 127) / 128);
+  p.a_s = a_s;
+  p.b_s = b_s;
+  p.c = c;
+  p.ldc = N;
+  p.bias = bias;
+  p.bias_dtype = bias_dtype;
+  p.idesc = idesc_f8(0, 0, BM, BN);
+  bool ok = make_tmap_2d(&maps.a, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, K, K, BM, BKB) &&
+            make_tmap_2d(&maps.b, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, K, K, BN, BKB);
+  if (!ok) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return LCB_E_CUDA;
+  }
+  const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (out_dtype == LCB_BF16) return launch_gemm<__nv_bfloat16>(maps, p, grid, st);
+  if (out_dtype == LCB_F16) return launch_gemm<__half>(maps, p, grid, st);
+  if (out_dtype == LCB_F32) return launch_gemm<float>(maps, p, grid, st);
+  return LCB_E_UNSUPPORTED;
+}
