@@ -140,7 +140,18 @@ def extras(torch, dev, tf_peak):
     cand = (torch.rand(4, C, device=dev, generator=g) + 0.5).to(torch.bfloat16)
     wq = IntegerQuantizer(4, False, 'per_group', group_size=128)
     t = ev(lambda: ops.awq_candidates(Wb, x, org, cand, wq), 3) / 4
-    del x, S, W, Wb, org, cand, Hinv, Hw
+    # block-wise FP8 inference step: act_quant (HBM bound) and the fp8 GEMM with fp32 block scales
+    from lightcompress_b200 import fp8_infer as fi
+    xa = torch.randn(8192, 7168, device=dev, generator=g).to(torch.bfloat16)
+    ta = ev(lambda: fi.act_quant(xa), 20)
+    a8, as8 = fi.act_quant(xa)
+    b8 = (torch.randn(2048, 7168, device=dev, generator=g) * 50).clamp(-448, 448).to(torch.float8_e4m3fn)
+    bs8 = torch.rand(16, 56, device=dev, generator=g) * 0.01 + 1e-3
+    tg = ev(lambda: fi.fp8_gemm(a8, as8, b8, bs8, out_dtype=torch.bfloat16), 10)
+    aq_bytes = xa.numel() * 3 + xa.numel() // 128 * 4
+    res['fp8_act_quant'] = {'shape': [8192, 7168], 'ms': ta * 1e3, 'GBps': aq_bytes / ta / 1e9}
+    res['fp8_gemm'] = {'M': 8192, 'N': 2048, 'K': 7168, 'ms': tg * 1e3, 'TFLOPs': 2.0 * 8192 * 2048 * 7168 / tg / 1e12}
+    del x, S, W, Wb, org, cand, Hinv, Hw, xa, a8, as8, b8, bs8
     torch.cuda.empty_cache()
     sys.path.insert(0, os.path.join(ROOT, 'tools'))
     import gptq_bench   # GPTQ calibration of one Llama-3-8B block: 128 x 2048 tokens, 7 linears (BASELINE configs[1])

@@ -20,95 +20,136 @@ namespace f8 {
 // act_quant: y = (x / s).to(e4m3), s = max|x| / 448 over each group of `G` consecutive elements (kernel.py:7-29)
 // 8 elements per lane, LANES = G / 8 lanes per group, UNROLL independent groups per lane in flight.
 // ----------------------------------------------------------------------------------------------------------------------
-template <typename T>
-__device__ __forceinline__ void load8(const T* p, float* f) {
-  if (sizeof(T) == 4) {
-    const uint4 a = ld_stream(p), b = ld_stream(reinterpret_cast<const uint8_t*>(p) + 16);
-    f[0] = __uint_as_float(a.x); f[1] = __uint_as_float(a.y); f[2] = __uint_as_float(a.z); f[3] = __uint_as_float(a.w);
-    f[4] = __uint_as_float(b.x); f[5] = __uint_as_float(b.y); f[6] = __uint_as_float(b.z); f[7] = __uint_as_float(b.w);
-  } else {
-    const uint4 a = ld_stream(p);
-    TI<T>::unpack(a, f);
-  }
-}
-
 __device__ __forceinline__ uint32_t cvt_e4m3x2(float lo, float hi) {
   uint16_t r;
   asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
   return r;
 }
 
+// cold path of one 8-element slot: s == 0 (all-zero group: 0 / 0 = NaN like the reference), denormal / huge / NaN / inf
+// ranges — IEEE divisions throughout
+__device__ __noinline__ uint4 act_quant_slot_exact(float f0, float f1, float f2, float f3, float f4, float f5, float f6,
+                                                   float f7, float a) {   // by value: nothing of the hot path lives in local memory
+  const float s = __fdiv_rn(a, 448.0f);
+  uint4 r;
+  r.x = cvt_e4m3x2(__fdiv_rn(f0, s), __fdiv_rn(f1, s)) | (cvt_e4m3x2(__fdiv_rn(f2, s), __fdiv_rn(f3, s)) << 16);
+  r.y = cvt_e4m3x2(__fdiv_rn(f4, s), __fdiv_rn(f5, s)) | (cvt_e4m3x2(__fdiv_rn(f6, s), __fdiv_rn(f7, s)) << 16);
+  r.z = __float_as_uint(s);
+  r.w = 0;
+  return r;
+}
+
+// max |x| over the 8 values of a slot. 16-bit inputs: on the packed words (|x| by clearing the sign bits, NaN-propagating
+// packed max), one unpack at the end.
+template <typename T>
+__device__ __forceinline__ float absmax8(const uint4& raw, const float* f) {
+  if (sizeof(T) == 4) {
+    float a = fabsf(f[0]);
+#pragma unroll
+    for (int i = 1; i < 8; ++i) a = max_nan(a, fabsf(f[i]));
+    return a;
+  } else if (TI<T>::ID == LCB_BF16) {
+    const uint32_t m = 0x7fff7fffu;
+    uint32_t x0 = raw.x & m, x1 = raw.y & m, x2 = raw.z & m, x3 = raw.w & m, r0, r1, r2;
+    asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(r0) : "r"(x0), "r"(x1));
+    asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(r1) : "r"(x2), "r"(x3));
+    asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(r2) : "r"(r0), "r"(r1));
+    return max_nan(__uint_as_float(r2 << 16), __uint_as_float(r2 & 0xffff0000u));
+  } else {
+    const uint32_t m = 0x7fff7fffu;
+    uint32_t x0 = raw.x & m, x1 = raw.y & m, x2 = raw.z & m, x3 = raw.w & m, r0, r1, r2;
+    asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(r0) : "r"(x0), "r"(x1));
+    asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(r1) : "r"(x2), "r"(x3));
+    asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(r2) : "r"(r0), "r"(r1));
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&r2));
+    return max_nan(t.x, t.y);
+  }
+}
+
+// One warp-chunk = UNROLL rows of 32 consecutive slots (slot = 8 elements; slot v belongs to group v / LANES), so that
+// every access of a chunk is the chunk pointer + lane offset + a compile-time immediate. FULL = false: the last, partial
+// chunk (per-slot guards).
+template <typename T, int LANES, int UNROLL, bool FULL>
+__device__ __forceinline__ void act_quant_chunk(const uint8_t* __restrict__ xp, uint8_t* __restrict__ yp,
+                                                float* __restrict__ sp, int lane, int n_live) {
+  constexpr int rs = 32;   // slots between the rows of a chunk
+  constexpr int SLOT_BYTES = 8 * (int)sizeof(T);
+  constexpr int NR = sizeof(T) == 4 ? 2 : 1;
+  uint4 raw[UNROLL][NR];
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    if (FULL || u * rs + lane < n_live) {
+#pragma unroll
+      for (int h = 0; h < NR; ++h) raw[u][h] = ld_stream(xp + (u * rs) * SLOT_BYTES + h * 16);
+    } else {
+#pragma unroll
+      for (int h = 0; h < NR; ++h) raw[u][h] = make_uint4(0, 0, 0, 0);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    float f[8];
+    if (sizeof(T) == 4) {
+      TI<float>::unpack(raw[u][0], f);
+      TI<float>::unpack(raw[u][NR - 1], f + 4);
+    } else {
+      TI<T>::unpack(raw[u][0], f);
+    }
+    float a = absmax8<T>(raw[u][0], f);
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) a = max_nan(a, __shfl_xor_sync(0xffffffffu, a, o));
+    uint32_t w[2];
+    float s;
+    // fast path (warp-uniform): every group of the warp has 1e-17 <= amax <= 1e22, so that s = RN(a / 448) and RN(x / s)
+    // are Markstein steps on correctly rounded reciprocals (tests/test_fp8_infer_oracle.py, tests/test_fq_math_identity.py)
+    if (__all_sync(0xffffffffu, a >= 1e-17f && a <= 1e22f)) {
+      const float r448 = 1.0f / 448.0f;
+      const float s0 = __fmul_rn(a, r448);
+      s = __fmaf_rn(__fmaf_rn(-448.0f, s0, a), r448, s0);
+      const float r = __frcp_rn(s);
+      float qv[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float q0 = __fmul_rn(f[i], r);
+        qv[i] = __fmaf_rn(__fmaf_rn(-s, q0, f[i]), r, q0);
+      }
+      w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
+      w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
+    } else {
+      const uint4 e = act_quant_slot_exact(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], a);
+      w[0] = e.x;
+      w[1] = e.y;
+      s = __uint_as_float(e.z);
+    }
+    if (FULL || u * rs + lane < n_live) {
+      *reinterpret_cast<uint2*>(yp + (u * rs) * 8) = make_uint2(w[0], w[1]);
+      if ((lane % LANES) == 0) sp[u * (rs / LANES)] = s;
+    }
+  }
+}
+
 template <typename T, int LANES, int UNROLL>
 __global__ void __launch_bounds__(256) act_quant_kernel(const T* __restrict__ x, uint8_t* __restrict__ y,
                                                         float* __restrict__ s_out, int64_t n_groups) {
-  // "slot" = one 8-element chunk; slot v belongs to group v / LANES. A warp covers 32 consecutive slots per step.
+  constexpr int SLOT_BYTES = 8 * (int)sizeof(T);
+  constexpr int CHUNK = 32 * UNROLL;   // slots per warp-chunk: UNROLL adjacent rows of 32 slots (2 KB of bf16 per warp)
   const int64_t n_slots = n_groups * LANES;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // every lane of a warp runs the same number of iterations (shuffles): loop on the warp's first slot
-  for (int64_t base = tid - (threadIdx.x & 31); base < n_slots; base += stride * UNROLL) {
-    float f[UNROLL][8];
-    bool live[UNROLL];
-#pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-      const int64_t v = base + u * stride + (threadIdx.x & 31);
-      live[u] = v < n_slots;
-      if (live[u]) {
-        load8<T>(x + v * 8, f[u]);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) f[u][i] = 0.f;
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < UNROLL; ++u) {
-      const int64_t v = base + u * stride + (threadIdx.x & 31);
-      float a = fabsf(f[u][0]);
-#pragma unroll
-      for (int i = 1; i < 8; ++i) a = max_nan(a, fabsf(f[u][i]));
-#pragma unroll
-      for (int o = LANES / 2; o > 0; o >>= 1) a = max_nan(a, __shfl_xor_sync(0xffffffffu, a, o));
-      // s = RN(a / 448): Markstein step on RN(1 / 448) inside the normal range (tests/test_fp8_infer_oracle.py proves it
-      // over every bf16 value and 2e7 random fp32 values), IEEE division otherwise
-      float s;
-      const bool fast = a >= 1e-17f && a <= 1e22f;
-      if (fast) {
-        const float r448 = 1.0f / 448.0f;
-        const float q0 = __fmul_rn(a, r448);
-        s = __fmaf_rn(__fmaf_rn(-448.0f, q0, a), r448, q0);
-      } else {
-        s = __fdiv_rn(a, 448.0f);
-      }
-      uint32_t w[2];
-      if (fast) {   // then 1e-20 < s < 1e20: the Markstein residual of x / s is exact
-        // RN(x / s) by a Markstein step on the correctly rounded reciprocal (fq_math.cuh; tests/test_fq_math_identity.py)
-        const float r = __frcp_rn(s);
-        float qv[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float q0 = __fmul_rn(f[u][i], r);
-          qv[i] = __fmaf_rn(__fmaf_rn(-s, q0, f[u][i]), r, q0);
-        }
-        w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
-        w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
-      } else {  // s == 0 (all-zero group: 0 / 0 = NaN like the reference), denormal / huge / NaN scales: IEEE division
-        float qv[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) qv[i] = __fdiv_rn(f[u][i], s);
-        w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
-        w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
-      }
-      if (live[u]) {
-        *reinterpret_cast<uint2*>(y + v * 8) = make_uint2(w[0], w[1]);
-        if ((v % LANES) == 0) s_out[v / LANES] = s;
-      }
-    }
+  const int64_t n_chunks = (n_slots + CHUNK - 1) / CHUNK;
+  const int lane = threadIdx.x & 31;
+  const int64_t n_warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t c = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < n_chunks; c += n_warps) {
+    const int64_t v0 = c * CHUNK;
+    const uint8_t* xp = reinterpret_cast<const uint8_t*>(x) + (v0 + lane) * SLOT_BYTES;
+    uint8_t* yp = y + (v0 + lane) * 8;
+    float* sp = s_out + (v0 + lane) / LANES;
+    if (v0 + CHUNK <= n_slots) act_quant_chunk<T, LANES, UNROLL, true>(xp, yp, sp, lane, CHUNK);
+    else act_quant_chunk<T, LANES, UNROLL, false>(xp, yp, sp, lane, (int)(n_slots - v0));
   }
 }
 
 template <typename T, int LANES>
 int launch_act_quant(const void* x, void* y, float* s, int64_t n_groups, cudaStream_t st) {
-  constexpr int UNROLL = 4;
+  constexpr int UNROLL = sizeof(T) == 4 ? 2 : 4;   // 64 B of loads in flight per lane (sweep: profiles/r1_fp8_bench.jsonl)
   const int64_t n_slots = n_groups * LANES;
   int64_t blocks = (n_slots + 256 * UNROLL - 1) / (256 * UNROLL);
   const int64_t cap = (int64_t)kNumSMs * 8;
