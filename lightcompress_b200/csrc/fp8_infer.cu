@@ -324,16 +324,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
         tc::mbar_wait(&tfull[acc], acc_phase);
         tc::tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + ch);
+        // software pipeline over 32-column chunks: the tcgen05.ld of chunk c + 1 is in flight while chunk c is promoted
+        uint32_t v0[32], v1[32];
+        tc::tmem_ld_32x32(taddr, v0);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int c = 0; c < EPI_COLS / 64; ++c) {
-          uint32_t v0[32], v1[32];
-          tc::tmem_ld_32x32(taddr + c * 64, v0);
-          tc::tmem_ld_32x32(taddr + c * 64 + 32, v1);
+        for (int c = 0; c < EPI_COLS / 32; c += 2) {
+          tc::tmem_ld_32x32(taddr + (c + 1) * 32, v1);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) accv[c * 32 + j] = __fmaf_rn(__uint_as_float(v0[j]), sc, accv[c * 32 + j]);
           tc::tmem_ld_wait();
+          if (c + 2 < EPI_COLS / 32) tc::tmem_ld_32x32(taddr + (c + 2) * 32, v0);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) accv[c * 64 + j] = __fmaf_rn(__uint_as_float(v0[j]), sc, accv[c * 64 + j]);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) accv[c * 64 + 32 + j] = __fmaf_rn(__uint_as_float(v1[j]), sc, accv[c * 64 + 32 + j]);
+          for (int j = 0; j < 32; ++j) accv[(c + 1) * 32 + j] = __fmaf_rn(__uint_as_float(v1[j]), sc, accv[(c + 1) * 32 + j]);
+          if (c + 2 < EPI_COLS / 32) tc::tmem_ld_wait();
         }
         tc::tc_fence_before();
         __syncwarp();

@@ -57,12 +57,18 @@ def main():
         ms = timeit(lambda: fi.fp8_gemm(a, a_s, b, b_s, out_dtype=torch.bfloat16), flush=flush)
         xa, xb = a.bfloat16(), b.bfloat16()
         ms_cublas = timeit(lambda: torch.nn.functional.linear(xa, xb), flush=flush)
+        try:   # cuBLASLt fp8 with per-tensor scales: the library's fp8 tensor-pipe rate on this chip (not the same op)
+            one = torch.ones((), device=dev)
+            ms_lt = timeit(lambda: torch._scaled_mm(a, b.t(), one, one, out_dtype=torch.bfloat16), flush=flush)
+        except Exception:
+            ms_lt = None
         x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
         ms_fwd = timeit(lambda: fi.block_wise_fp8_forward_func(x, b, b_s, 128, None), flush=flush)
         fl = 2.0 * M * N * K
         lines.append({'kernel': 'fp8_gemm', 'M': M, 'N': N, 'K': K, 'ms': ms, 'TFLOPs': fl / ms / 1e9,
                       'frac_of_fp8_nominal_4500': fl / ms / 1e9 / 4500.0, 'cublas_bf16_ms': ms_cublas,
                       'cublas_bf16_TFLOPs': fl / ms_cublas / 1e9, 'forward_func_ms': ms_fwd,
+                      'cublaslt_fp8_per_tensor_TFLOPs': None if ms_lt is None else fl / ms_lt / 1e9,
                       'weight_bytes_GBps': (N * K + M * K + 2 * M * N) / ms / 1e6})
     for ln in lines:
         print(json.dumps(ln))
