@@ -10,6 +10,8 @@
 //   fq_static_kernel  : scales / zeros given (fake_quant_*_static, per_tensor phase 2), pure elementwise.
 //   fq_generic_kernel : any unit shape / alignment / exotic spec; literal arithmetic, warp per unit.
 //   minmax kernels    : per_tensor phase 1.
+#include <type_traits>
+#include "tc.cuh"
 #include "fq_math.cuh"
 
 namespace lcb {

@@ -204,6 +204,27 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
     if (tiles > 0x7fffffff) return LCB_E_SHAPE;
     if (kindc == 1 && sp.osf == 1.0f && (sp.out_mode == LCB_OUT_FAKE || sp.out_mode == LCB_OUT_FP8)) {
       const bool e5 = sp.kind == LCB_KIND_FP8_E5M2, codes = sp.out_mode == LCB_OUT_FP8;
+      if (sizeof(T) == 2 && cols % 8 == 0 && rows < (1ll << 31) && cols < (1ll << 31)) {
+        // TMA-staged tiles (16-byte row pitch): no swizzle, box 128 rows x 128 elements, out-of-bounds = zeros
+        CUtensorMap tm;
+        lcb_encode_tiled_fn enc = get_encode_tiled();
+        const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+        const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+        const cuuint32_t box[2] = {128, 128};
+        const cuuint32_t estr[2] = {1, 1};
+        if (enc && enc(&tm, TI<T>::ID == LCB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                       const_cast<T*>(in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                       CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS) {
+          using T16 = typename std::conditional<sizeof(T) == 2, T, __nv_bfloat16>::type;
+          void* tm_out = out;
+          if (!e5 && !codes) fq_block2d_fp8_tma_kernel<T16, 0, 0><<<(int)tiles, 256, 0, st>>>(tm, tm_out, scales, rows, cols, sp);
+          else if (!e5 && codes) fq_block2d_fp8_tma_kernel<T16, 0, 1><<<(int)tiles, 256, 0, st>>>(tm, tm_out, scales, rows, cols, sp);
+          else if (e5 && !codes) fq_block2d_fp8_tma_kernel<T16, 1, 0><<<(int)tiles, 256, 0, st>>>(tm, tm_out, scales, rows, cols, sp);
+          else fq_block2d_fp8_tma_kernel<T16, 1, 1><<<(int)tiles, 256, 0, st>>>(tm, tm_out, scales, rows, cols, sp);
+          LCB_CUDA_CHECK_LAUNCH("fq_block2d_fp8_tma");
+          return LCB_OK;
+        }
+      }
       if (!e5 && !codes) fq_block2d_fp8_kernel<T, 0, 0><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
       else if (!e5 && codes) fq_block2d_fp8_kernel<T, 0, 1><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
       else if (e5 && !codes) fq_block2d_fp8_kernel<T, 1, 0><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);

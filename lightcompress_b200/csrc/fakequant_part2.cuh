@@ -207,6 +207,110 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Same arithmetic, 16-bit inputs, tile STAGED IN SHARED MEMORY BY TMA (one cp.async.bulk.tensor of the 128 x 128 box per
+// CTA: ragged edges arrive zero-filled = the reference's zero padding, quant.py:632-642). The register version above
+// keeps the tile in 8 vectors per thread across the CTA reduction, which costs it 128 registers and leaves 2 CTAs
+// (64 KB of loads) per SM; here nothing is live across the reduction (both passes read shared memory), so 5-6 CTAs of
+// 32 KB are resident per SM.
+template <typename T, int E5M2, int OUT_CODES>
+__global__ void __launch_bounds__(256)
+    fq_block2d_fp8_tma_kernel(const __grid_constant__ CUtensorMap tm, void* __restrict__ out, void* __restrict__ scales,
+                              int64_t rows, int64_t cols, SpecD sp) {
+  constexpr int VEC = 8, BS = 128, VPR = BS / VEC, RPP = 256 / VPR, NP = BS / RPP;
+  static_assert(sizeof(T) == 2, "16-bit inputs");
+  __shared__ __align__(128) uint8_t tile[BS * BS * 2];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ float red[64];
+  const int64_t ncb = (cols + BS - 1) / BS;
+  const int64_t bi = blockIdx.x / ncb, bj = blockIdx.x % ncb;
+  const int vr = threadIdx.x / VPR, vc = threadIdx.x % VPR;
+  if (threadIdx.x == 0) {
+    tc::mbar_init(&bar, 1);
+    tc::fence_barrier_init();
+    tc::mbar_expect_tx(&bar, BS * BS * 2);
+    tc::tma_load_2d(tile, &tm, &bar, (int32_t)(bj * BS), (int32_t)(bi * BS));
+  }
+  __syncthreads();
+  tc::mbar_wait(&bar, 0);
+  const uint8_t* mine = tile + vr * (BS * 2) + vc * 16;      // pass p: + p * RPP rows
+  // pass 1: |x| max on the packed words (sign bits cleared, NaN-propagating packed max)
+  uint32_t m2 = 0u;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    const uint4 v = *reinterpret_cast<const uint4*>(mine + p * RPP * (BS * 2));
+    const uint32_t msk = 0x7fff7fffu;
+    uint32_t a = v.x & msk, b = v.y & msk, c = v.z & msk, d = v.w & msk;
+    if (TI<T>::ID == LCB_BF16) {
+      asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(a) : "r"(a), "r"(b));
+      asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(c) : "r"(c), "r"(d));
+      asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(a) : "r"(a), "r"(c));
+      asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(m2) : "r"(m2), "r"(a));
+    } else {
+      asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(a) : "r"(a), "r"(b));
+      asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(c) : "r"(c), "r"(d));
+      asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(a) : "r"(a), "r"(c));
+      asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(m2) : "r"(m2), "r"(a));
+    }
+  }
+  float mx;
+  if (TI<T>::ID == LCB_BF16) {
+    mx = max_nan(__uint_as_float(m2 << 16), __uint_as_float(m2 & 0xffff0000u));
+  } else {
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&m2));
+    mx = max_nan(t.x, t.y);
+  }
+  float mn = mx;
+  block_minmax(mx, mn, red);
+  UnitQ u;
+  qparams_from_range(mx, mx, sp, u);
+  finish_unit(sp, u);
+  if (!finite_f(mx)) u.exact = 1;
+  if (threadIdx.x == 0 && scales) store_rt(scales, blockIdx.x, u.s_out, sp.qparam_dtype);
+  const int64_t col = bj * BS + vc * VEC;
+  if (u.exact) {   // CTA-uniform, rare (non-finite range): the literal chain
+#pragma unroll 1
+    for (int p = 0; p < NP; ++p) {
+      const int64_t row = bi * BS + p * RPP + vr;
+      if (row < rows && col < cols)
+        block_vec_slow<T>(*reinterpret_cast<const uint4*>(mine + p * RPP * (BS * 2)), u, sp, out, row * cols + col);
+    }
+    return;
+  }
+  const float s = u.s, r = u.r, so = u.s_out;
+  if (col >= cols) return;
+#pragma unroll 2
+  for (int p = 0; p < NP; ++p) {
+    const int64_t row = bi * BS + p * RPP + vr;
+    if (row >= rows) break;
+    const int64_t e0 = row * cols + col;
+    float f[VEC];
+    TI<T>::unpack(*reinterpret_cast<const uint4*>(mine + p * RPP * (BS * 2)), f);
+    uint32_t b2[VEC / 2];
+#pragma unroll
+    for (int i = 0; i < VEC; i += 2) {
+      float q[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float q0 = __fmul_rn(f[i + k], r);
+        q[k] = __fadd_rn(__fmaf_rn(__fmaf_rn(-s, q0, f[i + k]), r, q0), 0.0f);   // RN(x / s), -0 -> +0
+      }
+      b2[i / 2] = f32x2_to_fp8x2<E5M2>(q[0], q[1]);
+    }
+    if (OUT_CODES) {
+      *reinterpret_cast<uint2*>(reinterpret_cast<uint8_t*>(out) + e0) = make_uint2(b2[0] | (b2[1] << 16), b2[2] | (b2[3] << 16));
+    } else {
+      float val[VEC];
+#pragma unroll
+      for (int i = 0; i < VEC; i += 2) {
+        const float2 v = fp8x2_to_f32x2<E5M2>(b2[i / 2]);
+        val[i] = __fmul_rn(v.x, so);
+        val[i + 1] = __fmul_rn(v.y, so);
+      }
+      st_stream(reinterpret_cast<T*>(out) + e0, TI<T>::pack(val));
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // generic: warp per 2-D unit, scalar accesses, literal arithmetic. Any shape, any alignment, any spec.
 // ------------------------------------------------------------------------------------------------

@@ -67,6 +67,9 @@ BIG = [
     dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(1408, 2048)),
     dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(576, 2048)),
     dict(cls='fp', bit='e5m2', gran='per_group', kwargs={'group_size': 128}, shape=(256, 2048)),
+    dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(300, 264)),   # ragged both ways (TMA zero fill)
+    dict(cls='fp', bit='e5m2', gran='per_block', kwargs={'block_size': 128}, shape=(130, 72)),
+    dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(64, 100)),    # cols % 8 != 0: register kernel
     dict(cls='int', bit=8, sym=True, gran='per_block', kwargs={'block_size': 128}, shape=(300, 520)),
 ]
 
@@ -173,3 +176,15 @@ def test_multi_tensor_launch_equals_single_launches():
     qc = Q.IntegerQuantizer(8, True, 'per_channel')
     for w, m in zip(ws, qc.fake_quant_weights_dynamic(ws)):
         assert H.bits_equal(m.cpu(), qc.fake_quant_weight_dynamic(w).cpu())
+
+
+def test_per_block_fp8_nonfinite_tile_takes_the_literal_chain():
+    """A tile holding inf / NaN goes through the out-of-line literal chain of the TMA-staged kernel; other tiles are untouched."""
+    c = dict(cls='fp', bit='e4m3', gran='per_block', kwargs={'block_size': 128}, shape=(256, 384), dtype='bfloat16', seed=11)
+    x = H.case_input(c)
+    x[3, 5] = float('inf')
+    x[200, 300] = float('nan')
+    q = H.make_quantizer(Q, c)
+    fake = q.fake_quant_weight_dynamic(x.to(DEV)).cpu()
+    ref, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
+    assert H.equal_nan_aware(fake, ref)
