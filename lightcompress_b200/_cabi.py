@@ -35,6 +35,7 @@ SIGNATURES = {
     'lcb_mse_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, ctypes.POINTER(QuantSpec), _c_i32,
                                      ctypes.c_double, ctypes.c_float, _c_vp]),
     'lcb_fakequant_multi': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i32, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
+    'lcb_fakequant_block_fp8_multi': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i32, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_act_quant_fp8': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp]),
     'lcb_fp8_gemm': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),

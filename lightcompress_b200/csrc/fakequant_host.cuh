@@ -249,6 +249,59 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
 }  // namespace lcb
 
 namespace lcb {
+// ---- several 16-bit weights, one launch: FP8 per_block (128 x 128) dynamic fake-quant / real-quant ------------------------
+static bool encode_block_tmap(CUtensorMap* tm, const void* in, int dtype, int64_t rows, int64_t cols) {
+  lcb_encode_tiled_fn enc = get_encode_tiled();
+  if (!enc) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {128, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(tm, dtype == LCB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+             const_cast<void*>(in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <typename T>
+static int fakequant_block_fp8_multi_typed(const void* const* ins, void* const* outs, void* const* scales, const int64_t* rows,
+                                           const int64_t* cols, int n, SpecD sp, cudaStream_t st) {
+  BlockMultiDesc md;
+  md.n = n;
+  md.tile_start[0] = 0;
+  for (int t = 0; t < n; ++t) {
+    if (!ins[t] || !outs[t] || rows[t] < 0 || cols[t] < 0) return LCB_E_INVALID;
+    if (cols[t] % 8 || rows[t] >= (1ll << 31) || cols[t] >= (1ll << 31)) return LCB_E_UNSUPPORTED;
+    if (!aligned16(ins[t]) || !aligned16(outs[t])) return LCB_E_ALIGN;
+    const int64_t tiles = ((rows[t] + 127) / 128) * ((cols[t] + 127) / 128);
+    md.tile_start[t + 1] = md.tile_start[t] + tiles;
+    md.out[t] = outs[t];
+    md.scales[t] = scales ? scales[t] : nullptr;
+    md.rows[t] = rows[t];
+    md.cols[t] = cols[t];
+    if (tiles > 0 && !encode_block_tmap(&md.tm[t], ins[t], TI<T>::ID, rows[t], cols[t])) {
+      set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+      return LCB_E_CUDA;
+    }
+    if (tiles == 0) md.tm[t] = md.tm[0];
+  }
+  for (int t = n; t < kMaxBlockMulti; ++t) {
+    md.tm[t] = md.tm[0];
+    md.out[t] = md.scales[t] = nullptr;
+    md.rows[t] = md.cols[t] = 0;
+    md.tile_start[t + 1] = md.tile_start[n];
+  }
+  const int64_t tiles = md.tile_start[n];
+  if (tiles == 0) return LCB_OK;
+  if (tiles > 0x7fffffff) return LCB_E_SHAPE;
+  const bool e5 = sp.kind == LCB_KIND_FP8_E5M2, codes = sp.out_mode == LCB_OUT_FP8;
+  if (!e5 && !codes) fq_block2d_fp8_tma_multi_kernel<T, 0, 0><<<(int)tiles, 256, 0, st>>>(md, sp);
+  else if (!e5 && codes) fq_block2d_fp8_tma_multi_kernel<T, 0, 1><<<(int)tiles, 256, 0, st>>>(md, sp);
+  else if (e5 && !codes) fq_block2d_fp8_tma_multi_kernel<T, 1, 0><<<(int)tiles, 256, 0, st>>>(md, sp);
+  else fq_block2d_fp8_tma_multi_kernel<T, 1, 1><<<(int)tiles, 256, 0, st>>>(md, sp);
+  LCB_CUDA_CHECK_LAUNCH("fq_block2d_fp8_tma_multi");
+  return LCB_OK;
+}
+
 // ---- several tensors, one launch (per_group / short-row dynamic fake-quant) ----------------------------------------------
 template <typename T>
 static int fakequant_multi_typed(const void* const* ins, void* const* outs, const int64_t* rows, const int64_t* cols, int n,
@@ -321,6 +374,27 @@ extern "C" int lcb_fakequant_multi(const void* const* ins, void* const* outs, co
     case LCB_F32: return fakequant_multi_typed<float>(ins, outs, rows, cols, n, unit_cols, sp, st);
     case LCB_F16: return fakequant_multi_typed<__half>(ins, outs, rows, cols, n, unit_cols, sp, st);
     case LCB_BF16: return fakequant_multi_typed<__nv_bfloat16>(ins, outs, rows, cols, n, unit_cols, sp, st);
+    default: return LCB_E_UNSUPPORTED;
+  }
+}
+
+extern "C" int lcb_fakequant_block_fp8_multi(const void* const* ins, void* const* outs, void* const* scales,
+                                             const int64_t* rows, const int64_t* cols, int32_t n, const lcb_quant_spec* spec,
+                                             void* stream) {
+  using namespace lcb;
+  if (!ins || !outs || !rows || !cols || !spec || n < 0) return LCB_E_INVALID;
+  if (n == 0) return LCB_OK;
+  if (n > kMaxBlockMulti) return LCB_E_UNSUPPORTED;
+  if (!(spec->qmax > spec->qmin)) return LCB_E_INVALID;
+  if ((spec->kind != LCB_KIND_FP8_E4M3 && spec->kind != LCB_KIND_FP8_E5M2) || !spec->sym ||
+      (spec->out_mode != LCB_OUT_FAKE && spec->out_mode != LCB_OUT_FP8) || spec->math_dtype != LCB_F32 ||
+      spec->output_scale_factor != 1.0f || spec->clip_ratio != 1.0f)
+    return LCB_E_UNSUPPORTED;
+  SpecD sp = make_specd(spec);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (spec->dtype) {
+    case LCB_F16: return fakequant_block_fp8_multi_typed<__half>(ins, outs, scales, rows, cols, n, sp, st);
+    case LCB_BF16: return fakequant_block_fp8_multi_typed<__nv_bfloat16>(ins, outs, scales, rows, cols, n, sp, st);
     default: return LCB_E_UNSUPPORTED;
   }
 }

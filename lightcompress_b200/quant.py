@@ -568,6 +568,8 @@ class BaseQuantizer(object):
         tensor for specs / layouts outside the multi-tensor envelope; results are identical either way."""
         import ctypes
         ws = list(weights)
+        if self._block_fp8_multi_ok(ws):
+            return self._block_fp8_multi(ws, _cabi.OUT_FAKE)
         ok = (len(ws) > 0 and self.granularity == 'per_group' and self.calib_algo == 'minmax'
               and all(w.is_cuda and w.is_contiguous() and w.dtype == ws[0].dtype and w.device == ws[0].device
                       and w.dim() >= 1 and w.shape[-1] >= self.group_size and w.shape[-1] % self.group_size == 0
@@ -596,6 +598,50 @@ class BaseQuantizer(object):
                     _cabi.check(st, 'lcb_fakequant_multi')
                 outs_all.extend(outs)
         return outs_all
+
+    def _block_fp8_multi_ok(self, ws):
+        return (len(ws) > 0 and self.granularity == 'per_block' and self._kind() != _cabi.KIND_INT
+                and self.calib_algo != 'hqq' and self.calib_algo != 'mse' and getattr(self, 'block_size', 0) == 128
+                and all(w.is_cuda and w.dim() == 2 and w.is_contiguous() and w.dtype == ws[0].dtype
+                        and w.device == ws[0].device and w.shape[1] % 8 == 0 for w in ws)
+                and ws[0].dtype in (torch.bfloat16, torch.float16))
+
+    def _block_fp8_multi(self, ws, out_mode):
+        """FP8 per_block (128 x 128) dynamic quant of a list of 16-bit weights, 16 per launch
+        (lcb_fakequant_block_fp8_multi). out_mode OUT_FAKE -> [fake weights]; OUT_FP8 -> [(codes, scales, None)]."""
+        import ctypes
+        lib = _cabi._lib or _cabi.load()
+        dt = ws[0].dtype
+        qmin, qmax = self._qrange()
+        spec = self._spec(dt, torch.float32, torch.float32, out_mode, qmin, qmax, 1.0, 1.0, _DT[torch.float32] + 1)
+        res = []
+        real = out_mode == _cabi.OUT_FP8
+        with _on_device(ws[0].device):
+            for i0 in range(0, len(ws), 16):
+                part = ws[i0:i0 + 16]
+                n = len(part)
+                outs = [torch.empty(w.shape, dtype=torch.uint8 if real else dt, device=w.device) for w in part]
+                scs = [torch.empty(((w.shape[0] + 127) // 128, (w.shape[1] + 127) // 128), dtype=torch.float32,
+                                   device=w.device) for w in part] if real else None
+                ins_a = (ctypes.c_void_p * n)(*[w.data_ptr() for w in part])
+                outs_a = (ctypes.c_void_p * n)(*[o.data_ptr() for o in outs])
+                scs_a = (ctypes.c_void_p * n)(*[t.data_ptr() for t in scs]) if real else None
+                rows_a = (ctypes.c_int64 * n)(*[w.shape[0] for w in part])
+                cols_a = (ctypes.c_int64 * n)(*[w.shape[1] for w in part])
+                st = lib.lcb_fakequant_block_fp8_multi(ins_a, outs_a, scs_a, rows_a, cols_a, n, spec,
+                                                       _stream(ws[0].device.index))
+                if st == -3:   # LCB_E_UNSUPPORTED: outside the multi-tensor envelope
+                    if real:
+                        res.extend(self.real_quant_weight_dynamic(w) for w in part)
+                    else:
+                        res.extend(self.fake_quant_weight_dynamic(w) for w in part)
+                    continue
+                _cabi.check(st, 'lcb_fakequant_block_fp8_multi')
+                if real:
+                    res.extend((o.view(self._fp8_dtype()), sc, None) for o, sc in zip(outs, scs))
+                else:
+                    res.extend(outs)
+        return res
 
     def fake_quant_weight_clipped(self, weight, ratio, clip_sym=False):
         """AutoClipper.fake_quantize_weight, clip_version 'v1' (auto_clip.py:258-260) at one shrink step:
@@ -750,6 +796,14 @@ class FloatQuantizer(BaseQuantizer):
         codes, scales, _ = self._dynamic(weight, _cabi.OUT_FP8, torch.uint8, True, osf=osf)
         scales, _ = self._qparams_view(scales, None, codes)
         return codes.view(self._fp8_dtype()), scales, None
+
+    def real_quant_weights_dynamic(self, weights):
+        """Extension (not in the reference API): real_quant_weight_dynamic of a list of weights — FP8 per_block weights go
+        16 per launch (the expert matrices of a MoE block); anything else loops. Same results as the per-tensor calls."""
+        ws = list(weights)
+        if self.bit in ['e4m3', 'e5m2'] and self._block_fp8_multi_ok(ws):
+            return self._block_fp8_multi(ws, _cabi.OUT_FP8)
+        return [self.real_quant_weight_dynamic(w) for w in ws]
 
     def real_quant_weight_static(self, weight, args):
         """quant.py:1161-1193."""

@@ -188,3 +188,26 @@ def test_per_block_fp8_nonfinite_tile_takes_the_literal_chain():
     fake = q.fake_quant_weight_dynamic(x.to(DEV)).cpu()
     ref, _, _ = H.oracle_case(c, x, qo.OUT_FAKE)
     assert H.equal_nan_aware(fake, ref)
+
+
+@pytest.mark.parametrize('bit', ['e4m3', 'e5m2'])
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+def test_block_fp8_multi_launch_equals_single_launches(bit, dtype):
+    """lcb_fakequant_block_fp8_multi (16 weights per launch: MoE experts) == the per-tensor calls, bit for bit."""
+    torch.manual_seed(9)
+    shapes = [(1408, 2048), (2048, 1408), (576, 2048), (130, 72), (128, 128), (1, 8), (300, 264)] * 3    # 21 -> two launches
+    ws = [(torch.randn(s, device=DEV) * (0.02 * (i + 1))).to(dtype) for i, s in enumerate(shapes)]
+    ws[4][5, 7] = float('inf')     # one tile on the literal chain
+    q = Q.FloatQuantizer(bit, True, 'per_block', block_size=128, use_qtorch=True)
+    for w, m in zip(ws, q.fake_quant_weights_dynamic(ws)):
+        assert H.equal_nan_aware(m.cpu(), q.fake_quant_weight_dynamic(w).cpu())
+    for w, (c, s, z) in zip(ws, q.real_quant_weights_dynamic(ws)):
+        c1, s1, z1 = q.real_quant_weight_dynamic(w)
+        assert c.dtype == c1.dtype and z is None and z1 is None and s.shape == s1.shape and s.dtype == s1.dtype
+        assert torch.equal(c.view(torch.uint8), c1.view(torch.uint8))
+        assert H.equal_nan_aware(s.cpu(), s1.cpu())
+    # outside the envelope (fp32 weights, odd columns): the per-tensor path, same results
+    odd = [torch.randn(64, 100, device=DEV).to(dtype), torch.randn(256, 384, device=DEV)]
+    for w in odd:
+        assert H.equal_nan_aware(q.fake_quant_weights_dynamic([w])[0].cpu(), q.fake_quant_weight_dynamic(w).cpu())
+        assert torch.equal(q.real_quant_weights_dynamic([w])[0][0].view(torch.uint8), q.real_quant_weight_dynamic(w)[0].view(torch.uint8))

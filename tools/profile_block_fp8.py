@@ -25,3 +25,23 @@ for name, fn, by in (('fake', lambda: q.fake_quant_weight_dynamic(w), 4), ('real
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
     print(name, round(ms, 4), 'ms', round(w.numel() * by / ms / 1e6, 1), 'GB/s')
+
+# MoE experts (DeepSeek-V2-Lite: 66 experts x gate/up [1408, 2048] + down [2048, 1408]): per-tensor calls vs 16 per launch
+ex = []
+for _ in range(66):
+    ex += [(torch.randn(1408, 2048, device=dev) * 0.02).to(torch.bfloat16), (torch.randn(1408, 2048, device=dev) * 0.02).to(torch.bfloat16),
+           (torch.randn(2048, 1408, device=dev) * 0.02).to(torch.bfloat16)]
+nel = sum(w.numel() for w in ex)
+for name, fn, by in (('experts fake per-tensor', lambda: [q.fake_quant_weight_dynamic(w) for w in ex], 4),
+                     ('experts fake multi', lambda: q.fake_quant_weights_dynamic(ex), 4),
+                     ('experts real per-tensor', lambda: [q.real_quant_weight_dynamic(w) for w in ex], 3),
+                     ('experts real multi', lambda: q.real_quant_weights_dynamic(ex), 3)):
+    fn()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(3):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    print(name, round(ms, 3), 'ms', round(nel * by / ms / 1e6, 1), 'GB/s')
