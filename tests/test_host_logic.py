@@ -55,3 +55,35 @@ def test_unsupported_modes_fail_loudly():
         Q.IntegerQuantizer(4, True, 'per_channel', ste=True)
     with pytest.raises(AssertionError):
         Q.IntegerQuantizer(8, False, 'per_block', block_size=128)  # quant.py:60
+
+
+def test_fp8_infer_mirror_has_no_cpu_path_and_keeps_the_reference_assertions():
+    """lightcompress_b200.fp8_infer (mirror of kernel.py / module_utils.py:41-46, 223-261) on CPU tensors: the reference's
+    own assertions fire first, then the no-CPU-path error; the module keeps the reference's parameter layout."""
+    from lightcompress_b200 import fp8_infer as fi
+    with pytest.raises(AssertionError, match='divisible by block_size'):
+        fi.act_quant(torch.zeros(4, 100))
+    with pytest.raises(AssertionError, match='contiguous'):
+        fi.act_quant(torch.zeros(256, 4).t())
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        fi.act_quant(torch.zeros(4, 128))
+    a = torch.zeros(4, 128).to(torch.float8_e4m3fn)
+    b = torch.zeros(128, 128).to(torch.float8_e4m3fn)
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        fi.fp8_gemm(a, torch.ones(4, 1), b, torch.ones(1, 1))
+    with pytest.raises(AssertionError, match='contiguous'):
+        fi.fp8_gemm(a, torch.ones(4, 1), b.t(), torch.ones(1, 1))
+    m = fi.LlmcFp8Linear(300, 200, True, 128)
+    assert m.weight.dtype == torch.float8_e4m3fn and tuple(m.weight.shape) == (200, 300)
+    assert m.weight_scale_inv.dtype == torch.float32 and tuple(m.weight_scale_inv.shape) == (2, 3)
+    assert tuple(m.bias.shape) == (200,)
+
+
+def test_weight_lists_outside_the_multi_launch_envelope_loop_over_the_reference_api():
+    """fake / real_quant_weights_dynamic fall back to the per-tensor calls (which have no CPU path) instead of guessing."""
+    q = Q.FloatQuantizer('e4m3', True, 'per_block', block_size=128, use_qtorch=True)
+    assert not q._block_fp8_multi_ok([torch.zeros(128, 128, dtype=torch.bfloat16)])          # CPU tensor
+    assert not q._block_fp8_multi_ok([])
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        q.real_quant_weights_dynamic([torch.zeros(128, 128, dtype=torch.bfloat16)])
+    assert q.real_quant_weights_dynamic([]) == [] and q.fake_quant_weights_dynamic([]) == []
