@@ -11,7 +11,6 @@
 //   warp 1    : MMA issuer (one thread): 4 x (M = 128, N = 256, K = 32) per K block, accumulate flag cleared on the first
 //   warps 4-11: promotion + epilogue: thread = output row (TMEM lane) x 128-column half, 128 fp32 accumulators in
 //               registers (setmaxnreg: 232 for these two warpgroups, 40 for the producer / issuer warpgroup)
-#include <cstdlib>
 #include "tc.cuh"
 
 namespace lcb {
@@ -196,7 +195,6 @@ struct Params {
   const void* bias;   // NULL or [N]
   int bias_dtype;
   uint32_t idesc;
-  int dbg;
 };
 struct Maps {
   CUtensorMap a, b;
@@ -386,254 +384,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
   }
 }
 
-// ----------------------------------------------------------------------------------------------------------------------
-// CTA-pair variant (tcgen05 cta_group::2): the two CTAs of a cluster own a 256 x 256 output tile, 128 rows each. Every CTA
-// stages ITS 128 rows of A and ITS 128-row half of the weight tile (32 KB per K block instead of 48: 6 stages); the leader
-// (cluster rank 0) issues M 256 x N 256 MMAs that read both shared memories and write both tensor memories, so each
-// SM's shared memory feeds 64 B / clk of operands instead of 96. Barriers: `full` lives in the leader and counts the bytes
-// of both CTAs' TMA loads; MMA completion is multicast to `empty` and `tfull` of both CTAs; the promotion warps of both
-// CTAs release a TMEM stage by arriving on the LEADER's `tempty`.
-// ----------------------------------------------------------------------------------------------------------------------
-constexpr int STAGES2 = 6;
-constexpr int B2_BYTES = (BN / 2) * BKB, STAGE2_BYTES = A_BYTES + B2_BYTES;   // 32 KB
-constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 256 + 1024;
-
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-// TMA load whose completion bytes are counted by a barrier that may live in the peer CTA of the pair
-__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int32_t x, int32_t y) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-          tc::smem_u32(smem_dst)),
-      "l"(m), "r"(bar_cluster_addr), "r"(x), "r"(y)
-      : "memory");
-}
-__device__ __forceinline__ void mma_f8_ss_2sm(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void mma_commit_2sm(uint64_t* bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-                   tc::smem_u32(bar)),
-               "h"(mask)
-               : "memory");
-}
-
-template <typename TO>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
-    fp8_gemm2_kernel(const __grid_constant__ Maps maps, const Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES2 * STAGE2_BYTES);
-  uint64_t* empty = full + STAGES2;
-  uint64_t* tfull = empty + STAGES2;
-  uint64_t* tempty = tfull + NACC;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + NACC);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int crank = (int)cluster_ctarank();
-  if (warp == 0 && lane == 0) {
-    tc::tma_prefetch_desc(&maps.a);
-    tc::tma_prefetch_desc(&maps.b);
-    for (int s = 0; s < STAGES2; ++s) {
-      tc::mbar_init(&full[s], 1);
-      tc::mbar_init(&empty[s], 1);
-    }
-    for (int a = 0; a < NACC; ++a) {
-      tc::mbar_init(&tfull[a], 1);
-      tc::mbar_init(&tempty[a], 2 * EPI_WARPS);   // promotion warps of both CTAs (only the leader's copy is used)
-    }
-    tc::fence_barrier_init();
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"(512) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-  tc::tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();
-  tc::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  const int nkb = p.nkb;
-  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-  const int n_pair_i = (p.nblk_i + 1) >> 1;
-  const int n_ptiles = n_pair_i * p.nblk_j;
-
-  if (warp < FIRST_EPI_WARP) {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-  if (warp == 0) {
-    // ===== TMA producer (both CTAs) =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = cluster_id; t < n_ptiles; t += n_clusters) {
-        const int ti = (t % n_pair_i) * 2 + crank, tj = t / n_pair_i;
-        for (int kb = 0; kb < nkb; ++kb) {
-          tc::mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * STAGE2_BYTES;
-          const uint32_t lead_full = mapa_u32(tc::smem_u32(&full[stage]), 0);
-          if (crank == 0) tc::mbar_expect_tx(&full[stage], 2 * STAGE2_BYTES);
-          tma_load_2d_2sm(sa, &maps.a, lead_full, kb * BKB, ti * BM);
-          tma_load_2d_2sm(sa + A_BYTES, &maps.b, lead_full, kb * BKB, tj * BN + crank * (BN / 2));
-          if (++stage == STAGES2) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 1 && crank == 0) {
-    // ===== MMA issuer (leader CTA only) =====
-    int stage = 0, acc = 0;
-    uint32_t phase = 0, acc_phase = 0;
-    const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);
-    const uint32_t idesc2 = idesc_f8(0, 0, 2 * BM, BN);
-    for (int t = cluster_id; t < n_ptiles; t += n_clusters) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
-        tc::mbar_wait(&full[stage], phase);
-        tc::tc_fence_after();
-        if (lane == 0) {
-          const uint32_t sa = tc::smem_u32(smem + stage * STAGE2_BYTES);
-          const uint32_t sb = sa + A_BYTES;
-          const uint32_t d_tmem = tmem_base + (uint32_t)acc * BN;
-#pragma unroll
-          for (int k = 0; k < BKB / 32; ++k)
-            mma_f8_ss_2sm(d_tmem, tc::smem_desc_at(desc_k, sa + k * 32), tc::smem_desc_at(desc_k, sb + k * 32), idesc2, k != 0 ? 1u : 0u);
-          mma_commit_2sm(&empty[stage], (uint16_t)3);
-          mma_commit_2sm(&tfull[acc], (uint16_t)3);
-        }
-        __syncwarp();
-        if (++stage == STAGES2) {
-          stage = 0;
-          phase ^= 1;
-        }
-        if (++acc == NACC) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
-      }
-    }
-  }
-  } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
-    // ===== promotion + epilogue (both CTAs, own 128 rows) =====
-    const int q = warp & 3;
-    const int ch = ((warp - FIRST_EPI_WARP) >> 2) * EPI_COLS;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    float accv[EPI_COLS];
-    for (int t = cluster_id; t < n_ptiles; t += n_clusters) {
-      const int ti = (t % n_pair_i) * 2 + crank, tj = t / n_pair_i;
-      const int row = ti * BM + q * 32 + lane;
-      const float* asp = p.a_s + (int64_t)min(row, p.M - 1) * nkb;
-      const float* bsp = p.b_s + (int64_t)min((tj * BN + ch) >> 7, p.nsb - 1) * nkb;
-#pragma unroll
-      for (int j = 0; j < EPI_COLS; ++j) accv[j] = 0.f;
-      float sc = __fmul_rn(asp[0], bsp[0]);
-#pragma unroll 1
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int kn = min(kb + 1, nkb - 1);
-        const float sc_next = __fmul_rn(__ldg(asp + kn), __ldg(bsp + kn));
-        tc::mbar_wait(&tfull[acc], acc_phase);
-        tc::tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + ch);
-        if (!(p.dbg & 1)) {
-        uint32_t v0[32], v1[32];
-        tc::tmem_ld_32x32(taddr, v0);
-        tc::tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < EPI_COLS / 32; c += 2) {
-          tc::tmem_ld_32x32(taddr + (c + 1) * 32, v1);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) accv[c * 32 + j] = __fmaf_rn(__uint_as_float(v0[j]), sc, accv[c * 32 + j]);
-          tc::tmem_ld_wait();
-          if (c + 2 < EPI_COLS / 32) tc::tmem_ld_32x32(taddr + (c + 2) * 32, v0);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) accv[(c + 1) * 32 + j] = __fmaf_rn(__uint_as_float(v1[j]), sc, accv[(c + 1) * 32 + j]);
-          if (c + 2 < EPI_COLS / 32) tc::tmem_ld_wait();
-        }
-        }
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(mapa_u32(tc::smem_u32(&tempty[acc]), 0));   // the leader's barrier
-        if (++acc == NACC) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
-        sc = sc_next;
-      }
-      if (row < p.M) {
-        const int col0 = tj * BN + ch;
-        TO* crow = reinterpret_cast<TO*>(p.c) + (int64_t)row * p.ldc + col0;
-        constexpr int V = TI<TO>::VEC;
-        const bool vec_ok = (p.ldc % V == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
-#pragma unroll
-        for (int c = 0; c < EPI_COLS; c += V) {
-          float o[V];
-#pragma unroll
-          for (int i = 0; i < V; ++i) o[i] = TI<TO>::rd(accv[c + i]);
-          if (p.bias) {
-#pragma unroll
-            for (int i = 0; i < V; ++i)
-              if (col0 + c + i < p.N) o[i] = TI<TO>::rd(__fadd_rn(o[i], load_rt(p.bias, col0 + c + i, p.bias_dtype)));
-          }
-          if (vec_ok && col0 + c + V <= p.N) {
-            *reinterpret_cast<uint4*>(crow + c) = TI<TO>::pack(o);
-          } else {
-#pragma unroll
-            for (int i = 0; i < V; ++i)
-              if (col0 + c + i < p.N) TI<TO>::store1(crow + c + i, o[i]);
-          }
-        }
-      }
-    }
-  }
-
-  tc::tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();
-  if (warp == 1) {
-    tc::tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
-  }
-}
-
-template <typename TO>
-int launch_gemm2(const Maps& maps, const Params& p, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(fp8_gemm2_kernel<TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES) != cudaSuccess) {
-      set_last_error("cudaFuncSetAttribute(fp8_gemm2)", cudaGetLastError());
-      return LCB_E_CUDA;
-    }
-    attr_set = true;
-  }
-  const int n_ptiles = ((p.nblk_i + 1) / 2) * p.nblk_j;
-  const int grid = 2 * (n_ptiles < kNumSMs / 2 ? n_ptiles : kNumSMs / 2);
-  fp8_gemm2_kernel<TO><<<grid, NTHREADS, SMEM2_BYTES, st>>>(maps, p);
-  LCB_CUDA_CHECK_LAUNCH("fp8_gemm2");
-  return LCB_OK;
-}
-
 template <typename TO>
 int launch_gemm(const Maps& maps, const Params& p, int grid, cudaStream_t st) {
   static bool attr_set = false;
@@ -691,7 +441,6 @@ extern "C" int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, cons
   p.bias = bias;
   p.bias_dtype = bias_dtype;
   p.idesc = idesc_f8(0, 0, BM, BN);
-  p.dbg = getenv("LCB_FP8_DBG") ? atoi(getenv("LCB_FP8_DBG")) : 0;
   bool ok = make_tmap_2d(&maps.a, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, K, K, BM, BKB) &&
             make_tmap_2d(&maps.b, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, K, K, BN, BKB);
   if (!ok) {
@@ -700,15 +449,6 @@ extern "C" int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, cons
   }
   const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  static const int use2 = getenv("LCB_FP8_GEMM2") ? atoi(getenv("LCB_FP8_GEMM2")) : 0;
-  if (use2) {
-    Maps m2 = maps;
-    if (!make_tmap_2d(&m2.b, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, K, K, BN / 2, BKB)) return LCB_E_CUDA;
-    if (out_dtype == LCB_BF16) return launch_gemm2<__nv_bfloat16>(m2, p, st);
-    if (out_dtype == LCB_F16) return launch_gemm2<__half>(m2, p, st);
-    if (out_dtype == LCB_F32) return launch_gemm2<float>(m2, p, st);
-    return LCB_E_UNSUPPORTED;
-  }
   if (out_dtype == LCB_BF16) return launch_gemm<__nv_bfloat16>(maps, p, grid, st);
   if (out_dtype == LCB_F16) return launch_gemm<__half>(maps, p, grid, st);
   if (out_dtype == LCB_F32) return launch_gemm<float>(maps, p, grid, st);
