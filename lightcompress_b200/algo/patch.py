@@ -192,3 +192,23 @@ def patch_reference(registry):
         s._lcb_patched = True
         done.append('SmoothQuant')
     return done
+
+
+def patch_fp8_inference(*modules):
+    """Rebind the reference's block-wise FP8 inference functions — the Triton module `kernel.py` (`act_quant` :31-54,
+    `fp8_gemm` :218-242, `weight_cast_to_fp8 / weight_cast_to_bf16` :73-138) and `module_utils.py`
+    (`block_wise_fp8_forward_func` :41-46, which `LlmcFp8Linear.forward` and the FP8 fake / real linears call) — onto
+    `lightcompress_b200.fp8_infer`. Pass every module object that holds one of those names
+    (`llmc.compression.quantization.kernel`, `.module_utils`, `.quant`); names a module does not define are left alone.
+    Returns {module name: [rebound names]}."""
+    from .. import fp8_infer
+    names = ('act_quant', 'fp8_gemm', 'block_wise_fp8_forward_func', 'weight_cast_to_fp8', 'weight_cast_to_bf16')
+    done = {}
+    for mod in modules:
+        hit = []
+        for n in names:
+            if hasattr(mod, n):
+                setattr(mod, n, getattr(fp8_infer, n))
+                hit.append(n)
+        done[getattr(mod, '__name__', repr(mod))] = hit
+    return done

@@ -181,3 +181,13 @@ def test_block_wise_forward_and_module(bias):
     full = lin.float().cpu()(x.float())
     assert float((y.float() - full).norm() / full.norm()) < 0.06
     del g
+
+
+def test_c_abi_status_codes_surface_as_exceptions():
+    """K % 16 != 0 (TMA row pitch) and unsupported group sizes are refused by the C ABI, not silently mis-computed."""
+    a = torch.zeros(4, 136, device=DEV).to(F8)
+    b = torch.zeros(128, 136, device=DEV).to(F8)
+    with pytest.raises(Exception, match='lcb_fp8_gemm'):
+        fi.fp8_gemm(a, torch.ones(4, 2, device=DEV), b, torch.ones(1, 2, device=DEV), out_dtype=torch.bfloat16)
+    with pytest.raises(Exception, match='lcb_act_quant_fp8'):
+        fi.act_quant(torch.zeros(4, 96, device=DEV, dtype=torch.bfloat16), 48)

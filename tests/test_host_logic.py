@@ -87,3 +87,21 @@ def test_weight_lists_outside_the_multi_launch_envelope_loop_over_the_reference_
     with pytest.raises(RuntimeError, match='no CPU path'):
         q.real_quant_weights_dynamic([torch.zeros(128, 128, dtype=torch.bfloat16)])
     assert q.real_quant_weights_dynamic([]) == [] and q.fake_quant_weights_dynamic([]) == []
+
+
+def test_patch_fp8_inference_rebinds_only_what_a_module_defines():
+    import types
+
+    from lightcompress_b200 import fp8_infer as fi
+    from lightcompress_b200.algo import patch_fp8_inference
+    kernel = types.ModuleType('ref_kernel')
+    kernel.act_quant = kernel.fp8_gemm = kernel.weight_cast_to_fp8 = kernel.weight_cast_to_bf16 = object()
+    kernel.fp8_gemm_configs = [1, 2]
+    mu = types.ModuleType('ref_module_utils')
+    mu.act_quant = mu.fp8_gemm = mu.block_wise_fp8_forward_func = object()
+    done = patch_fp8_inference(kernel, mu)
+    assert kernel.act_quant is fi.act_quant and kernel.fp8_gemm is fi.fp8_gemm and mu.fp8_gemm is fi.fp8_gemm
+    assert mu.block_wise_fp8_forward_func is fi.block_wise_fp8_forward_func
+    assert kernel.weight_cast_to_fp8 is fi.weight_cast_to_fp8 and kernel.fp8_gemm_configs == [1, 2]
+    assert not hasattr(kernel, 'block_wise_fp8_forward_func') and not hasattr(mu, 'weight_cast_to_fp8')
+    assert sorted(done['ref_module_utils']) == ['act_quant', 'block_wise_fp8_forward_func', 'fp8_gemm']
