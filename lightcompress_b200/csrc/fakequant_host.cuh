@@ -5,6 +5,7 @@
 
 namespace lcb {
 
+static bool encode_block_tmap(CUtensorMap* tm, const void* in, int dtype, int64_t rows, int64_t cols);
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 static SpecD make_specd(const lcb_quant_spec* s) {
@@ -231,6 +232,15 @@ static int fakequant_typed(const void* in_, void* out, void* scales, void* zeros
       else fq_block2d_fp8_kernel<T, 1, 1><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp);
       LCB_CUDA_CHECK_LAUNCH("fq_block2d_fp8");
       return LCB_OK;
+    }
+    if (sizeof(T) == 2 && cols % 8 == 0 && rows < (1ll << 31) && cols < (1ll << 31) && aligned16(in)) {
+      CUtensorMap tm;
+      if (encode_block_tmap(&tm, in, TI<T>::ID, rows, cols)) {
+        using T16 = typename std::conditional<sizeof(T) == 2, T, __nv_bfloat16>::type;
+        LCB_KIND_SWITCH(fq_block2d_tma_kernel<T16, KINDC><<<(int)tiles, 256, 0, st>>>(tm, out, scales, rows, cols, sp));
+        LCB_CUDA_CHECK_LAUNCH("fq_block2d_tma");
+        return LCB_OK;
+      }
     }
     LCB_KIND_SWITCH(fq_block2d_kernel<T, KINDC><<<(int)tiles, 256, 0, st>>>(in, out, scales, rows, cols, sp));
     LCB_CUDA_CHECK_LAUNCH("fq_block2d");

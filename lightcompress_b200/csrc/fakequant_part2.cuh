@@ -317,6 +317,57 @@ __global__ void __launch_bounds__(256)
   block2d_fp8_tma_tile<T, E5M2, OUT_CODES>(&tm, out, scales, rows, cols, blockIdx.x, sp);
 }
 
+// The same staging for every other per_block spec of a 16-bit tensor (integer grids, output_scale_factor != 1, code
+// outputs): pass 2 runs the generic per-vector chain (quant_store_vec) from shared memory.
+template <typename T, int KINDC>
+__global__ void __launch_bounds__(256)
+    fq_block2d_tma_kernel(const __grid_constant__ CUtensorMap tm, void* __restrict__ out, void* __restrict__ scales,
+                          int64_t rows, int64_t cols, SpecD sp) {
+  constexpr int VEC = 8, BS = 128, VPR = BS / VEC, RPP = 256 / VPR, NP = BS / RPP;
+  static_assert(sizeof(T) == 2, "16-bit inputs");
+  __shared__ __align__(128) uint8_t tile[BS * BS * 2];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ float red[64];
+  const int64_t ncb = (cols + BS - 1) / BS;
+  const int64_t bi = blockIdx.x / ncb, bj = blockIdx.x % ncb;
+  const int vr = threadIdx.x / VPR, vc = threadIdx.x % VPR;
+  if (threadIdx.x == 0) {
+    tc::mbar_init(&bar, 1);
+    tc::fence_barrier_init();
+    tc::mbar_expect_tx(&bar, BS * BS * 2);
+    tc::tma_load_2d(tile, &tm, &bar, (int32_t)(bj * BS), (int32_t)(bi * BS));
+  }
+  __syncthreads();
+  tc::mbar_wait(&bar, 0);
+  const uint8_t* mine = tile + vr * (BS * 2) + vc * 16;
+  float mx = 0.f;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    float f[VEC];
+    TI<T>::unpack(*reinterpret_cast<const uint4*>(mine + p * RPP * (BS * 2)), f);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) mx = max_nan(mx, fabsf(f[i]));
+  }
+  float mn = mx;
+  block_minmax(mx, mn, red);
+  UnitQ u;
+  qparams_from_range(mx, mx, sp, u);
+  finish_unit(sp, u);
+  if (!finite_f(mx)) u.exact = 1;
+  if (threadIdx.x == 0 && scales) store_rt(scales, blockIdx.x, u.s_out, sp.qparam_dtype);
+  if (sp.out_mode == LCB_OUT_NONE) return;
+  const int64_t col = bj * BS + vc * VEC;
+  if (col >= cols) return;
+#pragma unroll 2
+  for (int p = 0; p < NP; ++p) {
+    const int64_t row = bi * BS + p * RPP + vr;
+    if (row >= rows) break;
+    float f[VEC];
+    TI<T>::unpack(*reinterpret_cast<const uint4*>(mine + p * RPP * (BS * 2)), f);
+    quant_store_vec<T, float, KINDC>(f, u, sp, out, row * cols + col);
+  }
+}
+
 // Several weights in ONE launch (the expert matrices of a MoE block: 2.9 M elements each for DeepSeek-V2-Lite, ~1 us of
 // kernel against ~10 us of host work per call). Tiles of all tensors are laid end to end.
 constexpr int kMaxBlockMulti = 16;
