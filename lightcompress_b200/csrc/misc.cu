@@ -4,6 +4,36 @@
 namespace lcb {
 
 // y[r, c] = fp8(codes[r, c]) * scales[r / bs, c / bs]   (kernel.py:86-138 / quant.py:18-31)
+// 16 codes per thread: one 16-byte load, packed fp8x2 -> f16x2 conversions (exact), fp32 product, 16-byte stores
+template <typename TO, int E5M2>
+__global__ void __launch_bounds__(256)
+    fp8_block_dequant_vec16_kernel(const uint8_t* __restrict__ codes, const float* __restrict__ scales, TO* __restrict__ out,
+                                   int64_t rows, int64_t cols, int64_t bs) {
+  const int64_t ncb = (cols + bs - 1) / bs;
+  const int64_t nv = rows * cols / 16;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += stride) {
+    const int64_t e = v * 16, r = e / cols, c = e % cols;
+    const float s = __ldg(scales + (r / bs) * ncb + c / bs);
+    const uint4 raw = ld_stream(codes + e);
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    float f[16];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint16_t b2 = (uint16_t)(w[i >> 1] >> (16 * (i & 1)));
+      uint32_t h2;
+      if (E5M2) asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(h2) : "h"(b2));
+      else asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"(b2));
+      const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&h2));
+      f[2 * i] = __fmul_rn(t.x, s);
+      f[2 * i + 1] = __fmul_rn(t.y, s);
+    }
+    constexpr int V = TI<TO>::VEC;
+#pragma unroll
+    for (int k = 0; k < 16 / V; ++k) st_stream(out + e + k * V, TI<TO>::pack(f + k * V));
+  }
+}
+
 template <typename TO>
 __global__ void __launch_bounds__(256)
     fp8_block_dequant_kernel(const uint8_t* __restrict__ codes, const float* __restrict__ scales, TO* __restrict__ out,
@@ -69,6 +99,23 @@ extern "C" int lcb_fp8_block_dequant(const void* codes, const float* scales, voi
   int64_t work = (rows * cols / 8 + 255) / 256;
   int grid = (int)(work < 148 * 8 ? (work < 1 ? 1 : work) : 148 * 8);
   const uint8_t* c = reinterpret_cast<const uint8_t*>(codes);
+  if (cols % 16 == 0 && block % 16 == 0 && !(reinterpret_cast<uintptr_t>(codes) & 15) && !(reinterpret_cast<uintptr_t>(out) & 15)) {
+    int64_t w16 = (rows * cols / 16 + 255) / 256;
+    const int g16 = (int)(w16 < 148 * 8 ? (w16 < 1 ? 1 : w16) : 148 * 8);
+    const bool e5 = kind == LCB_KIND_FP8_E5M2;
+#define LCB_DQ16(TO_)                                                                                                  \
+  {                                                                                                                    \
+    if (e5) fp8_block_dequant_vec16_kernel<TO_, 1><<<g16, 256, 0, st>>>(c, scales, (TO_*)out, rows, cols, block);       \
+    else fp8_block_dequant_vec16_kernel<TO_, 0><<<g16, 256, 0, st>>>(c, scales, (TO_*)out, rows, cols, block);          \
+    LCB_CUDA_CHECK_LAUNCH("fp8_block_dequant");                                                                        \
+    return LCB_OK;                                                                                                     \
+  }
+    if (out_dtype == LCB_BF16) LCB_DQ16(__nv_bfloat16)
+    if (out_dtype == LCB_F16) LCB_DQ16(__half)
+    if (out_dtype == LCB_F32) LCB_DQ16(float)
+#undef LCB_DQ16
+    return LCB_E_UNSUPPORTED;
+  }
   if (out_dtype == LCB_BF16) fp8_block_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(c, scales, (__nv_bfloat16*)out, rows, cols, block, kind);
   else if (out_dtype == LCB_F16) fp8_block_dequant_kernel<__half><<<grid, 256, 0, st>>>(c, scales, (__half*)out, rows, cols, block, kind);
   else if (out_dtype == LCB_F32) fp8_block_dequant_kernel<float><<<grid, 256, 0, st>>>(c, scales, (float*)out, rows, cols, block, kind);

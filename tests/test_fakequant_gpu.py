@@ -211,3 +211,17 @@ def test_block_fp8_multi_launch_equals_single_launches(bit, dtype):
     for w in odd:
         assert H.equal_nan_aware(q.fake_quant_weights_dynamic([w])[0].cpu(), q.fake_quant_weight_dynamic(w).cpu())
         assert torch.equal(q.real_quant_weights_dynamic([w])[0][0].view(torch.uint8), q.real_quant_weight_dynamic(w)[0].view(torch.uint8))
+
+
+@pytest.mark.parametrize('shape', [(1408, 2048), (200, 272), (130, 72), (1, 16)])
+@pytest.mark.parametrize('fp8', [torch.float8_e4m3fn, torch.float8_e5m2])
+def test_weight_cast_to_bf16_matches_torch(shape, fp8):
+    """lcb_fp8_block_dequant (vector path for cols % 16 == 0, element path otherwise) == fp8.float() * scale[block] -> bf16
+    (quant.py:18-31 / kernel.py:86-138), bit for bit."""
+    g = torch.Generator().manual_seed(shape[0] + shape[1])
+    codes = (torch.randn(shape, generator=g) * 40).to(fp8)
+    nb = ((shape[0] + 127) // 128, (shape[1] + 127) // 128)
+    scales = torch.rand(nb, generator=g) * 0.01 + 1e-4
+    ref = (codes.float() * scales.repeat_interleave(128, 0)[:shape[0]].repeat_interleave(128, 1)[:, :shape[1]]).to(torch.bfloat16)
+    got = Q.weight_cast_to_bf16(codes.to(DEV), scales.to(DEV), 128).cpu()
+    assert H.bits_equal(got, ref)
