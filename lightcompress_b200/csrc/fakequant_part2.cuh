@@ -311,7 +311,7 @@ __device__ __forceinline__ void block2d_fp8_tma_tile(const CUtensorMap* tmp, voi
 }
 
 template <typename T, int E5M2, int OUT_CODES>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
     fq_block2d_fp8_tma_kernel(const __grid_constant__ CUtensorMap tm, void* __restrict__ out, void* __restrict__ scales,
                               int64_t rows, int64_t cols, SpecD sp) {
   block2d_fp8_tma_tile<T, E5M2, OUT_CODES>(&tm, out, scales, rows, cols, blockIdx.x, sp);
