@@ -102,6 +102,20 @@ int lcb_fakequant(const void* in, void* out, void* scales, void* zeros, int64_t 
 int64_t lcb_fakequant_workspace_bytes(void);
 
 /*
+ * Call plans for lcb_fakequant: (rows, cols, unit_rows, unit_cols, spec, dynamic) bundled once, so that the per-call
+ * binding cost of a Python / JNI / cgo caller is 7 pointers instead of 12 mixed arguments — the reference issues one
+ * fake_quant_act_dynamic per linear per forward (module_utils.py:799-813: 224 calls per Llama-3-8B forward), where the
+ * host cost per call bounds the achieved bandwidth. lcb_fakequant_plan_run(plan, ...) is exactly
+ * lcb_fakequant(in, out, scales, zeros, <plan>, workspace, stream): same checks, same kernels, same status codes.
+ * plan_create returns NULL on invalid arguments; plans are immutable and may be shared between threads and streams.
+ */
+void* lcb_fakequant_plan_create(int64_t rows, int64_t cols, int64_t unit_rows, int64_t unit_cols,
+                                const lcb_quant_spec* spec, int dynamic);
+int lcb_fakequant_plan_run(const void* plan, const void* in, void* out, void* scales, void* zeros, void* workspace,
+                           void* stream);
+void lcb_fakequant_plan_destroy(void* plan);
+
+/*
  * Range of every quantization unit (same unit grid as lcb_fakequant): mins / maxs receive amin / amax over the unit in
  * `range_dtype` (the tensor dtype; LCB_F32 with abs_range != 0 = per_block, which ranges |x|.float() and counts the zero
  * padding of ragged edge blocks, quant.py:137-138, 637-638). Replaces get_minmax_range (quant.py:132-143).

@@ -30,6 +30,9 @@ SIGNATURES = {
     'lcb_fakequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64,
                                      ctypes.POINTER(QuantSpec), ctypes.c_int, _c_vp, _c_vp]),
     'lcb_fakequant_workspace_bytes': (_c_i64, []),
+    'lcb_fakequant_plan_create': (_c_vp, [_c_i64, _c_i64, _c_i64, _c_i64, ctypes.POINTER(QuantSpec), ctypes.c_int]),
+    'lcb_fakequant_plan_run': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
+    'lcb_fakequant_plan_destroy': (None, [_c_vp]),
     'lcb_minmax': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp, _c_vp]),
     'lcb_qparams_from_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, ctypes.POINTER(QuantSpec), _c_vp]),
     'lcb_mse_range': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, ctypes.POINTER(QuantSpec), _c_i32,

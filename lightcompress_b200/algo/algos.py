@@ -22,7 +22,7 @@ class GPTQ(BaseBlockwiseQuantization):
             raise NotImplementedError('OWQ outlier columns: use ops.gptq_weight_transform(n_nonout=...) directly')
         self.model_dtype = next(self.blocks[0].parameters()).dtype
         self.layers_cache = {}
-        self.qparams = {}     # module -> (scales [R*C/g, 1], zeros) for deploy (update_model_qparams, gptq.py:398-409)
+        self.qparams = {}     # module -> buf_scales / buf_zeros (+ act-order perm) for deploy (gptq.py:398-452)
 
     def _new_layer(self, m, hessian=None):
         return GPTQLayer(m.weight, self.wquantizer, self.blocksize, self.percdamp, self.actorder, self.static_groups,
@@ -30,6 +30,13 @@ class GPTQ(BaseBlockwiseQuantization):
 
     def block_init(self, block):                       # gptq.py:318-322
         self.named_layers = self.model.get_block_linears(block)
+        # collect_model_qparams (gptq.py:325-331, base_bq.py:338-365): buf_scales / buf_zeros of the ORIGINAL weight in the
+        # model dtype. The reference collects them for every block at construction; a block's weights do not change
+        # before its own turn, so collecting at block_init is the same arithmetic.
+        for m in self.named_layers.values():
+            if isinstance(m, nn.Linear) and m not in self.qparams:
+                _, sc, zp, _, _ = self.wquantizer.get_tensor_qparams(m.weight.data)
+                self.qparams[m] = {'scales': sc, 'zeros': None if self.wquantizer.sym else zp, 'perm': None, 'invperm': None}
         self.layers_cache, self.hessian_owner = {}, {}
         subsets = self.model.get_subsets_in_block(block)
         for i, subset in enumerate(subsets):
@@ -70,26 +77,46 @@ class GPTQ(BaseBlockwiseQuantization):
 
     @torch.no_grad()
     def subset_transform(self, subset, input_feat, subset_kwargs):   # gptq.py:97-126
+        wq = self.wquantizer
+        per_group = wq.granularity == 'per_group'
         for name, layer in subset['layers'].items():
             if not isinstance(layer, nn.Linear):
                 continue
             g = self.layers_cache.pop(name)
-            layer.weight.data = g.quantize()
-            if g.scales is not None and self.wquantizer.granularity == 'per_group':
-                self.qparams[layer] = g.buf_qparams() + (g.perm, g.invperm)
+            buf = self.qparams[layer]
+            R = layer.weight.shape[0]
+            ss = sz = None
+            if per_group and self.static_groups:      # search_group_qparams (gptq.py:380-395): split the model-dtype buffers
+                ss = buf['scales'].float().reshape(R, -1).t().contiguous()
+                sz = None if wq.sym else buf['zeros'].float().reshape(R, -1).t().contiguous()
+            elif not per_group:                       # search_layer_qparams (gptq.py:368-378)
+                ss = buf['scales'].float().reshape(1, R)
+                sz = None if wq.sym else buf['zeros'].float().reshape(1, R)
+            layer.weight.data = g.quantize(static_scales=ss, static_zeros=sz)
+            if per_group and not self.static_groups:  # update_model_qparams (gptq.py:398-409): the searched fp32 groups
+                buf['scales'], buf['zeros'] = g.buf_qparams()
+                buf['perm'], buf['invperm'] = g.perm, g.invperm
             self.last_losses = g.losses
 
-    def w_qdq(self, module, wquantizer):               # gptq.py:425-452
-        if module not in self.qparams:
-            return wquantizer.fake_quant_weight_dynamic(module.weight.data.to(self.model_dtype))
-        scales, zeros, perm, invperm = self.qparams[module]
+    def w_qdq(self, module, wquantizer):               # gptq.py:425-452: always the stored (static) qparams
+        buf = self.qparams.get(module)
+        if buf is None:
+            raise RuntimeError('GPTQ.w_qdq: the module was never calibrated (no buf_scales)')
         w = module.weight.data
-        need_perm = perm is not None and not self.static_groups
+        need_perm = buf['perm'] is not None and wquantizer.granularity == 'per_group' and not self.static_groups
         if need_perm:
-            w = w[:, perm]
-        args = {'scales': scales, 'zeros': zeros, 'qmax': wquantizer.qmax, 'qmin': wquantizer.qmin}
+            w = w[:, buf['perm']]
+        args = {'scales': buf['scales'], 'zeros': buf['zeros'], 'qmax': wquantizer.qmax, 'qmin': wquantizer.qmin}
         q = wquantizer.fake_quant_weight_static(w, args).to(self.model_dtype)
-        return q[:, invperm] if need_perm else q
+        return q[:, buf['invperm']] if need_perm else q
+
+    def w_q(self, module, wquantizer):                 # gptq.py:412-422
+        buf = self.qparams[module]
+        assert buf['perm'] is None or self.static_groups or wquantizer.granularity != 'per_group', \
+            'act-order with dynamic groups cannot be exported (gptq.py:455-457)'
+        args = {'scales': buf['scales'].to(self.model_dtype), 'zeros': buf['zeros'], 'qmax': wquantizer.qmax,
+                'qmin': wquantizer.qmin}
+        return wquantizer.real_quant_weight_static(module.weight.data, args)
 
 
 @ALGO_REGISTRY
@@ -103,6 +130,8 @@ class Awq(BaseBlockwiseQuantization):
         self.clip_sym = sp.get('clip_sym', self.wquantizer.sym)
         self.true_sequential = False
         self.best_index = {}   # (block, first layer name) -> selected candidate, for parity reports
+        self.act_scales = {}   # '<prefix>.<block>.<layer>' -> applied scale (awq.py:365-368, kept whether or not save_scale)
+        self.clips = {}        # (block, layer name) -> (best_max_val, best_min_val) of AutoClip
 
     @torch.no_grad()
     def block_transform(self, block, input_feat, block_kwargs):   # awq.py:280-298
@@ -110,9 +139,12 @@ class Awq(BaseBlockwiseQuantization):
             super().block_transform(block, input_feat, block_kwargs)
         if self.weight_clip:
             from .autoclip import auto_clip_block
+            rec = {}
             auto_clip_block(self.model.get_block_linears(block), input_feat, self.wquantizer, self.clip_sym,
                             n_sample_token=(self.config or {}).get('calib', {}).get('seq_len', None)
-                            if isinstance(self.config, dict) else None)
+                            if isinstance(self.config, dict) else None, record=rec)
+            for n, v in rec.items():
+                self.clips[(self.block_idx, n)] = v
 
     @torch.no_grad()
     def subset_transform(self, subset, input_feat, subset_kwargs):   # awq.py:300-372
@@ -137,5 +169,8 @@ class Awq(BaseBlockwiseQuantization):
             scale, best, _ = lcawq.awq_search_scale_module(x, layers, inspect, self.wquantizer, kwargs,
                                                            self.trans_version)
         self.best_index[(self.block_idx, next(iter(layers_dict)))] = best
+        prefix = getattr(self.model, 'block_name_prefix', 'model.layers')
+        for n in layers_dict:
+            self.act_scales[f'{prefix}.{self.block_idx}.{n}'] = scale
         self.apply_scale(scale, prev_op, layers)
         self.update_input_feat(scale, input_feat, layers_dict)

@@ -38,7 +38,7 @@ def apply_clip(weight, min_val, max_val, clip_sym):
 
 
 @torch.no_grad()
-def auto_clip_block(named_linears, input_feat, wquantizer, clip_sym, n_sample_token=None):
+def auto_clip_block(named_linears, input_feat, wquantizer, clip_sym, n_sample_token=None, record=None):
     """AutoClipper.run (auto_clip.py:44-82): every linear except q/k-like ones; ranges averaged over the ranks."""
     rank, ws = lcdist.world()
     for n, m in named_linears.items():
@@ -53,4 +53,6 @@ def auto_clip_block(named_linears, input_feat, wquantizer, clip_sym, n_sample_to
             max_val /= ws
             dist.all_reduce(min_val, op=dist.ReduceOp.SUM)
             min_val /= ws
+        if record is not None:
+            record[n] = (max_val, min_val)
         apply_clip(m.weight, min_val, max_val, clip_sym)

@@ -61,6 +61,7 @@ class BaseBlockwiseQuantization(object):
             raise NotImplementedError('static activation quantization is not on the CUDA hot path')
         self.special = quant_config.get('special', {}) or {}
         self.true_sequential = self.special.get('true_sequential', False)
+        self.quant_out = quant_config.get('quant_out', False)
         # per-sample block forwards are launch-bound on a B200 (≈1 ms of host work against ≈0.3-0.6 ms of kernels for a
         # 2048-token sample): with capture-safe hooks the forward is recorded once per pass and replayed per sample
         self.use_graph = self.special.get('cuda_graph', True)
@@ -77,7 +78,14 @@ class BaseBlockwiseQuantization(object):
 
     # ---- closures bound into modules at deploy time (base_bq.py:46-82) ------------------------------------------------
     def w_qdq(self, module, wquantizer):
-        return wquantizer.fake_quant_weight_dynamic(module.weight.data)
+        args = {}
+        lo, up = getattr(module, 'buf_lowbound_factor', None), getattr(module, 'buf_upbound_factor', None)
+        if lo is not None or up is not None:   # AWQ clip v2 / learnable ranges (base_bq.py:46-52)
+            args = {'lowbound_factor': lo, 'upbound_factor': up}
+        return wquantizer.fake_quant_weight_dynamic(module.weight.data, args)
+
+    def w_q(self, module, wquantizer):
+        return wquantizer.real_quant_weight_dynamic(module.weight.data)
 
     def a_qdq(self, act, module, aquantizer):
         return aquantizer.fake_quant_act_dynamic(act)
@@ -199,12 +207,38 @@ class BaseBlockwiseQuantization(object):
         if not self.data_free:
             handles = self.register_hooks(named_linears, input_feat)
             self.block_init(block)
-            self.input['data'] = self.block_forward(block)   # quant_out = False: next block sees the float output
+            out = self.block_forward(block)
+            if not self.quant_out:
+                self.input['data'] = out     # next block sees the float output (base_bq.py:423-428)
+            del out
             for h in handles:
                 h.remove()
             self.block_transform(block, input_feat, self.input['kwargs'])
+            if self.quant_out:               # base_bq.py:438-449: the next block sees the fake-quantized block's output
+                self.input['data'] = self._forward_fake_quant(block, named_linears)
         else:
             self.block_transform(block, input_feat, None)
+
+    def _forward_fake_quant(self, block, linears):
+        """One block forward with every linear fake-quantized (FakeQuantLinear: w_qdq weight, a_qdq input when w+a),
+        the float weights restored afterwards."""
+        mdt = getattr(self, 'model_dtype', None)
+        saved = {n: m.weight.data for n, m in linears.items()}
+        handles = []
+        for n, m in linears.items():
+            m.weight.data = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            if not self.w_only:
+                handles.append(m.register_forward_pre_hook(self._act_hook))
+        hooks, self.graph_safe_hooks = self.graph_safe_hooks, self.w_only
+        try:
+            out = self.block_forward(block)
+        finally:
+            self.graph_safe_hooks = hooks
+            for h in handles:
+                h.remove()
+            for n, m in linears.items():
+                m.weight.data = saved[n]
+        return out
 
     def block_transform(self, block, input_feat, block_kwargs):
         subsets = self.model.get_subsets_in_block(block)

@@ -37,6 +37,9 @@ def argmin_across_ranks(losses, indices, device):
         if l < best_l or (l == best_l and i < best_i):
             best_l, best_i = l, i
     if ws == 1:
+        if best_i < 0:
+            raise RuntimeError('argmin_across_ranks: every candidate loss is NaN / inf (the reference ends with '
+                               'best_scales = None, awq.py:245-248, and fails on its next use)')
         return best_l, best_i
     t = torch.tensor([best_l, float(best_i if best_i >= 0 else 1 << 30)], dtype=torch.float64, device=device)
     gathered = [torch.zeros_like(t) for _ in range(ws)]
@@ -45,6 +48,8 @@ def argmin_across_ranks(losses, indices, device):
         l, i = float(g[0]), int(g[1])
         if l < best_l or (l == best_l and i < best_i):
             best_l, best_i = l, i
+    if best_i < 0 or best_i >= (1 << 30):
+        raise RuntimeError('argmin_across_ranks: every candidate loss on every rank is NaN / inf')
     return best_l, best_i
 
 

@@ -123,16 +123,17 @@ class GPTQLayer(object):
             raise NotImplementedError('GPTQ with on-the-fly group qparams fuses the min/max search into the column kernel; '
                                       f"calib_algo={wq.calib_algo!r} needs static_groups=True or per_channel")
         if gs > 0 and self.static_groups:
-            if static_scales is None:   # search_group_qparams (gptq.py:380-395): qparams of the original weight
-                _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data.float())
-                static_scales = s.reshape(self.rows, -1).t().contiguous()
-                static_zeros = None if wq.sym else z.reshape(self.rows, -1).t().contiguous()
+            if static_scales is None:   # search_group_qparams (gptq.py:380-395): qparams of the original weight IN THE
+                # MODEL DTYPE (collect_block_qparams, base_bq.py:338-365), upcast exactly when they meet the fp32 column
+                _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data)
+                static_scales = s.float().reshape(self.rows, -1).t().contiguous()
+                static_zeros = None if wq.sym else z.float().reshape(self.rows, -1).t().contiguous()
             if self.actorder:
                 col_group = (self.perm // gs).to(torch.int32)
-        elif gs <= 0 and static_scales is None:   # per_channel: search_layer_qparams (gptq.py:368-378)
-            _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data.float())
-            static_scales = s.reshape(1, self.rows)
-            static_zeros = None if wq.sym else z.reshape(1, self.rows)
+        elif gs <= 0 and static_scales is None:   # per_channel: search_layer_qparams (gptq.py:368-378), model dtype
+            _, s, z, _, _ = wq.get_tensor_qparams(self.weight.data)
+            static_scales = s.float().reshape(1, self.rows)
+            static_zeros = None if wq.sym else z.float().reshape(1, self.rows)
         tmp, losses, scales, zeros = ops.gptq_weight_transform(
             W, Hinv, self.blocksize, gs, qmin, qmax, wq.sym, wq.round_zp, static_scales=static_scales,
             static_zeros=static_zeros, col_group=col_group)

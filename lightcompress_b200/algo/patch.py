@@ -1,8 +1,8 @@
 """`patch_reference(ALGO_REGISTRY)`: rebind the hot methods of the reference's own algorithm classes onto the sm_100a
 kernels, leaving their block loop, hooks, bookkeeping and deploy untouched.
 
-The reference is not importable on the GPU box, so these bindings are exercised in tests/test_algo_gpu.py with stand-in
-classes that reproduce the attribute contract of gptq.py / awq.py / smoothquant.py (layers_cache, groups, qparams, ...).
+Exercised on the REAL reference classes in tests/test_ref_pipeline_gpu.py (the unmodified reference ships to the GPU box
+as test infrastructure under oracle/_ref) and on stand-in classes in tests/test_algo_gpu.py.
 """
 import os
 
@@ -10,8 +10,32 @@ import torch
 import torch.nn as nn
 
 from .. import ops
+from .. import quant as lcquant
 from . import awq as lcawq
 from . import dist as lcdist
+
+
+def _lookup(registry, name):
+    """The reference's Register is a dict SUBCLASS that keeps its entries in `self._dict` and overrides __getitem__ /
+    __contains__ only (registry_factory.py:1-37): `registry.get(name)` answers from the empty base dict."""
+    try:
+        return registry[name] if name in registry else None
+    except KeyError:
+        return None
+
+
+def as_lcb_quantizer(q):
+    """The product quantizer that computes what `q` computes: `q` itself after the class swap of INTEGRATION.md §3(a), or a
+    twin built from the reference quantizer's constructor arguments (quant.py:47-101 keeps them: bit, sym, granularity,
+    kwargs) when only the algorithms were patched."""
+    if q is None or isinstance(q, lcquant.BaseQuantizer):
+        return q
+    twin = q.__dict__.get('_lcb_twin')
+    if twin is None:
+        cls = lcquant.FloatQuantizer if type(q).__name__ == 'FloatQuantizer' else lcquant.IntegerQuantizer
+        twin = cls(q.bit, q.sym, q.granularity, **dict(getattr(q, 'kwargs', {})))
+        q.__dict__['_lcb_twin'] = twin
+    return twin
 
 
 # ---- GPTQ (gptq.py) ------------------------------------------------------------------------------------------------------
@@ -76,7 +100,7 @@ def _gptq_process(orig):
 
 def _gptq_weight_transform(orig):
     def weight_transform(self, W, Hinv, Losses, tmp):
-        wq = self.wquantizer
+        wq = as_lcb_quantizer(self.wquantizer)
         if type(wq).__name__ != 'IntegerQuantizer' or self.blocksize > 128 or self.blocksize % 8 or W.shape[1] % 8:
             return orig(self, W, Hinv, Losses, tmp)
         R = W.shape[0]
@@ -126,7 +150,8 @@ def _awq_search(orig):
         if not fused:
             return orig(self, prev_op, layers_dict, input, inspect_module, is_gqa, subset_kwargs)
         x = input[0].to(inspect_module.weight.device)
-        scales, _, _ = lcawq.awq_search_scale(x, inspect_module.weight.data, self.wquantizer, self.trans_version)
+        scales, _, _ = lcawq.awq_search_scale(x, inspect_module.weight.data, as_lcb_quantizer(self.wquantizer),
+                                              self.trans_version)
         return scales
     return search_scale_subset
 
@@ -147,12 +172,12 @@ def _sq_act_scale(orig):
 # ---- AutoClip (auto_clip.py) ----------------------------------------------------------------------------------------------
 def _autoclip_layer(orig):
     def auto_clip_layer(self, block_idx, layer_name, w, inputs, n_grid=20, max_shrink=0.5, n_sample_token=512, eps=0.0):
-        wq = self.wquantizer
+        wq = as_lcb_quantizer(self.wquantizer)
         gs = wq.group_size if wq.granularity == 'per_group' else w.shape[1]
         ok = (self.clip_version == 'v1' and self.w_only and len(inputs) == 1 and not self.padding_mask and w.dim() == 2
               and type(wq).__name__ == 'IntegerQuantizer' and wq.granularity in ('per_group', 'per_channel')
               and w.dtype in (torch.bfloat16, torch.float16) and inputs[0].dtype == w.dtype
-              and w.shape[1] % gs == 0 and gs % 64 == 0 and w.shape[0] % 64 == 0)
+              and w.shape[1] % gs == 0 and gs % 8 == 0 and (gs <= 128 or gs % 128 == 0) and w.shape[0] % 64 == 0)
         if not ok:
             return orig(self, block_idx, layer_name, w, inputs, n_grid, max_shrink, n_sample_token, eps)
         from .autoclip import auto_clip_layer as lcb_layer
@@ -161,34 +186,66 @@ def _autoclip_layer(orig):
     return auto_clip_layer
 
 
+def _rebind(cls, name, wrap):
+    orig = getattr(cls, name)
+    saved = cls.__dict__.get('_lcb_originals') or {}
+    saved[name] = (name in cls.__dict__, orig)     # (defined on this class itself?, function)
+    cls._lcb_originals = saved
+    setattr(cls, name, wrap(orig))
+
+
+def _restore(cls):
+    """Undo `_rebind` on a class. Returns True when something was restored."""
+    saved = cls.__dict__.get('_lcb_originals')
+    if not saved:
+        return False
+    for name, (own, orig) in saved.items():
+        if own:
+            setattr(cls, name, orig)
+        else:
+            delattr(cls, name)                      # inherited: fall back to the base class again
+    cls._lcb_originals = None
+    cls._lcb_patched = False
+    return True
+
+
 def patch_autoclipper(cls):
     """cls: llmc.compression.quantization.auto_clip.AutoClipper. Routes auto_clip_layer (v1, w_only) to
     lcb_autoclip_search; anything else keeps the reference path. Returns True when newly patched."""
-    if getattr(cls, '_lcb_patched', False):
+    if cls.__dict__.get('_lcb_patched', False):
         return False
-    cls.auto_clip_layer = _autoclip_layer(cls.auto_clip_layer)
+    _rebind(cls, 'auto_clip_layer', _autoclip_layer)
     cls._lcb_patched = True
     return True
+
+
+def unpatch_autoclipper(cls):
+    return _restore(cls)
+
+
+def unpatch_reference(registry):
+    """Restore the reference methods `patch_reference` rebound. Returns the restored names."""
+    return [n for n in ('GPTQ', 'Awq', 'SmoothQuant') if _lookup(registry, n) is not None and _restore(_lookup(registry, n))]
 
 
 def patch_reference(registry):
     """registry: llmc.utils.registry_factory.ALGO_REGISTRY (or any dict name -> class). Returns the patched names."""
     done = []
-    g = registry.get('GPTQ')
-    if g is not None and not getattr(g, '_lcb_patched', False):
-        g.add_batch = _gptq_add_batch(g.add_batch)
-        g.process_hessian_and_weights = _gptq_process(g.process_hessian_and_weights)
-        g.weight_transform = _gptq_weight_transform(g.weight_transform)
+    g = _lookup(registry, 'GPTQ')
+    if g is not None and not g.__dict__.get('_lcb_patched', False):
+        _rebind(g, 'add_batch', _gptq_add_batch)
+        _rebind(g, 'process_hessian_and_weights', _gptq_process)
+        _rebind(g, 'weight_transform', _gptq_weight_transform)
         g._lcb_patched = True
         done.append('GPTQ')
-    a = registry.get('Awq')
-    if a is not None and not getattr(a, '_lcb_patched', False):
-        a.search_scale_subset = _awq_search(a.search_scale_subset)
+    a = _lookup(registry, 'Awq')
+    if a is not None and not a.__dict__.get('_lcb_patched', False):
+        _rebind(a, 'search_scale_subset', _awq_search)
         a._lcb_patched = True
         done.append('Awq')
-    s = registry.get('SmoothQuant')
-    if s is not None and not getattr(s, '_lcb_patched', False):
-        s.get_act_scale = _sq_act_scale(s.get_act_scale)
+    s = _lookup(registry, 'SmoothQuant')
+    if s is not None and not s.__dict__.get('_lcb_patched', False):
+        _rebind(s, 'get_act_scale', _sq_act_scale)
         s._lcb_patched = True
         done.append('SmoothQuant')
     return done

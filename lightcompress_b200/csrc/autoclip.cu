@@ -1,14 +1,24 @@
 // autoclip.cu — AutoClip v1 search (auto_clip.py:84-191): for every (output channel, group) pick the shrink step
 // i_s in [0, n_steps) whose clamped + fake-quantized weights reproduce the layer output best on the sampled tokens.
 //
-//   ac_init_kernel   : org_max / org_min per (row, group) (clip_sym: org_max = |w|.amax), best = org, min_err = 1e9
-//   tc_gemm (grouped): org_out[g] = rd(W_g x_g^T)                          (EPI_STORE16, K = group_size per group)
-//   per step         : lcb_fakequant with spec.clip_ratio = +/- (1 - i_s / n_grid)   (clamp fused into the quant kernel)
-//                      tc_gemm (grouped, EPI_ROWSSE): sse[r, g] = sum_t rd(rd(rd(out) - org)^2)   (no output tensor)
-//                      ac_update_kernel: err = rd(sse / T); strict < keeps the first minimum like the reference loop
-// The reference materialises x * w as a [256, tok, C] tensor per step; here a step is one fake-quant pass over W and one
-// tensor-core pass whose epilogue reduces over tokens. Products are exact and summed in fp32 (the reference rounds each
-// product to the tensor dtype first), so near-tied steps can resolve differently: tests report the agreement.
+//   ac_init_kernel    : org_max / org_min per (row, group) (clip_sym: org_max = |w|.amax), best = org, min_err = 1e9
+//   ac_literal_kernel : out[r, g, t] = rd( sum_j rd(x[t, g, j] * w[r, g, j]) )  — the reference's `(x * w).sum(dim=-1)`
+//                       (auto_clip.py:137, 148) LITERALLY: every product is rounded to the tensor dtype (one packed
+//                       HMUL2 per two products), the sum runs in fp32 and is rounded once. ORG mode stores it
+//                       (org_out); STEP mode compares it with org_out: err = rd(mean_t rd(rd(out - org)^2)), and keeps
+//                       the step when err < min_err (strict: the first minimum wins, like the reference loop).
+//   per step          : lcb_fakequant with spec.clip_ratio = +/- (1 - i_s / n_grid)   (clamp fused into the quant kernel)
+//                       then ac_literal_kernel<STEP>.
+// Round 1 ran the products on tcgen05 (exact products summed in fp32): 3.6x faster, but the per-product rounding of the
+// reference moves ~30 % of the outputs by one ulp of the tensor dtype, which moves the bf16-rounded error mean and picked
+// another shrink step for 3-15 % of the (channel, group) pairs. The selected index is the contract (north star: "same
+// selected clip index"), so the arithmetic is the reference's. The reference materialises x * w as a [256, tok, C] tensor
+// per step (1 GiB at Llama-3-8B shapes); here a thread owns one (row, group), keeps the 128 weights of its row in 64
+// packed registers and streams token tiles from shared memory (broadcast LDS.128): no intermediate tensor.
+// What cannot be pinned: the ORDER of torch's fp32 sum over the 128 rounded products (CPU: vectorised cascade, CUDA: a
+// tree of per-thread partials). Here: even elements in order, odd elements in order, then one add. A different order
+// changes the fp32 sum by ~1e-7 relative, which matters only when that sum lies within that distance of a rounding
+// boundary of the tensor dtype (probability ~2^-15 per output).
 #include "tc_gemm.cuh"
 
 namespace lcb {
@@ -42,21 +52,134 @@ __global__ void __launch_bounds__(256) ac_init_kernel(const T* __restrict__ W, T
   }
 }
 
+// packed pair product rounded to the tensor dtype (IEEE RN, subnormals kept), accumulated in fp32
 template <typename T>
-__global__ void __launch_bounds__(256) ac_update_kernel(const double* __restrict__ sse, const float* __restrict__ omax,
-                                                        const float* __restrict__ omin, float* __restrict__ min_err,
-                                                        T* __restrict__ best_max, T* __restrict__ best_min, int64_t n_units,
-                                                        float ratio, float tokens, int clip_sym) {
-  const int64_t u = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (u >= n_units) return;
-  // .pow(2).mean(dim=1): fp32 accumulation, one division, rounded to the tensor dtype (auto_clip.py:150)
-  const float err = TI<T>::rd(__fdiv_rn((float)sse[u], tokens));
-  if (err < min_err[u]) {
-    const float mxv = TI<T>::rd(__fmul_rn(omax[u], ratio));                         // org_max_val * (1 - i_s / n_grid)
-    const float mnv = clip_sym ? -mxv : TI<T>::rd(__fmul_rn(omin[u], ratio));
-    min_err[u] = err;
-    TI<T>::store1(best_max + u, mxv);
-    TI<T>::store1(best_min + u, mnv);
+struct P2;
+template <>
+struct P2<__nv_bfloat16> {
+  __device__ __forceinline__ static void mul_acc(uint32_t a, uint32_t b, float& even, float& odd) {
+    __nv_bfloat162 p = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    const uint32_t u = *reinterpret_cast<const uint32_t*>(&p);
+    even = __fadd_rn(even, __uint_as_float(u << 16));
+    odd = __fadd_rn(odd, __uint_as_float(u & 0xffff0000u));
+  }
+};
+template <>
+struct P2<__half> {
+  __device__ __forceinline__ static void mul_acc(uint32_t a, uint32_t b, float& even, float& odd) {
+    __half2 p = __hmul2(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+    const float2 f = __half22float2(p);
+    even = __fadd_rn(even, f.x);
+    odd = __fadd_rn(odd, f.y);
+  }
+};
+
+constexpr int AC_ROWS = 128;   // rows (threads) per CTA
+constexpr int AC_TOK = 16;     // tokens per shared-memory tile
+constexpr int AC_COLS = 128;   // columns per tile (= one group for group_size 128)
+
+// grid (ceil(R / 128), C / gs). ORG: writes org[(g * R + r) * T_rows + t]. STEP: reads it, updates best_* / min_err.
+template <typename T, bool ORG>
+__global__ void __launch_bounds__(AC_ROWS) ac_literal_kernel(const T* __restrict__ Wq, const T* __restrict__ x, T* __restrict__ org,
+                                                            const float* __restrict__ omax, const float* __restrict__ omin,
+                                                            float* __restrict__ min_err, T* __restrict__ best_max,
+                                                            T* __restrict__ best_min, int64_t R, int64_t C, int64_t T_rows,
+                                                            int gs, float ratio, float tokens, int clip_sym) {
+  __shared__ __align__(16) uint4 xs[2][AC_TOK * AC_COLS / 8];
+  const int64_t r = (int64_t)blockIdx.x * AC_ROWS + threadIdx.x;
+  const int g = blockIdx.y;
+  const bool live = r < R;
+  const int njc = gs / AC_COLS > 0 ? gs / AC_COLS : 1;
+  const int cols = gs < AC_COLS ? gs : AC_COLS;            // gs: a multiple of 8 up to 128, or k * 128
+  const int nv = cols / 8;                                  // uint4 per tile row
+  const T* wrow = Wq + (live ? r : 0) * C + (int64_t)g * gs;
+  const T* xcol = x + (int64_t)g * gs;
+  T* orow = org + ((int64_t)g * R + (live ? r : 0)) * T_rows;
+  uint32_t w[AC_COLS / 2];
+  auto load_w = [&](int jc) {
+#pragma unroll
+    for (int k = 0; k < AC_COLS / 8; ++k) {
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (k < nv) v = *reinterpret_cast<const uint4*>(wrow + (int64_t)jc * AC_COLS + k * 8);
+      w[4 * k] = v.x;
+      w[4 * k + 1] = v.y;
+      w[4 * k + 2] = v.z;
+      w[4 * k + 3] = v.w;
+    }
+  };
+  auto stage = [&](int buf, int64_t t0, int jc) {             // x[t0 .. t0+16, g*gs + jc*128 .. +cols] -> shared memory
+    for (int i = threadIdx.x; i < AC_TOK * nv; i += AC_ROWS) {
+      const int t = i / nv, k = i - t * nv;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (t0 + t < T_rows) v = *reinterpret_cast<const uint4*>(xcol + (t0 + t) * C + (int64_t)jc * AC_COLS + k * 8);
+      xs[buf][t * (AC_COLS / 8) + k] = v;
+    }
+  };
+  if (njc == 1) load_w(0);
+  double sse = 0.0;
+  const int64_t ntile = (T_rows + AC_TOK - 1) / AC_TOK * njc;
+  stage(0, 0, 0);
+  __syncthreads();
+  float even[AC_TOK], odd[AC_TOK];
+  for (int64_t it = 0; it < ntile; ++it) {
+    const int64_t t0 = it / njc * AC_TOK;
+    const int jc = (int)(it % njc);
+    const int buf = (int)(it & 1);
+    if (it + 1 < ntile) stage(buf ^ 1, (it + 1) / njc * AC_TOK, (int)((it + 1) % njc));   // the other buffer: free since the last barrier
+    if (jc == 0) {
+#pragma unroll
+      for (int t = 0; t < AC_TOK; ++t) even[t] = odd[t] = 0.f;
+    }
+    if (njc > 1) load_w(jc);
+    if (live) {
+#pragma unroll
+      for (int t = 0; t < AC_TOK; ++t) {
+#pragma unroll
+        for (int k = 0; k < AC_COLS / 8; ++k) {
+          if (k < nv) {
+            const uint4 xv = xs[buf][t * (AC_COLS / 8) + k];
+            P2<T>::mul_acc(xv.x, w[4 * k], even[t], odd[t]);
+            P2<T>::mul_acc(xv.y, w[4 * k + 1], even[t], odd[t]);
+            P2<T>::mul_acc(xv.z, w[4 * k + 2], even[t], odd[t]);
+            P2<T>::mul_acc(xv.w, w[4 * k + 3], even[t], odd[t]);
+          }
+        }
+      }
+      if (jc == njc - 1) {
+        float out[AC_TOK];
+#pragma unroll
+        for (int t = 0; t < AC_TOK; ++t) out[t] = TI<T>::rd(__fadd_rn(even[t], odd[t]));
+#pragma unroll
+        for (int h = 0; h < AC_TOK / 8; ++h) {
+          if (t0 + h * 8 < T_rows) {                       // T_rows % 8 == 0
+            if (ORG) {
+              *reinterpret_cast<uint4*>(orow + t0 + h * 8) = TI<T>::pack(out + h * 8);
+            } else {
+              float o[8];
+              TI<T>::unpack(*reinterpret_cast<const uint4*>(orow + t0 + h * 8), o);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float d = TI<T>::rd(__fsub_rn(out[h * 8 + i], o[i]));       // cur_out - org_out
+                sse += (double)TI<T>::rd(__fmul_rn(d, d));                          // .pow(2)
+              }
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (!ORG && live) {
+    const int64_t u = r * gridDim.y + g;
+    // .mean(dim=1): fp32 accumulation, one division, rounded to the tensor dtype (auto_clip.py:150)
+    const float err = TI<T>::rd(__fdiv_rn((float)sse, tokens));
+    if (err < min_err[u]) {
+      const float mxv = TI<T>::rd(__fmul_rn(omax[u], ratio));                       // org_max_val * (1 - i_s / n_grid)
+      const float mnv = clip_sym ? -mxv : TI<T>::rd(__fmul_rn(omin[u], ratio));
+      min_err[u] = err;
+      TI<T>::store1(best_max + u, mxv);
+      TI<T>::store1(best_min + u, mnv);
+    }
   }
 }
 
@@ -80,24 +203,23 @@ int autoclip_typed(const void* W, const void* x, void* best_max, void* best_min,
   float* min_err = reinterpret_cast<float*>(q);
   q += align_up(nu * 4, 256);
   void* fqws = q;
-  const int fmt = TI<T>::ID == LCB_F16 ? 0 : 1;
+  (void)sse;
   ac_init_kernel<T><<<(int)((nu * 32 + 255) / 256), 256, 0, st>>>((const T*)W, (T*)best_max, (T*)best_min, omax, omin, min_err,
                                                                   nu, (int)gs, clip_sym);
   LCB_CUDA_CHECK_LAUNCH("ac_init");
-  int rc = tc_grouped_rowsse_launch(fmt, 1, W, x, org, nullptr, R, T_rows, C, gs, st);
-  if (rc != LCB_OK) return rc;
+  const dim3 grid((unsigned)((R + AC_ROWS - 1) / AC_ROWS), (unsigned)ng);
+  ac_literal_kernel<T, true><<<grid, AC_ROWS, 0, st>>>((const T*)W, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max,
+                                                       (T*)best_min, R, C, T_rows, (int)gs, 1.f, (float)tokens, clip_sym);
+  LCB_CUDA_CHECK_LAUNCH("ac_literal_org");
   lcb_quant_spec sp = *spec;
   for (int i_s = 0; i_s < n_steps; ++i_s) {
     const float ratio = (float)(1.0 - (double)i_s / (double)n_grid);
     sp.clip_ratio = clip_sym ? -ratio : ratio;
-    rc = lcb_fakequant(W, Q, nullptr, nullptr, R, C, 1, gs, &sp, 1, fqws, st);
+    int rc = lcb_fakequant(W, Q, nullptr, nullptr, R, C, 1, gs, &sp, 1, fqws, st);
     if (rc != LCB_OK) return rc;
-    if (cudaMemsetAsync(sse, 0, (size_t)nu * 8, st) != cudaSuccess) return LCB_E_CUDA;
-    rc = tc_grouped_rowsse_launch(fmt, 0, Q, x, org, sse, R, T_rows, C, gs, st);
-    if (rc != LCB_OK) return rc;
-    ac_update_kernel<T><<<(int)((nu + 255) / 256), 256, 0, st>>>(sse, omax, omin, min_err, (T*)best_max, (T*)best_min, nu,
-                                                                 ratio, (float)tokens, clip_sym);
-    LCB_CUDA_CHECK_LAUNCH("ac_update");
+    ac_literal_kernel<T, false><<<grid, AC_ROWS, 0, st>>>((const T*)Q, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max,
+                                                          (T*)best_min, R, C, T_rows, (int)gs, ratio, (float)tokens, clip_sym);
+    LCB_CUDA_CHECK_LAUNCH("ac_literal_step");
   }
   return LCB_OK;
 }
@@ -125,7 +247,7 @@ extern "C" int lcb_autoclip_search(const void* W, const void* x, void* best_max,
   if (spec->out_mode != LCB_OUT_FAKE || spec->math_dtype != spec->dtype) return LCB_E_INVALID;
   const int64_t gs = group_size > 0 ? group_size : C;
   if (C % gs) return LCB_E_SHAPE;
-  if (gs % 64 || T_rows % 8) return LCB_E_UNSUPPORTED;
+  if (gs % 8 || (gs > 128 && gs % 128) || T_rows % 8) return LCB_E_UNSUPPORTED;   // tiles of <= 128 or k * 128 columns, 16-byte vectors
   uint8_t* ws = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~uintptr_t(255));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (spec->dtype == LCB_BF16)

@@ -410,8 +410,8 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
   float* T = reinterpret_cast<float*>(ws + L.off_T);
 
   constexpr int SM_DIAG = (NB * LDS_ + NB * XLD) * 4, SM_TRSM = (NB * LDS_ + NB) * 4, SM_INV = (NB * LDS_ + NB * NB) * 4, SM_ROW = (NB * NB + NB * RW_COLS) * 4;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (attr_once.needed()) {
     if (cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_DIAG) != cudaSuccess ||
         cudaFuncSetAttribute(chol_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TRSM) != cudaSuccess ||
         cudaFuncSetAttribute(tri_inv_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_INV) != cudaSuccess ||
@@ -419,7 +419,7 @@ extern "C" int lcb_cholinv_upper(float* H, int64_t n, int64_t ld, float percdamp
       set_last_error("cudaFuncSetAttribute(cholinv)", cudaGetLastError());
       return LCB_E_CUDA;
     }
-    attr_set = true;
+    attr_once.done();
   }
   if (cudaMemsetAsync(info, 0, sizeof(int32_t), st) != cudaSuccess) return LCB_E_CUDA;
   if (percdamp != 0.f) {

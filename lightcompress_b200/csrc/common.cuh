@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp8.h>
 #include <stdint.h>
+#include <atomic>
 #include "../../include/lcb200.h"
 
 namespace lcb {
@@ -21,6 +22,24 @@ void set_last_error(const char* what, cudaError_t e);
   } while (0)
 
 constexpr int kNumSMs = 148;  // B200
+
+// cudaFuncSetAttribute is a per-device (per-context) setting: one "configured" bit per device, so that a process that
+// drives several GPUs opts every one of them in. Setting an attribute twice from two racing threads is harmless.
+struct DeviceOnce {
+  std::atomic<unsigned long long> mask{0};
+  int dev = 0;
+  bool needed() {
+    int d = 0;
+    cudaGetDevice(&d);
+    if (d < 0 || d >= 64) return true;
+    return ((mask.load(std::memory_order_acquire) >> d) & 1ull) == 0;
+  }
+  void done() {
+    int d = 0;
+    cudaGetDevice(&d);
+    if (d >= 0 && d < 64) mask.fetch_or(1ull << d, std::memory_order_release);
+  }
+};
 
 // ---------------------------------------------------------------------------------------------
 // Storage-type traits: 16-byte vectors, unpack to fp32, pack with round-to-nearest-even.

@@ -386,13 +386,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
 
 template <typename TO>
 int launch_gemm(const Maps& maps, const Params& p, int grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (attr_once.needed()) {
     if (cudaFuncSetAttribute(fp8_gemm_kernel<TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) {
       set_last_error("cudaFuncSetAttribute(fp8_gemm)", cudaGetLastError());
       return LCB_E_CUDA;
     }
-    attr_set = true;
+    attr_once.done();
   }
   fp8_gemm_kernel<TO><<<grid, NTHREADS, SMEM_BYTES, st>>>(maps, p);
   LCB_CUDA_CHECK_LAUNCH("fp8_gemm");

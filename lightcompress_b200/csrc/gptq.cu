@@ -350,14 +350,14 @@ extern "C" int lcb_gptq_weight_transform(float* W, const float* Hinv, float* Out
   __nv_bfloat16* err_hi = reinterpret_cast<__nv_bfloat16*>(ws + 2 * align_up(C * C * 2, 256));
   __nv_bfloat16* err_lo = reinterpret_cast<__nv_bfloat16*>(ws + 2 * align_up(C * C * 2, 256) + align_up(R * sb * 2, 256));
 
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (attr_once.needed()) {
     if (cudaFuncSetAttribute(gptq_block_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BLOCK_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(gptq_block_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BLOCK_SMEM) != cudaSuccess) {
       set_last_error("cudaFuncSetAttribute(gptq_block)", cudaGetLastError());
       return LCB_E_CUDA;
     }
-    attr_set = true;
+    attr_once.done();
   }
   {
     const int64_t n = C * C;

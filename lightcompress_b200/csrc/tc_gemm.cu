@@ -33,14 +33,14 @@ bool make_tmap_2d(CUtensorMap* m, const void* base, CUtensorMapDataType dt, int 
 namespace {
 template <bool AK, bool BK_, bool SY, bool NG, int EP>
 int launch_variant(const tcg::Maps& maps, const tcg::Params& p, int grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_once;
+  if (attr_once.needed()) {
     if (cudaFuncSetAttribute(tcg::gemm_kernel<AK, BK_, SY, NG, EP>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcg::SMEM_BYTES) !=
         cudaSuccess) {
       set_last_error("cudaFuncSetAttribute(tc_gemm)", cudaGetLastError());
       return LCB_E_CUDA;
     }
-    attr_set = true;
+    attr_once.done();
   }
   tcg::gemm_kernel<AK, BK_, SY, NG, EP><<<grid, tcg::NTHREADS, tcg::SMEM_BYTES, st>>>(maps, p);
   LCB_CUDA_CHECK_LAUNCH("tc_gemm");

@@ -16,6 +16,10 @@ class HostFakeQuant(object):
     def __init__(self, quantizer, device, chunk_bytes=16 << 20, depth=4):
         if quantizer.granularity not in ('per_group', 'per_channel', 'per_token'):
             raise NotImplementedError('HostFakeQuant: units must lie inside one row (per_group / per_channel / per_token)')
+        if quantizer.calib_algo != 'minmax':
+            # the mse / learnable paths allocate their own output (quant.py `_dynamic_mse`): the ring buffers would be
+            # copied back unwritten
+            raise NotImplementedError(f"HostFakeQuant: calib_algo={quantizer.calib_algo!r} (only 'minmax' writes in place)")
         self.q = quantizer
         self.dev = torch.device(device)
         self.chunk_bytes, self.depth = int(chunk_bytes), int(depth)

@@ -25,6 +25,9 @@ def _promote(*dtypes):
 _raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
 
 
+_cur_dev = torch.cuda.current_device
+
+
 def _stream(index=None):
     """cudaStream_t of torch's current stream on device `index` (raw handle: no Stream object is built)."""
     if _raw_stream is not None:
@@ -88,6 +91,40 @@ class BaseQuantizer(object):
         self.maxshrink = kwargs.get('maxshrink', 0.8)
         self.mse_grid = kwargs.get('mse_grid', 100)
         self.bins = kwargs.get('bins', 2048)
+
+    def __setattr__(self, name, value):
+        # any public attribute (bit, sym, qmin, qmax, granularity, group_size, ...) may change what a call plan encodes
+        object.__setattr__(self, name, value)
+        if name[0] != '_':
+            plans = self.__dict__.get('_plans')
+            if plans:
+                self._drop_plans()
+
+    def _drop_plans(self):
+        plans = self.__dict__.get('_plans')
+        if plans:
+            lib = _cabi._lib
+            for p in plans.values():
+                if lib is not None and p[0]:
+                    lib.lcb_fakequant_plan_destroy(p[0])
+            plans.clear()
+
+    def __del__(self):
+        try:
+            self._drop_plans()
+        except Exception:   # noqa: BLE001  (interpreter shutdown)
+            pass
+
+    def _make_plan(self, key, dev_index, u, spec):
+        """Remember the argument bundle of a dynamic fake-quant call (lcb_fakequant_plan_*): the next call with a tensor of
+        the same shape / dtype / device goes from Python to the launch in one 7-pointer ctypes call."""
+        lib = _cabi._lib or _cabi.load()
+        plans = self.__dict__.setdefault('_plans', {})
+        if len(plans) >= 64:
+            self._drop_plans()
+        h = lib.lcb_fakequant_plan_create(u.rows, u.cols, u.ur, u.uc, spec, 1)
+        if h:
+            plans[key] = (h, dev_index, lib.lcb_fakequant_plan_run)
 
     # ---- layout ---------------------------------------------------------------------------------
     def _units(self, tensor):
@@ -212,7 +249,7 @@ class BaseQuantizer(object):
             c = self.__dict__['_qrange_cache'] = (self.qmin, self.qmax, float(self.qmin), float(self.qmax))
         return c[2], c[3]
 
-    def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0, out=None):
+    def _dynamic(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0, clip=1.0, out=None, plan_key=None):
         """get_tensor_qparams [+ quant / quant_dequant] in one pass. Returns (out, scales, zeros)."""
         _require_cuda(tensor, 'dynamic quant')
         if self.calib_algo == 'hqq':   # every other value ranges by min/max here, as get_tensor_range does (quant.py:119-130)
@@ -245,6 +282,9 @@ class BaseQuantizer(object):
                 zeros = torch.empty(u.qshape, dtype=qd, device=x.device)
         with _on_device(x.device):
             self._run(x, u.rows, u.cols, u.ur, u.uc, spec, True, out, scales, zeros)
+        if plan_key is not None and out_mode == _cabi.OUT_FAKE and not want_qparams and osf == 1.0 and clip == 1.0 \
+                and not (u.ur >= u.rows and u.uc >= u.cols) and x.device.index is not None:
+            self._make_plan(plan_key, x.device.index, u, spec)
         return out, scales, zeros
 
     def _dynamic_mse(self, tensor, out_mode, out_dtype, want_qparams, osf=1.0):
@@ -511,10 +551,25 @@ class BaseQuantizer(object):
         return None
 
     def _fake_dynamic(self, tensor, args, is_weight):
+        if not args:
+            # hot path (deploy-time w_qdq, one a_qdq per linear per forward): a remembered call plan, no Python bookkeeping
+            key = (tensor.shape, tensor.dtype, tensor.device)
+            plans = self.__dict__.get('_plans')
+            p = plans.get(key) if plans else None
+            if p is not None and tensor.is_contiguous() and _cur_dev() == p[1]:
+                out = torch.empty_like(tensor)
+                st = p[2](p[0], tensor.data_ptr(), out.data_ptr(), None, None, None, _stream(p[1]))
+                if st:
+                    _cabi.check(st, 'lcb_fakequant')
+                return out
+            if self.calib_algo == 'minmax' and tensor.is_contiguous():
+                q, _, _ = self._dynamic(tensor, _cabi.OUT_FAKE, tensor.dtype, False, plan_key=key)
+                return q
         org_bit = None
         if 'current_bit' in args:
+            # quant.py:754-783 / 833-869: only `self.bit` changes for the duration of the call; qmin / qmax keep their
+            # constructor values, so the grid does not move (QUIK's buf_current_bit is bookkeeping in the reference too)
             org_bit, self.bit = self.bit, args['current_bit']
-            self._set_int_range()
         try:
             dim = 1 if is_weight else 2
             sub = self._split_mixed(tensor, args, dim)
@@ -534,9 +589,9 @@ class BaseQuantizer(object):
         finally:
             if org_bit is not None:
                 self.bit = org_bit
-                self._set_int_range()
 
     def _fake_static(self, tensor, args, is_weight):
+        # args['current_bit'] (quant.py:785-831) only renames self.bit for the call: no effect on the result
         if 'rounding' in args:
             raise NotImplementedError("args['rounding'] (AdaRound-style floor+offset) is not on the CUDA hot path")
         osf = args.get('output_scale_factor', 1) if is_weight else 1

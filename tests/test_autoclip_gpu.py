@@ -77,7 +77,7 @@ def _check_search(W, x, c, tok):
     step = torch.round((1 - ratio) * 20).long().clamp(0, errs.shape[0] - 1)
     e_sel = errs.gather(0, step.unsqueeze(0)).squeeze(0)
     e_min = errs.min(0).values
-    bad = (~same.squeeze(-1)) & (e_sel > 1.05 * e_min + 1e-12)
+    bad = (~same.squeeze(-1)) & (e_sel > 1.005 * e_min + 1e-12)      # one ulp of a bf16 / fp16 error mean
     return agree, int(bad.sum()), same.numel()
 
 
@@ -86,23 +86,26 @@ def test_autoclip_search_matches_oracle(rec):
     c = rec['case']
     W, x = inputs(c)
     agree, bad, n = _check_search(W, x, c, c['tok'])
-    assert agree >= 0.85, f'agreement {agree:.3f}'
-    assert bad <= max(1, n // 100), f'{bad} of {n} picks are not near-ties (agreement {agree:.3f})'
+    print(f'[autoclip {c}] identical (best_max, best_min) on {agree * n:.0f} of {n} (channel, group) pairs')
+    # the arithmetic is the reference's op for op; only the ORDER of the fp32 sum over a group's rounded products is not
+    # pinned (torch CPU: vectorised cascade), which can move an output by one ulp when the sum sits on a rounding boundary
+    assert agree >= 0.999 and bad == 0, f'agreement {agree:.5f}, {bad} picks are not exact ties of the oracle error curve'
 
 
 def test_autoclip_search_ragged_tokens_and_llama_shape():
     c = dict(oc=256, C=1024, tok=75, dtype='bfloat16', seed=31, bit=4, sym=False, gs=128, clip_sym=False)
     W, x = inputs(c)
     agree, bad, n = _check_search(W, x, c, c['tok'])    # 75 tokens: padded to 80 rows, mean over 75
-    assert agree >= 0.85 and bad <= max(1, n // 100), (agree, bad)
+    print(f'[autoclip ragged] identical on {agree * n:.0f} of {n}')
+    assert agree >= 0.999 and bad == 0, (agree, bad)
 
 
 def test_autoclip_rejects_unsupported():
-    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=32)
-    W = torch.randn(64, 256, device=DEV).to(torch.bfloat16)
-    x = torch.randn(16, 256, device=DEV).to(torch.bfloat16)
+    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=192)
+    W = torch.randn(64, 384, device=DEV).to(torch.bfloat16)
+    x = torch.randn(16, 384, device=DEV).to(torch.bfloat16)
     with pytest.raises(NotImplementedError):
-        ops.autoclip_search(W, x, wq, False)            # group of 32 < one 64-deep K block: no kernel, no fallback
+        ops.autoclip_search(W, x, wq, False)            # groups are tiles of <= 128 or k * 128 columns: no kernel, no fallback
     with pytest.raises(RuntimeError):
         ops.autoclip_search(W.cpu(), x.cpu(), Q.IntegerQuantizer(4, False, 'per_group', group_size=128), False)
 
@@ -128,4 +131,4 @@ def test_patch_autoclipper_contract():
     bmax, bmin = ac.auto_clip_layer(0, 'fc', W.to(DEV), [x.to(DEV)], n_sample_token=c['tok'])
     assert bmax.shape == GOLD[0]['best_max'].shape and bmax.dtype == W.dtype
     same = (bmax.cpu().view(torch.int16) == GOLD[0]['best_max'].view(torch.int16))
-    assert float(same.float().mean()) >= 0.85
+    assert float(same.float().mean()) >= 0.999

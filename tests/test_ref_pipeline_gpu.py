@@ -1,0 +1,366 @@
+"""The UNMODIFIED reference pipeline (oracle/_ref = a verbatim copy of /root/reference/llmc, assembled by
+oracle/build_ref.py) run on CUDA eager BESIDE the product on the same seeded tiny models — SURVEY.md §8c recipes 3/4.
+
+Covers the configs the reference itself ships: GPTQ `actorder: True, true_sequential: True, quant_out: True`
+(configs/quantization/methods/GPTQ/gptq_w_only.yml:31-38), `static_groups: True`, per_channel; AWQ trans v2 + clip on an
+fp16 OPT with biases (ci_check/awq_w4a16_fakequant_eval.yml) and on a GQA Llama; RTN; SmoothQuant w8a8; and INTEGRATION.md
+§3 verbatim: `patch_reference` / `patch_autoclipper` on the REAL reference classes.
+
+Bars: integer tier (RTN weights, AWQ scales given identical inputs) bit-exact; floating tier = the north star's: same
+selected AWQ candidate, GPTQ weights 1e-3-class agreement where the inputs are identical, end-to-end perplexity within
+0.01 at perplexity ~6, i.e. |d ln ppl| <= 0.01 / 6 (tests/test_ppl_gpu.py explains the synthetic-text construction).
+"""
+import copy
+import math
+
+import pytest
+import torch
+
+from lightcompress_b200 import algo
+from oracle import ref_harness as rh
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not rh.available(), reason='oracle/_ref missing: run python oracle/build_ref.py where '
+                                                            '/root/reference exists (it ships with the snapshot)')]
+DEV = torch.device('cuda:0')
+BAR = 0.01 / 6
+W4 = {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128}
+
+
+# ---- models / data ---------------------------------------------------------------------------------------------------
+def tiny_llama(seed=0, kv_heads=4, dtype=torch.bfloat16):
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(seed)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=kv_heads, max_position_embeddings=256, initializer_range=0.06)
+    return LlamaForCausalLM(cfg).to(dtype).eval()
+
+
+def tiny_opt(seed=0, dtype=torch.float16):
+    from transformers import OPTConfig, OPTForCausalLM
+    torch.manual_seed(seed)
+    cfg = OPTConfig(vocab_size=512, hidden_size=256, ffn_dim=512, num_hidden_layers=2, num_attention_heads=4,
+                    max_position_embeddings=256, word_embed_proj_dim=256, init_std=0.06)
+    m = OPTForCausalLM(cfg)
+    with torch.no_grad():   # HF initialises biases to zero: give them values so that the bias paths are exercised
+        g = torch.Generator().manual_seed(seed + 100)
+        for n, p in m.named_parameters():
+            if n.endswith('bias'):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.05)
+    return m.to(dtype).eval()
+
+
+def tokens(n, seq, seed, batch=1):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.randint(0, 512, (batch, seq), generator=g) for _ in range(n)]
+
+
+@torch.no_grad()
+def teacher_labels(model, batches):
+    model = copy.deepcopy(model).to(DEV)
+    return [model(input_ids=ids.to(DEV)).logits.float()[:, :-1].argmax(-1) for ids in batches]
+
+
+@torch.no_grad()
+def log_ppl(model, batches, labels):
+    model = model.to(DEV)
+    tot, n = 0.0, 0
+    for ids, tgt in zip(batches, labels):
+        logits = model(input_ids=ids.to(DEV)).logits.float()[:, :-1]
+        tot += float(torch.nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]), tgt.reshape(-1),
+                                                       reduction='sum'))
+        n += tgt.numel()
+    return tot / n
+
+
+def blocks_of(model):
+    return model.model.layers if hasattr(model.model, 'layers') else model.model.decoder.layers
+
+
+def linear_weights(model):
+    """name -> deployed 2-D weight of every block linear (nn.Linear in the product, EffcientFakeQuantLinear in the
+    reference: both carry `.weight` and in/out_features)."""
+    out = {}
+    for i, b in enumerate(blocks_of(model)):
+        for n, m in b.named_modules():
+            w = getattr(m, 'weight', None)
+            if torch.is_tensor(w) and w.dim() == 2 and hasattr(m, 'in_features'):
+                out[f'{i}.{n}'] = w.detach().to(DEV)
+    return out
+
+
+# ---- the two pipelines -----------------------------------------------------------------------------------------------
+def run_reference(model, mtype, qcfg, calib, patch=None):
+    m = copy.deepcopy(model)
+    opt, ad = rh.run_pipeline(m, mtype, copy.deepcopy(qcfg), [{'input_ids': ids} for ids in calib], device='cuda',
+                              patch=patch)
+    return m, opt
+
+
+def run_product(model, mtype, qcfg, calib):
+    m = copy.deepcopy(model).to(DEV)
+    ad = (algo.adapters.LlamaAdapter if mtype == 'Llama' else algo.adapters.OptAdapter)(m)
+    inp = None
+    if qcfg['method'] != 'RTN':
+        inp = ad.collect_first_block_input([{'input_ids': ids.to(DEV)} for ids in calib])
+    a = algo.ALGO_REGISTRY[qcfg['method']](ad, copy.deepcopy(qcfg), inp, None, {'calib': {'seq_len': calib[0].shape[1]},
+                                                                               'model': {'type': mtype}})
+    a.run_block_loop()
+    a.deploy('fake_quant')
+    return m, a
+
+
+def compare(ref_model, got_model, model, ev, what):
+    """Prints and returns the agreement record of two deployed models."""
+    wr, wg = linear_weights(ref_model), linear_weights(got_model)
+    assert wr.keys() == wg.keys(), (sorted(wr), sorted(wg))
+    same = {k: float((wr[k] == wg[k]).float().mean()) for k in wr}
+    rel = {k: float((wr[k].double() - wg[k].double()).norm() / wr[k].double().norm()) for k in wr}
+    lab = teacher_labels(model, ev)
+    lp = dict(float=log_ppl(copy.deepcopy(model), ev, lab), ref=log_ppl(ref_model, ev, lab), got=log_ppl(got_model, ev, lab))
+    print(f'[{what}] ln ppl float / reference / product: {lp["float"]:.5f} {lp["ref"]:.5f} {lp["got"]:.5f}; '
+          f'equal-weight fraction min {min(same.values()):.4f} mean {sum(same.values()) / len(same):.4f}; '
+          f'rel weight err max {max(rel.values()):.2e}')
+    print('    per layer equal fraction: ' + ' '.join(f'{k.replace("self_attn.", "").replace("mlp.", "")}={v:.3f}'
+                                                     for k, v in same.items()))
+    return same, rel, lp
+
+
+# ---- reference sanity: CPU eager == CUDA eager for the integer tier (SURVEY §8c "first thing to confirm") -------------
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('bit,sym,gran,kw', [(4, False, 'per_group', {'group_size': 128}), (8, True, 'per_token', {}),
+                                             (3, True, 'per_group', {'group_size': 64}), (8, True, 'per_channel', {})])
+def test_reference_cpu_equals_reference_cuda_and_product(dtype, bit, sym, gran, kw):
+    mods = rh.activate('cuda')
+    from lightcompress_b200 import quant as Q
+    g = torch.Generator().manual_seed(3)
+    w = (torch.randn(512, 1024, generator=g) * 0.02).to(dtype)
+    w[7, 5] = 0.9
+    rq = mods['quant'].IntegerQuantizer(bit, sym, gran, **kw)
+    pq = Q.IntegerQuantizer(bit, sym, gran, **kw)
+    f_cpu = rq.fake_quant_weight_dynamic(w.clone())
+    f_gpu = rq.fake_quant_weight_dynamic(w.clone().to(DEV))
+    f_got = pq.fake_quant_weight_dynamic(w.clone().to(DEV))
+    assert torch.equal(f_cpu, f_gpu.cpu()), 'reference CPU vs reference CUDA eager'
+    assert torch.equal(f_gpu, f_got), 'product vs reference CUDA eager'
+    c_cpu, s_cpu, z_cpu = rq.real_quant_weight_dynamic(w.clone())
+    c_gpu, s_gpu, z_gpu = rq.real_quant_weight_dynamic(w.clone().to(DEV))
+    c_got, s_got, z_got = pq.real_quant_weight_dynamic(w.clone().to(DEV))
+    assert torch.equal(c_cpu, c_gpu.cpu()) and torch.equal(s_cpu, s_gpu.cpu())
+    assert torch.equal(c_gpu, c_got) and torch.equal(s_gpu, s_got) and c_gpu.dtype == c_got.dtype
+    if z_gpu is not None:
+        assert torch.equal(z_cpu, z_gpu.cpu()) and torch.equal(z_gpu, z_got)
+
+
+def test_reference_copy_is_unmodified():
+    """The shipped copy is byte-identical to its source for every file (MANIFEST holds the source hashes)."""
+    import hashlib
+    import json
+    import os
+    from oracle import build_ref
+    man = json.load(open(os.path.join(build_ref.OUT, 'MANIFEST.json')))['files']
+    assert len(man) > 100
+    for rel, sha in man.items():
+        with open(os.path.join(build_ref.OUT, 'llmc', rel), 'rb') as f:
+            assert hashlib.sha256(f.read()).hexdigest() == sha, rel
+
+
+# ---- RTN --------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('wcfg', [W4, {'bit': 8, 'symmetric': True, 'granularity': 'per_channel'}])
+def test_rtn_bit_exact_vs_reference_pipeline(wcfg):
+    model = tiny_llama(seed=1)
+    q = {'method': 'RTN', 'weight': wcfg}
+    ref, _ = run_reference(model, 'Llama', q, tokens(2, 64, 5))
+    got, _ = run_product(model, 'Llama', q, tokens(2, 64, 5))
+    same, rel, lp = compare(ref, got, model, tokens(8, 128, 6), f'RTN {wcfg["granularity"]}')
+    assert min(same.values()) == 1.0
+    assert lp['ref'] == lp['got']
+
+
+# ---- GPTQ: the shipped recipe and its variants ----------------------------------------------------------------------
+GPTQ_SP = {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
+
+
+@pytest.mark.parametrize('name,weight,special,quant_out', [
+    ('shipped', W4, GPTQ_SP, True),                                         # gptq_w_only.yml verbatim
+    ('static_groups', W4, dict(GPTQ_SP, static_groups=True), True),
+    ('no_actorder_float_out', W4, dict(GPTQ_SP, actorder=False), False),
+    ('per_channel_sym', {'bit': 4, 'symmetric': True, 'granularity': 'per_channel'}, dict(GPTQ_SP, actorder=False), True),
+    ('per_channel_actorder', {'bit': 4, 'symmetric': False, 'granularity': 'per_channel'}, GPTQ_SP, False),
+])
+def test_gptq_vs_reference_pipeline(name, weight, special, quant_out):
+    model = tiny_llama(seed=2)
+    calib, ev = tokens(16, 128, 101), tokens(48, 128, 102)
+    q = {'method': 'GPTQ', 'weight': weight, 'special': special, 'quant_out': quant_out}
+    ref, ropt = run_reference(model, 'Llama', q, calib)
+    got, gopt = run_product(model, 'Llama', q, calib)
+    same, rel, lp = compare(ref, got, model, ev, f'GPTQ {name}')
+    # the reference against ITSELF with its own `chunk_num: 2` option (gptq.py:279-290: the same Hessian summed in two
+    # chunks, i.e. only the fp32 summation order changes): how far GPTQ's error feedback carries a last-bit difference
+    ref2, _ = run_reference(model, 'Llama', dict(q, special=dict(special, chunk_num=2)), calib)
+    same2, rel2, lp2 = compare(ref, ref2, model, ev, f'GPTQ {name}: reference vs reference(chunk_num=2)')
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    assert lp['ref'] - lp['float'] > 10 * BAR and math.isfinite(lp['got'])     # the bar is not vacuous
+    # q / k / v of block 0 see bit-identical inputs in both pipelines: same grid points up to Hessian-rounding flips
+    first = [same[k] for k in ('0.self_attn.q_proj', '0.self_attn.k_proj', '0.self_attn.v_proj')]
+    assert min(first) > 0.98, first
+    assert min(same.values()) > 0.5 and max(rel.values()) < 0.2, (same, rel)
+
+
+def test_gptq_per_channel_uses_the_static_qparams_of_the_original_weight():
+    """the deployed per_channel weight must sit on the grid of buf_scales (model-dtype qparams of the ORIGINAL
+    weight, gptq.py:425-452), not on scales re-derived from the compensated weight."""
+    model = tiny_llama(seed=4)
+    q = {'method': 'GPTQ', 'weight': {'bit': 4, 'symmetric': True, 'granularity': 'per_channel'},
+         'special': dict(GPTQ_SP, actorder=False), 'quant_out': False}
+    got, gopt = run_product(model, 'Llama', q, tokens(8, 128, 7))
+    from lightcompress_b200 import quant as Q
+    wq = Q.IntegerQuantizer(4, True, 'per_channel')
+    w0 = model.model.layers[0].self_attn.q_proj.weight.data.to(DEV)
+    _, s, _, _, _ = wq.get_tensor_qparams(w0)
+    wd = got.model.layers[0].self_attn.q_proj.weight.data
+    codes = (wd.float() / s.float()).round()
+    assert float(codes.abs().max()) <= 8
+    assert torch.equal(wd, (codes * s.float()).to(wd.dtype))      # exactly on the grid of the ORIGINAL weight's scales
+
+
+# ---- AWQ: OPT fp16 with biases (ci_check config) and GQA Llama --------------------------------------------------------
+AWQ_SP = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False, 'save_scale': True,
+          'scale_path': '/tmp/lcb_ref_scales'}
+
+
+def _record_clips(store):
+    def patch(mods):
+        cls = mods['auto_clip'].AutoClipper
+        if getattr(cls, '_lcb_recording', None) is not None:
+            cls._lcb_recording = store
+            return
+        orig = cls.auto_clip_layer
+
+        def rec(self, block_idx, layer_name, *a, **k):
+            mx, mn = orig(self, block_idx, layer_name, *a, **k)
+            if cls._lcb_recording is not None:
+                cls._lcb_recording[(block_idx, layer_name)] = (mx.clone(), mn.clone())
+            return mx, mn
+        cls.auto_clip_layer = rec
+        cls._lcb_recording = store
+    return patch
+
+
+@pytest.mark.parametrize('mtype,clip', [('Opt', True), ('Llama', True), ('Llama', False)])
+def test_awq_vs_reference_pipeline(mtype, clip):
+    model = tiny_opt(seed=3) if mtype == 'Opt' else tiny_llama(seed=3, kv_heads=2)
+    calib, ev = tokens(1, 64, 201, batch=16), tokens(24, 128, 202)     # bs: -1 -> one batch holding every sample
+    q = {'method': 'Awq', 'weight': W4, 'special': dict(AWQ_SP, weight_clip=clip)}
+    ref_clips = {}
+    ref, ropt = run_reference(model, mtype, q, calib, patch=_record_clips(ref_clips))
+    _record_clips(None)(rh.activate('cuda'))
+    got, gopt = run_product(model, mtype, q, calib)
+    # same selected candidate per searched subset: the applied scales agree (adjacent ratios differ by far more)
+    assert set(ropt.act_scales) == set(gopt.act_scales), (sorted(ropt.act_scales), sorted(gopt.act_scales))
+    for k, s_ref in ropt.act_scales.items():
+        s_got = gopt.act_scales[k]
+        assert torch.allclose(s_ref.float().to(DEV), s_got.float(), rtol=2e-2, atol=0), k
+    print(f'[AWQ {mtype}] selected candidate per subset:', gopt.best_index)
+    if clip:
+        agree = []
+        for (bi, name), (mx, mn) in ref_clips.items():
+            gmx, gmn = gopt.clips[(bi, name)]
+            agree.append(float(((mx.to(DEV) == gmx) & (mn.to(DEV) == gmn)).float().mean()))
+        print(f'[AWQ {mtype}] AutoClip range agreement per layer: min {min(agree):.4f} mean {sum(agree) / len(agree):.4f}')
+        assert min(agree) > 0.97, agree
+    same, rel, lp = compare(ref, got, model, ev, f'AWQ {mtype} clip={clip}')
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    if not clip:
+        assert min(same.values()) > 0.995, same
+
+
+# ---- SmoothQuant w8a8 ------------------------------------------------------------------------------------------------
+def test_smoothquant_vs_reference_pipeline():
+    model = tiny_llama(seed=5)
+    calib, ev = tokens(8, 64, 301), tokens(16, 128, 302)
+    q = {'method': 'SmoothQuant', 'weight': {'bit': 8, 'symmetric': True, 'granularity': 'per_channel'},
+         'act': {'bit': 8, 'symmetric': True, 'granularity': 'per_token'}, 'special': {'alpha': 0.8}}
+    ref, _ = run_reference(model, 'Llama', q, calib)
+    got, _ = run_product(model, 'Llama', q, calib)
+    same, rel, lp = compare(ref, got, model, ev, 'SmoothQuant w8a8')
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    assert min(same.values()) > 0.99 and max(rel.values()) < 1e-2, (same, rel)
+
+
+# ---- INTEGRATION.md §3 verbatim: the reference's own classes with their hot methods rebound ---------------------------
+_SWAPPED = {}
+
+
+def _swap_classes(mods):
+    """the reference instantiates its quantizers by name from these two modules."""
+    import lightcompress_b200 as lcb
+    for key in ('quant', 'base_blockwise_quantization'):
+        mod = mods[key]
+        for name in ('IntegerQuantizer', 'FloatQuantizer'):
+            _SWAPPED.setdefault((key, name), getattr(mod, name))
+            setattr(mod, name, getattr(lcb, name))
+
+
+def _unswap_classes(mods):
+    for (key, name), orig in _SWAPPED.items():
+        setattr(mods[key], name, orig)
+    _SWAPPED.clear()
+
+
+def _patch_all(mods):
+    reg = mods['registry'].ALGO_REGISTRY
+    done = algo.patch_reference(reg)
+    assert set(done) == {'GPTQ', 'Awq', 'SmoothQuant'}, done
+    assert algo.patch_autoclipper(mods['auto_clip'].AutoClipper)
+    return done
+
+
+def _swap_and_patch(mods):
+    _swap_classes(mods)
+    _patch_all(mods)
+
+
+def _unpatch_all(mods):
+    algo.patch.unpatch_reference(mods['registry'].ALGO_REGISTRY)
+    algo.patch.unpatch_autoclipper(mods['auto_clip'].AutoClipper)
+    _unswap_classes(mods)
+
+
+@pytest.mark.parametrize('mode', ['swap', 'patch', 'swap+patch'])
+@pytest.mark.parametrize('method', ['GPTQ', 'Awq', 'SmoothQuant'])
+def test_patch_reference_on_the_real_classes(method, mode):
+    """mode 'swap': only the quantizer classes are replaced — the reference's OWN algorithm code (its column loop, its
+    candidate loop, its AutoClipper) drives the product quantizer through every call site it has. 'patch': the
+    reference's quantizers stay, the hot methods are rebound. 'swap+patch': INTEGRATION.md §3 in full."""
+    mods = rh.activate('cuda')
+    patch = {'swap': _swap_classes, 'patch': _patch_all, 'swap+patch': _swap_and_patch}[mode]
+    if method == 'GPTQ':
+        model = tiny_llama(seed=2)
+        calib = tokens(16, 128, 101)
+        q = {'method': 'GPTQ', 'weight': W4, 'special': GPTQ_SP, 'quant_out': True}
+    elif method == 'Awq':
+        model = tiny_llama(seed=3, kv_heads=2)
+        calib = tokens(1, 64, 201, batch=16)
+        q = {'method': 'Awq', 'weight': W4, 'special': dict(AWQ_SP)}
+    else:
+        model = tiny_llama(seed=5)
+        calib = tokens(8, 64, 301)
+        q = {'method': 'SmoothQuant', 'weight': {'bit': 8, 'symmetric': True, 'granularity': 'per_channel'},
+             'act': {'bit': 8, 'symmetric': True, 'granularity': 'per_token'}, 'special': {'alpha': 0.8}}
+    ev = tokens(32, 128, 402)
+    ref, _ = run_reference(model, 'Llama', q, calib)
+    try:
+        patched, popt = run_reference(model, 'Llama', q, calib, patch=patch)
+        if 'patch' in mode:
+            assert mods['registry'].ALGO_REGISTRY[method].__dict__.get('_lcb_patched', False)
+        if 'swap' in mode:
+            import lightcompress_b200 as lcb
+            assert isinstance(popt.wquantizer, lcb.quant.BaseQuantizer)
+    finally:
+        _unpatch_all(mods)
+    same, rel, lp = compare(ref, patched, model, ev, f'INTEGRATION 3 [{mode}] {method}')
+    if mode == 'swap' and method != 'GPTQ':
+        assert min(same.values()) == 1.0, same      # integer tier only: the quantizer swap changes nothing
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    assert min(same.values()) > 0.5 and max(rel.values()) < 0.2, (same, rel)
