@@ -30,11 +30,13 @@ WORKLOAD = 'Llama-3-8B block (7 linears, 218.1M bf16 params) w4a16 asym group-12
 
 
 def peaks():
+    """(HBM GB/s, bf16 TFLOP/s sustained, source, bf16 TFLOP/s burst). Loops shorter than ~1 s are held to the BURST figure."""
     p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(p):
         d = json.load(open(p))
-        return float(d['hbm_gbs']), float(d.get('bf16_tflops_sustained', d.get('bf16_tflops', 1400.0))), 'measured'
-    return 6650.0, 1590.0, 'fallback'
+        burst = float(d.get('bf16_tflops', 1600.0))
+        return float(d['hbm_gbs']), float(d.get('bf16_tflops_sustained', burst)), 'measured', burst
+    return 6650.0, 1590.0, 'fallback', 1590.0
 
 
 class ClockSampler:
@@ -85,30 +87,58 @@ def make_weights(torch, dev, seed):
     return ws
 
 
-def cpu_baseline(steps=3, sample=('q_proj', 4096, 4096)):
-    """The oracle port (oracle/lc_oracle.c, OpenMP over all host cores) on a bounded sample of the workload."""
+def _host_cores():
+    return len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else os.cpu_count()
+
+
+def cpu_block_weights(torch):
+    g = torch.Generator().manual_seed(0)
+    return [(torch.randn(r, c, generator=g) * 0.02).to(torch.bfloat16) for _, r, c in LLAMA3_8B_BLOCK]
+
+
+def cpu_reference_step(torch, ws, q):
+    """One step of the workload on the host: fake_quant_weight_dynamic over the 7 weights of the block."""
+    t0 = time.perf_counter()
+    for w in ws:
+        q(w)
+    return time.perf_counter() - t0
+
+
+def cpu_arm():
+    """(callable(weight) -> fake-quantized weight, kind, description). The reference's OWN quantizer
+    (llmc/compression/quantization/quant.py, shipped unmodified under oracle/_ref) on CPU tensors with every host core;
+    the C/OpenMP port (oracle/lc_oracle.c) only when that copy is absent."""
     import ctypes
     import torch
-    from oracle import quant_oracle as qo
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else os.cpu_count()
+    cores = _host_cores()
     try:   # torchrun exports OMP_NUM_THREADS=1: the CPU arm is entitled to every host core it can use
         ctypes.CDLL('libgomp.so.1').omp_set_num_threads(cores)
     except OSError:
         pass
-    _, r, c = sample
-    x = (torch.randn(r, c, generator=torch.Generator().manual_seed(0)) * 0.02).to(torch.bfloat16)
+    torch.set_num_threads(cores)
+    from oracle import ref_harness
+    if ref_harness.available():
+        refq = ref_harness.load_quant_only()
+        q = refq.IntegerQuantizer(4, False, 'per_group', group_size=128)
+        return q.fake_quant_weight_dynamic, 'reference', 'IntegerQuantizer.fake_quant_weight_dynamic (quant.py:833-869) on CPU tensors'
+    from oracle import quant_oracle as qo
     kw = dict(kind=0, sym=False, qmin=0.0, qmax=15.0)
-    qo.fakequant(x, r, c, 1, 128, **kw)
-    best = 1e30
-    for _ in range(steps):
-        t0 = time.perf_counter()
-        qo.fakequant(x, r, c, 1, 128, **kw)
-        best = min(best, time.perf_counter() - t0)
-    return {'value': r * c * 4 / best / 1e9, 'unit': 'GB/s', 'cores': cores, 'kind': 'port',
-            'sample': f'{sample[0]} [{r},{c}] bf16 w4 asym g128, best of {steps} (oracle/lc_oracle.c, OpenMP)'}, best
+    return (lambda w: qo.fakequant(w, w.shape[0], w.shape[1], 1, 128, **kw)[0]), 'port', 'oracle/lc_oracle.c (OpenMP)'
 
 
-def extras(torch, dev, tf_peak):
+def cpu_baseline(steps=3):
+    """The CPU arm on the WHOLE workload (the 7 weights of one Llama-3-8B block), best of `steps`."""
+    import torch
+    fn, kind, what = cpu_arm()
+    ws = cpu_block_weights(torch)
+    cpu_reference_step(torch, ws[:2], fn)
+    best = min(cpu_reference_step(torch, ws, fn) for _ in range(steps))
+    nbytes = sum(w.numel() for w in ws) * 4
+    return {'value': nbytes / best / 1e9, 'unit': 'GB/s', 'cores': _host_cores(), 'kind': kind,
+            'sample': f'the whole step: 7 weights of one Llama-3-8B block (218.1M bf16 elements), best of {steps}; {what}'}, best
+
+
+def extras(torch, dev, tf_peak, tf_burst, hbm_peak):
     """Tensor-path numbers of the same hot path (short runs): Hessian, GPTQ update, AWQ candidate at Llama-3-8B shapes."""
     from lightcompress_b200 import ops
     from lightcompress_b200.quant import IntegerQuantizer
@@ -131,7 +161,8 @@ def extras(torch, dev, tf_peak):
     S = torch.zeros(C, C, device=dev)
     t = ev(lambda: ops.hessian_accum(S, x), 20)
     res['hessian'] = {'C': C, 'T': T, 'ms': t * 1e3, 'gemm_equiv_TFLOPs': 2.0 * T * C * C / t / 1e12,
-                      'hw_syrk_TFLOPs': 2.0 * T * C * C / t / 1e12 * 33 / 64, 'frac_of_bf16_peak_hw': 2.0 * T * C * C / t / 1e12 * 33 / 64 / tf_peak}
+                      'hw_syrk_TFLOPs': 2.0 * T * C * C / t / 1e12 * 33 / 64,
+                      'frac_of_bf16_burst_peak_hw': 2.0 * T * C * C / t / 1e12 * 33 / 64 / tf_burst}
     ops.hessian_finalize(S, 20)
     Hw = S.clone()
     ops.cholinv_upper(Hw, 0.01, check=False)
@@ -163,7 +194,94 @@ def extras(torch, dev, tf_peak):
     import gptq_bench   # GPTQ calibration of one Llama-3-8B block: 128 x 2048 tokens, 7 linears (BASELINE configs[1])
     res['gptq_calib_llama3_8b_block'] = gptq_bench.run(dev, nb=128)
     res['awq_candidate'] = {'T': T, 'R': C, 'C': C, 'ms': t * 1e3, 'TFLOPs': 2.0 * T * C * C / t / 1e12,
-                            'frac_of_bf16_peak': 2.0 * T * C * C / t / 1e12 / tf_peak}
+                            'frac_of_bf16_burst_peak': 2.0 * T * C * C / t / 1e12 / tf_burst}
+    res.update(hbm_extras(torch, dev, hbm_peak))
+    import block_bench   # END TO END through ALGO_REGISTRY on one Llama-3-8B-sized decoder block (hooked forwards included)
+    bb = block_bench.main(['gptq', 'awq'], emit=False)
+    if 'gptq_s_per_block' in bb:   # 2 T sum C^2 = 160.6 TFLOP of Hessian work per block (GEMM convention)
+        bb['gptq_frac_of_bf16_sustained'] = 160.6 / bb['gptq_s_per_block'] / tf_peak
+    res['calib_e2e'] = bb
+    return res
+
+
+def hbm_extras(torch, dev, hbm_peak):
+    """The other HBM-bound call sites of the path at the reference's own call sizes, through the reference API, one call
+    per tensor. Inputs rotate through a pool larger than the 126 MB L2 and every output stays alive until the clock
+    stops (a recycled output block would be rewritten in L2 and never reach HBM)."""
+    from lightcompress_b200.quant import FloatQuantizer, IntegerQuantizer
+    res = {}
+
+    def timed_calls(fn, xs, n_calls, graph=False):
+        keep = []
+        for i in range(3):
+            keep.append(fn(xs[i % len(xs)]))
+        keep.clear()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if graph:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for i in range(n_calls):
+                    keep.append(fn(xs[i % len(xs)]))
+            g.replay()
+            torch.cuda.synchronize()
+            a.record()
+            g.replay()
+            b.record()
+        else:
+            a.record()
+            for i in range(n_calls):
+                keep.append(fn(xs[i % len(xs)]))
+            b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) * 1e-3 / n_calls
+
+    # configs[2]: SmoothQuant w8a8 — per-token dynamic int8 fake-quant of the activation in front of every linear
+    # (module_utils.py:799-813: 224 calls per Llama-3-8B forward)
+    q8 = IntegerQuantizer(8, True, 'per_token')
+    gen = torch.Generator(device=dev).manual_seed(11)
+    act = {}
+    for shape in ((1, 2048, 4096), (8, 2048, 4096), (8, 2048, 14336)):
+        numel = shape[0] * shape[1] * shape[2]
+        pool = max(2, min(16, (300 << 20) // (numel * 2) + 1))
+        xs = [torch.randn(shape, device=dev, generator=gen, dtype=torch.float32).to(torch.bfloat16) for _ in range(pool)]
+        n_calls = max(8, min(224, (6 << 30) // (numel * 2)))
+        rec = {}
+        for mode in ('eager', 'graph'):
+            t = timed_calls(q8.fake_quant_act_dynamic, xs, n_calls, graph=(mode == 'graph'))
+            rec[mode] = {'us_per_call': t * 1e6, 'GBps': numel * 4 / t / 1e9, 'frac': numel * 4 / t / 1e9 / hbm_peak}
+        rec['calls'] = n_calls
+        act['x'.join(map(str, shape))] = rec
+        del xs
+        torch.cuda.empty_cache()
+    res['act_per_token_int8'] = act
+    # configs[4]: DeepSeek-V2-Lite MoE block, FP8 E4M3 per-block (128 x 128) real quant of the 66 x 3 expert matrices
+    f8 = FloatQuantizer('e4m3', True, 'per_block', block_size=128, use_qtorch=True)
+    ws = []
+    for _ in range(66):
+        for r, c in ((1408, 2048), (1408, 2048), (2048, 1408)):
+            ws.append((torch.randn(r, c, device=dev, generator=gen, dtype=torch.float32) * 0.02).to(torch.bfloat16))
+    nbytes = sum(w.numel() for w in ws) * 3 + sum(-(-w.shape[0] // 128) * -(-w.shape[1] // 128) for w in ws) * 4
+
+    def ev(fn, rep=3):
+        out = fn()
+        del out
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        outs = [fn() for _ in range(rep)]
+        b.record()
+        torch.cuda.synchronize()
+        del outs
+        return a.elapsed_time(b) * 1e-3 / rep
+    t_multi = ev(lambda: f8.real_quant_weights_dynamic(ws))
+    t_each = ev(lambda: [f8.real_quant_weight_dynamic(w) for w in ws])
+    res['fp8_per_block_deepseek_v2_lite_moe_block'] = {
+        'matrices': len(ws), 'bytes': nbytes,
+        'multi_launch': {'ms': t_multi * 1e3, 'GBps': nbytes / t_multi / 1e9, 'frac': nbytes / t_multi / 1e9 / hbm_peak},
+        'per_tensor_calls': {'ms': t_each * 1e3, 'GBps': nbytes / t_each / 1e9, 'frac': nbytes / t_each / 1e9 / hbm_peak}}
+    del ws
+    torch.cuda.empty_cache()
     return res
 
 
@@ -228,23 +346,27 @@ def sharded_extras(torch, dist, dev, world, rank):
 
 
 def run_reference(args):
+    """`--impl reference`: the reference's own CPU implementation of the path on the host cores — every step is the
+    whole workload (7 weights, 872 MB of algorithmic traffic), rank 0 only."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    total = 0.0
-    for _ in range(args.warmup):
-        cpu_baseline(1)
-    vals = []
-    for _ in range(args.steps):
-        cb, t = cpu_baseline(1)
-        vals.append(cb['value'])
-        total += t
-    v = sum(vals) / len(vals)
-    cb['value'] = v
+    import torch
+    fn, kind, what = cpu_arm()
+    ws = cpu_block_weights(torch)
+    nbytes = sum(w.numel() for w in ws) * 4
+    for _ in range(max(1, min(args.warmup, 3))):
+        cpu_reference_step(torch, ws, fn)
+    times = [cpu_reference_step(torch, ws, fn) for _ in range(args.steps)]
+    total = sum(times)
+    v = nbytes * args.steps / total / 1e9
+    cb = {'value': v, 'unit': 'GB/s', 'cores': _host_cores(), 'kind': kind,
+          'sample': f'every step = the whole workload (7 weights, 218.1M bf16 elements); {what}; '
+                    f'best step {nbytes / min(times) / 1e9:.2f} GB/s'}
     print(json.dumps({'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': 'GB/s', 'n_gpus': args.gpus,
                       'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': total / args.steps * 1e3,
                       'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16',
-                      'data': 'synthetic', 'config': {'workload': WORKLOAD, 'sample': cb['sample']},
+                      'data': 'synthetic', 'config': {'workload': WORKLOAD, 'device': f'host CPU, {cb["cores"]} threads'},
                       'cpu_baseline': cb,
                       'e2e': {'value': v, 'unit': 'GB/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
@@ -344,7 +466,7 @@ def main():
            'd2h_bytes_per_step': numel * 2, 'ms_per_step': e2e_ms, 'api': 'lightcompress_b200.host.HostFakeQuant.run',
            'checked': bool(torch.equal(hout[0].view(torch.int16), q.fake_quant_weight_dynamic(ws[0]).cpu().view(torch.int16)))}
 
-    hbm_peak, tf_peak, which = peaks()
+    hbm_peak, tf_peak, which, tf_burst = peaks()
     per_gpu = alg_bytes / (ms * 1e-3) / 1e9
     roofline = {'bound': 'hbm', 'kernel': 'fq_group_multi_kernel<bf16,NV=2,int,CHAIN_BF16_SMALL>', 'achieved': per_gpu,
                 'peak': hbm_peak, 'peak_source': f'{which} (MEASURED_PEAKS.json hbm_gbs)', 'unit': 'GB/s',
@@ -371,10 +493,25 @@ def main():
         e1.record()
         sync()
         pt_ms = e0.elapsed_time(e1) / args.steps
-        out['extras'] = {'per_tensor_calls_GBps': alg_bytes / (pt_ms * 1e-3) / 1e9, 'per_tensor_calls_ms': pt_ms}
+        out['extras'] = {'per_tensor_calls_GBps': alg_bytes / (pt_ms * 1e-3) / 1e9, 'per_tensor_calls_ms': pt_ms,
+                         'per_tensor_calls_frac': alg_bytes / (pt_ms * 1e-3) / 1e9 / hbm_peak}
+        # the same 7 reference-API calls recorded into a CUDA graph (what a deploy loop over many blocks would replay)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            keep = step_per_tensor()
+        gr.replay()
+        sync()
+        e0.record()
+        for _ in range(args.steps):
+            gr.replay()
+        e1.record()
+        sync()
+        g_ms = e0.elapsed_time(e1) / args.steps
+        out['extras'].update({'per_tensor_calls_graph_GBps': alg_bytes / (g_ms * 1e-3) / 1e9, 'per_tensor_calls_graph_ms': g_ms})
+        del gr, keep
         del ws, hin, hout
         torch.cuda.empty_cache()
-        out['extras'].update(extras(torch, dev, tf_peak))
+        out['extras'].update(extras(torch, dev, tf_peak, tf_burst, hbm_peak))
     if world > 1 and not args.no_extras:
         del ws, hin, hout
         torch.cuda.empty_cache()

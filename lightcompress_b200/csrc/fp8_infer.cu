@@ -26,16 +26,14 @@ __device__ __forceinline__ uint32_t cvt_e4m3x2(float lo, float hi) {
   return r;
 }
 
-// cold path of one 8-element slot: s == 0 (all-zero group: 0 / 0 = NaN like the reference), denormal / huge / NaN / inf
-// ranges — IEEE divisions throughout
-__device__ __noinline__ uint4 act_quant_slot_exact(float f0, float f1, float f2, float f3, float f4, float f5, float f6,
-                                                   float f7, float a) {   // by value: nothing of the hot path lives in local memory
-  const float s = __fdiv_rn(a, 448.0f);
-  uint4 r;
-  r.x = cvt_e4m3x2(__fdiv_rn(f0, s), __fdiv_rn(f1, s)) | (cvt_e4m3x2(__fdiv_rn(f2, s), __fdiv_rn(f3, s)) << 16);
-  r.y = cvt_e4m3x2(__fdiv_rn(f4, s), __fdiv_rn(f5, s)) | (cvt_e4m3x2(__fdiv_rn(f6, s), __fdiv_rn(f7, s)) << 16);
-  r.z = __float_as_uint(s);
-  r.w = 0;
+// The reference's only definition of act_quant is its Triton kernel (kernel.py:7-29), and Triton lowers fp32 `/` to
+// PTX div.full.f32 (seen in the PTX it generates on this B200: `div.full.f32 %s, %amax, 448.0; div.full.f32 %y, %x, %s`):
+// a full-range approximate division, <= 2 ulp, NOT the IEEE quotient. bf16 inputs put many x / s exactly on an e4m3
+// rounding tie, where the last bit of the quotient decides the code — so the same instruction is used here, for the scale
+// and for the elements (0 / 0 and inf / inf give NaN codes as in the reference, no special cases).
+__device__ __forceinline__ float div_full(float a, float b) {
+  float r;
+  asm("div.full.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
   return r;
 }
 
@@ -99,28 +97,12 @@ __device__ __forceinline__ void act_quant_chunk(const uint8_t* __restrict__ xp, 
 #pragma unroll
     for (int o = LANES / 2; o > 0; o >>= 1) a = max_nan(a, __shfl_xor_sync(0xffffffffu, a, o));
     uint32_t w[2];
-    float s;
-    // fast path (warp-uniform): every group of the warp has 1e-17 <= amax <= 1e22, so that s = RN(a / 448) and RN(x / s)
-    // are Markstein steps on correctly rounded reciprocals (tests/test_fp8_infer_oracle.py, tests/test_fq_math_identity.py)
-    if (__all_sync(0xffffffffu, a >= 1e-17f && a <= 1e22f)) {
-      const float r448 = 1.0f / 448.0f;
-      const float s0 = __fmul_rn(a, r448);
-      s = __fmaf_rn(__fmaf_rn(-448.0f, s0, a), r448, s0);
-      const float r = __frcp_rn(s);
-      float qv[8];
+    const float s = div_full(a, 448.0f);
+    float qv[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float q0 = __fmul_rn(f[i], r);
-        qv[i] = __fmaf_rn(__fmaf_rn(-s, q0, f[i]), r, q0);
-      }
-      w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
-      w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
-    } else {
-      const uint4 e = act_quant_slot_exact(f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], a);
-      w[0] = e.x;
-      w[1] = e.y;
-      s = __uint_as_float(e.z);
-    }
+    for (int i = 0; i < 8; ++i) qv[i] = div_full(f[i], s);
+    w[0] = cvt_e4m3x2(qv[0], qv[1]) | (cvt_e4m3x2(qv[2], qv[3]) << 16);
+    w[1] = cvt_e4m3x2(qv[4], qv[5]) | (cvt_e4m3x2(qv[6], qv[7]) << 16);
     if (FULL || u * rs + lane < n_live) {
       *reinterpret_cast<uint2*>(yp + (u * rs) * 8) = make_uint2(w[0], w[1]);
       if ((lane % LANES) == 0) sp[u * (rs / LANES)] = s;

@@ -126,3 +126,22 @@ def run_pipeline(hf_model, model_type, quant_cfg, calib_batches, device='cuda', 
     if deploy:
         opt.deploy(deploy)
     return opt, model
+
+
+def load_quant_only():
+    """The reference's quantizer module (llmc/compression/quantization/quant.py) WITHOUT importing the package __init__
+    (which pulls in every algorithm, vllm, transformers: ~30 s): a stub package whose __path__ is the reference
+    directory, so that quant.py's `from .utils import ceil_div` resolves. Used by bench.py's CPU arm."""
+    import types
+    name = '_lcb_refq'
+    if name + '.quant' in sys.modules:
+        return sys.modules[name + '.quant']
+    if not available():
+        raise RuntimeError('oracle/_ref is missing')
+    pkg = types.ModuleType(name)
+    pkg.__path__ = [os.path.join(build_ref.OUT, 'llmc', 'compression', 'quantization')]
+    sys.modules[name] = pkg
+    from loguru import logger
+    logger.remove()
+    logger.add(sys.stderr, level='ERROR')
+    return importlib.import_module(name + '.quant')

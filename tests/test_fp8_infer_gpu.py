@@ -1,6 +1,8 @@
 """GPU parity of the block-wise FP8 inference kernels (csrc/fp8_infer.cu through the C ABI) against the CPU oracle
 (oracle/fp8_infer_oracle.py = kernel.py:7-54, 140-242; module_utils.py:41-46).
-Bars: act_quant — scales and e4m3 codes BIT-EXACT; fp8_gemm — floating point: the tensor pipe's accumulation inside a
+Bars: act_quant — the kernel divides with PTX div.full.f32 like the reference's Triton kernel (bit-exact against THAT in
+tests/test_ref_kernels_gpu.py); this oracle divides with IEEE rounding, so here scales agree to one fp32 ulp and codes
+everywhere except on e4m3 rounding ties (each within one code step); fp8_gemm — floating point: the tensor pipe's accumulation inside a
 128-deep block is not IEEE-ordered, so the fp32 result is held to 2e-6 of the row/column scale product (|a_s| |b_s|
 448^2 * 128 bounds a block sum) and the bf16 / fp16 output to one ulp of the output dtype on every element (north star:
 1e-3 relative for floating-point outputs)."""
@@ -22,22 +24,39 @@ def _acts(shape, dtype, seed):
     return x.to(dtype)
 
 
-def _codes_equal(a, b):
+def _codes_equal(a, b, max_frac=3e-3):
+    """Same NaN pattern; codes equal except on rounding ties of x / s (div.full.f32 vs IEEE division), one step apart."""
     a, b = a.view(torch.uint8), b.view(torch.uint8)
     nan_a, nan_b = (a & 0x7f) == 0x7f, (b & 0x7f) == 0x7f
-    return bool(torch.equal(nan_a, nan_b)) and bool(torch.equal(a[~nan_a], b[~nan_b]))
+    if not bool(torch.equal(nan_a, nan_b)):
+        return False
+    x, y = a[~nan_a].to(torch.int16), b[~nan_b].to(torch.int16)
+    ne = x != y
+    if not bool(ne.any()):
+        return True
+    return float(ne.float().mean()) <= max_frac and int((x[ne] - y[ne]).abs().max()) <= 1
+
+
+def _scales_close(s, s_ref):
+    """fp32 scales within one ulp (a * rcp(448) against the IEEE quotient), NaN where the oracle has NaN."""
+    na, nb = s.isnan(), s_ref.isnan()
+    if not bool(torch.equal(na, nb)):
+        return False
+    a = s[~na].contiguous().view(torch.int32).long()
+    b = s_ref[~nb].contiguous().view(torch.int32).long()
+    return a.numel() == 0 or int((a - b).abs().max()) <= 1
 
 
 @pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16, torch.float32])
 @pytest.mark.parametrize('shape,bs', [((3, 7, 512), 128), ((1000, 128), 128), ((64, 2048), 128), ((33, 768), 64),
                                       ((5, 512), 256), ((17, 96), 32), ((9, 80), 16), ((4, 40), 8), ((1, 128), 128)])
-def test_act_quant_bit_exact(dtype, shape, bs):
+def test_act_quant_vs_ieee_oracle(dtype, shape, bs):
     x = _acts(shape, dtype, 0)
     y_ref, s_ref = fo.act_quant(x, bs)
     y, s = fi.act_quant(x.to(DEV), bs)
     assert y.dtype == F8 and y.shape == x.shape and s.dtype == torch.float32 and s.shape == s_ref.shape
-    assert torch.equal(s.cpu(), s_ref)
-    assert _codes_equal(y.cpu(), y_ref)
+    assert _scales_close(s.cpu(), s_ref)
+    assert _codes_equal(y.cpu(), y_ref, max_frac=3e-3 if x.numel() >= 4096 else 0.05)
 
 
 def test_act_quant_edge_cases():
@@ -47,9 +66,8 @@ def test_act_quant_edge_cases():
     x[3, 7] = float('inf')     # inf / inf = NaN for that element, 0 elsewhere
     y_ref, s_ref = fo.act_quant(x, 128)
     y, s = fi.act_quant(x.to(DEV), 128)
-    sr, sg = s_ref.flatten(), s.cpu().flatten()
-    assert torch.equal(sr.isnan(), sg.isnan()) and torch.equal(sr[~sr.isnan()], sg[~sg.isnan()])
-    assert _codes_equal(y.cpu(), y_ref)
+    assert _scales_close(s.cpu().flatten(), s_ref.flatten())
+    assert _codes_equal(y.cpu(), y_ref, max_frac=0.05)
     # empty input and the reference's assertions
     e, es = fi.act_quant(torch.empty(0, 128, dtype=torch.bfloat16, device=DEV))
     assert e.shape == (0, 128) and es.shape == (0, 1)
@@ -68,7 +86,7 @@ def test_act_quant_large_roundtrip_property():
     y, s = fi.act_quant(x)
     xf = x.float().view(8192, 56, 128)
     amax = xf.abs().amax(-1)
-    assert torch.equal(s, amax / torch.full_like(amax, 448.0))   # tensor / tensor: torch turns `/ scalar` into `* (1 / scalar)` on CUDA
+    assert _scales_close(s.flatten(), (amax / torch.full_like(amax, 448.0)).flatten())
     err = (y.float().view(8192, 56, 128) * s[..., None] - xf).abs()
     bound = torch.maximum(xf.abs() * 2.0 ** -4, s[..., None] * 2.0 ** -10) * 1.0001
     assert bool((err <= bound).all())
