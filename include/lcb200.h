@@ -214,6 +214,16 @@ int lcb_hessian_accum(float* S, const void* X, int64_t tokens, int64_t C, int32_
 int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C, int32_t x_dtype);
 /* H = scale * sym(S) in place: scales the upper blocks and mirrors them into the lower ones. scale = 2 / nsamples. */
 int lcb_hessian_finalize(float* S, int64_t C, double scale, void* stream);
+/*
+ * Token-sharded Hessians (replaces the all-reduce per batch of gptq.py:292-295 by ONE per linear):
+ * lcb_hessian_pack copies the maintained part of S (block row i keeps columns i*128 .., i.e. half of S) into a contiguous
+ * buffer of lcb_hessian_packed_elems(C) floats whose LAST element is this rank's batch count; the caller all-reduces
+ * (SUM) that buffer; lcb_hessian_unpack_finalize writes the sums back and applies H = (2 / total count) * sym(S) with the
+ * count read on the device — no second collective, no host synchronisation.
+ */
+int64_t lcb_hessian_packed_elems(int64_t C);
+int lcb_hessian_pack(const float* S, float* packed, int64_t C, double count, void* stream);
+int lcb_hessian_unpack_finalize(float* S, const float* packed, int64_t C, void* stream);
 
 /*
  * GPTQ blocked column update (gptq.py:199-244).

@@ -65,6 +65,9 @@ class BaseBlockwiseQuantization(object):
         # per-sample block forwards are launch-bound on a B200 (≈1 ms of host work against ≈0.3-0.6 ms of kernels for a
         # 2048-token sample): with capture-safe hooks the forward is recorded once per pass and replayed per sample
         self.use_graph = self.special.get('cuda_graph', True)
+        # ... and several calibration samples ride one block forward when the hooks only accumulate sums over tokens
+        # (GPTQ: H is a sum, nsamples counts the samples of a batch like gptq.py:258, 281-285) or when there is no hook
+        self.forward_batch = int(self.special.get('forward_batch', 16))
         self._capturing = False
         self._on_replay = []
         self._uniform = None
@@ -106,9 +109,11 @@ class BaseBlockwiseQuantization(object):
                     kw[k] = v.to(dev)
                 elif isinstance(v, tuple):
                     kw[k] = tuple(t.to(dev) if torch.is_tensor(t) else t for t in v)
-        if self.use_graph and self.graph_safe_hooks and dev.type == 'cuda' and len(data) >= 4 \
-                and self._uniform_samples(data, dev):
-            return self._block_forward_graph(block, data, may_stop)
+        if self.graph_safe_hooks and dev.type == 'cuda' and len(data) >= 2 and self._uniform_samples(data, dev):
+            if self.forward_batch > 1:
+                return self._block_forward_batched(block, data, may_stop)
+            if self.use_graph and len(data) >= 4:
+                return self._block_forward_graph(block, data, may_stop)
         out = []
         for i, x in enumerate(data):
             kw = self.input['kwargs'][i]
@@ -138,6 +143,26 @@ class BaseBlockwiseQuantization(object):
             self._uniform = all(kw.keys() == kws[0].keys() and all(same(kw[k], kws[0][k]) for k in kw) for kw in kws[1:])
         return self._uniform and all(x.shape == data[0].shape and x.dtype == data[0].dtype and x.device == dev
                                      for x in data)
+
+    def _block_forward_batched(self, block, data, may_stop):
+        """`forward_batch` samples per block forward: the same per-token arithmetic in fewer, larger GEMMs (the keyword
+        tensors — position ids / embeddings, masks — are identical for every sample, so they broadcast over the batch).
+        Outputs are handed back per sample (views), in order."""
+        kw = self.input['kwargs'][0]
+        out = []
+        B = self.forward_batch
+        for i in range(0, len(data), B):
+            part = data[i:i + B]
+            x = part[0] if len(part) == 1 else torch.cat(part, 0)
+            try:
+                y = block(x, **kw)
+            except _StopForward:
+                if not may_stop:
+                    raise
+                continue
+            y = y[0] if isinstance(y, tuple) else y
+            out.extend(y.split([p.shape[0] for p in part], 0))
+        return out
 
     def _block_forward_graph(self, block, data, may_stop):
         """Sample 0 runs eagerly (real work, and the warm-up a capture needs); the forward of sample 1 is recorded —
@@ -205,14 +230,20 @@ class BaseBlockwiseQuantization(object):
         named_linears = self.model.get_block_linears(block)
         input_feat = defaultdict(list)
         if not self.data_free:
-            handles = self.register_hooks(named_linears, input_feat)
             self.block_init(block)
-            out = self.block_forward(block)
-            if not self.quant_out:
-                self.input['data'] = out     # next block sees the float output (base_bq.py:423-428)
-            del out
-            for h in handles:
-                h.remove()
+            if self.quant_out and self.true_sequential:
+                # the float output is discarded (base_bq.py:423-426) and every subset after the first re-collects its
+                # inputs once its predecessors are quantized (:505-526): the first pass only has to reach subset 0
+                subsets = self.model.get_subsets_in_block(block)
+                input_feat.update(self._collect_inputs(block, subsets[0]['layers']))
+            else:
+                handles = self.register_hooks(named_linears, input_feat)
+                out = self.block_forward(block)
+                if not self.quant_out:
+                    self.input['data'] = out     # next block sees the float output (base_bq.py:423-428)
+                del out
+                for h in handles:
+                    h.remove()
             self.block_transform(block, input_feat, self.input['kwargs'])
             if self.quant_out:               # base_bq.py:438-449: the next block sees the fake-quantized block's output
                 self.input['data'] = self._forward_fake_quant(block, named_linears)
@@ -261,28 +292,43 @@ class BaseBlockwiseQuantization(object):
         self._done_layers.update(subset['layers'])   # every subset transformed so far stays fake-quantised (FakeQuantLinear)
         saved = {n: m.weight.data for n, m in self._done_layers.items()}
         mdt = getattr(self, 'model_dtype', None)
+        handles = []
         for n, m in self._done_layers.items():
             m.weight.data = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            if not self.w_only:                      # FakeQuantLinear.forward applies a_qdq too (module_utils.py:712-737)
+                handles.append(m.register_forward_pre_hook(self._act_hook))
+        hooks, self.graph_safe_hooks = self.graph_safe_hooks, self.graph_safe_hooks and self.w_only
+        try:
+            feat = self._collect_inputs(block, next_subset['layers'])
+        finally:
+            self.graph_safe_hooks = hooks
+            for h in handles:
+                h.remove()
+            for n, m in self._done_layers.items():
+                m.weight.data = saved[n]
+        return feat
+
+    def _collect_inputs(self, block, layers):
+        """Run the block until every module of `layers` has seen its input (cache_input_hook on each), and no further:
+        pre-hooks — the input is all the hook needs — so neither these modules' own products nor anything after them is
+        computed; the forward is cut as soon as the last of them has been reached."""
         feat = defaultdict(list)
-        # pre-hooks: the input is all the hook needs, so neither the next subset's own products nor anything after them
-        # is computed — the forward is cut as soon as the last layer of the subset has been reached
         pending = set()
 
         def pre_hook(m, x, name):
             self.cache_input_hook(m, x, None, name, feat)
             pending.discard(name)
             if not pending:
-                pending.update(next_subset['layers'])
+                pending.update(layers)
                 raise _StopForward()
 
-        pending.update(next_subset['layers'])
-        handles = [m.register_forward_pre_hook(functools.partial(pre_hook, name=n))
-                   for n, m in next_subset['layers'].items()]
-        self.block_forward(block, may_stop=True)
-        for h in handles:
-            h.remove()
-        for n, m in self._done_layers.items():
-            m.weight.data = saved[n]
+        pending.update(layers)
+        handles = [m.register_forward_pre_hook(functools.partial(pre_hook, name=n)) for n, m in layers.items()]
+        try:
+            self.block_forward(block, may_stop=True)
+        finally:
+            for h in handles:
+                h.remove()
         return feat
 
     def subset_transform(self, subset, input_feat, subset_kwargs):

@@ -22,6 +22,38 @@ def allreduce_hessian(S, nsamples):
     return float(n.item())
 
 
+def finalize_sharded_hessian(S, nsamples):
+    """H = (2 / total batches) * sym(sum over ranks of S), in place, for a token-sharded Hessian on CUDA devices: the
+    maintained half of S (upper 128-blocks) and the batch count travel in ONE all-reduce (ops.hessian_pack), the scale is
+    applied with the count read on the device (no second collective, no host sync). Returns S (now H)."""
+    from .. import ops
+    rank, ws = world()
+    if ws == 1:
+        return ops.hessian_finalize(S, nsamples)
+    packed = ops.hessian_pack(S, nsamples)
+    dist.all_reduce(packed, op=dist.ReduceOp.SUM)
+    return ops.hessian_unpack_finalize(S, packed)
+
+
+def shard_units(n_cand, n_tiles=None):
+    """Work units (candidate, row tile) of this rank for a grid search whose loss is a SUM over output rows: with
+    n_tiles = world / gcd(n_cand, world) row tiles the n_cand * n_tiles units divide evenly over the ranks (20 candidates
+    on 8 ranks: 2 tiles, 5 units each — candidate-only sharding gives 3 / 2 / 2 ...). Returns (n_tiles, [(cand, tile)])."""
+    import math
+    rank, ws = world()
+    if n_tiles is None:
+        n_tiles = ws // math.gcd(n_cand, ws)
+    units = [(u // n_tiles, u % n_tiles) for u in range(rank, n_cand * n_tiles, ws)]
+    return n_tiles, units
+
+
+def reduce_sum(t):
+    rank, ws = world()
+    if ws > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t
+
+
 def shard_candidates(n_cand):
     """Candidate indices of this rank: n = rank (mod world)."""
     rank, ws = world()

@@ -39,9 +39,7 @@ class HessianState(object):
     def finalize(self):
         """One all-reduce of (S, nsamples) over the ranks, then H = (2 / n) * sym(S)."""
         if self.H is None:
-            n = lcdist.allreduce_hessian(self.S, self.nsamples)
-            self.nsamples = n
-            self.H = ops.hessian_finalize(self.S, n)
+            self.H = lcdist.finalize_sharded_hessian(self.S, self.nsamples)   # nsamples stays this rank's own count
             self.S = None
         return self.H
 

@@ -86,9 +86,90 @@ __global__ void __launch_bounds__(256) hessian_finalize_kernel(float* __restrict
   }
 }
 
+// ---- pack / unpack of the maintained part of S (128-row block i keeps columns i*128 ..): the payload of the one all-reduce
+// of a token-sharded Hessian. Packed layout: block rows end to end, row-major inside a block row; one extra float at the
+// end carries the batch count, so that sum and count travel in ONE collective.
+__device__ __forceinline__ int64_t packed_row_offset(int64_t r, int64_t C) {
+  const int64_t bi = r >> 7, rin = r & 127;
+  // elements of block rows 0 .. bi-1: sum_{b<bi} rows_b * (C - 128 b) with rows_b = 128
+  const int64_t before = 128 * (bi * C - 128 * (bi * (bi - 1) / 2));
+  return before + rin * (C - 128 * bi);
+}
+
+template <bool PACK>
+__global__ void __launch_bounds__(256) hessian_pack_kernel(float* __restrict__ S, float* __restrict__ P, int64_t C, float count) {
+  const int64_t r = blockIdx.x;
+  const int64_t c0 = (r >> 7) << 7;
+  float* srow = S + r * C + c0;
+  float* prow = P + packed_row_offset(r, C);
+  const int64_t n = C - c0;
+  if ((n & 3) == 0 && ((reinterpret_cast<uintptr_t>(srow) | reinterpret_cast<uintptr_t>(prow)) & 15) == 0) {
+    for (int64_t i = threadIdx.x * 4; i < n; i += 1024) {
+      if (PACK) *reinterpret_cast<float4*>(prow + i) = *reinterpret_cast<const float4*>(srow + i);
+      else *reinterpret_cast<float4*>(srow + i) = *reinterpret_cast<const float4*>(prow + i);
+    }
+  } else {
+    for (int64_t i = threadIdx.x; i < n; i += 256) {
+      if (PACK) prow[i] = srow[i];
+      else srow[i] = prow[i];
+    }
+  }
+  if (PACK && r == 0 && threadIdx.x == 0) P[packed_row_offset(C, C)] = count;
+}
+
+__global__ void __launch_bounds__(256) hessian_finalize_dev_kernel(float* __restrict__ S, int64_t C, const float* __restrict__ count) {
+  __shared__ float t[32][33];
+  const float scale = 2.0f / *count;
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj < bi) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t gr = (int64_t)bi * 32 + r, gc = (int64_t)bj * 32 + tx;
+    float v = 0.f;
+    if (gr < C && gc < C) {
+      v = S[gr * C + gc] * scale;
+      if (bi != bj || tx >= r) S[gr * C + gc] = v;
+    }
+    t[r][tx] = v;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t gr = (int64_t)bj * 32 + r, gc = (int64_t)bi * 32 + tx;
+    if (gr < C && gc < C && (bi != bj || tx < r)) S[gr * C + gc] = t[tx][r];
+  }
+}
+
+inline int64_t packed_elems_host(int64_t C) {
+  int64_t n = 0;
+  for (int64_t r0 = 0; r0 < C; r0 += 128) n += std::min<int64_t>(128, C - r0) * (C - r0);
+  return n;
+}
+
 }  // namespace
 
 }  // namespace lcb
+
+extern "C" int64_t lcb_hessian_packed_elems(int64_t C) { return C < 1 ? 0 : lcb::packed_elems_host(C) + 1; }
+
+extern "C" int lcb_hessian_pack(const float* S, float* packed, int64_t C, double count, void* stream) {
+  using namespace lcb;
+  if (!S || !packed || C < 1) return LCB_E_INVALID;
+  hessian_pack_kernel<true><<<(unsigned)C, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(const_cast<float*>(S), packed, C, (float)count);
+  LCB_CUDA_CHECK_LAUNCH("hessian_pack");
+  return LCB_OK;
+}
+
+extern "C" int lcb_hessian_unpack_finalize(float* S, const float* packed, int64_t C, void* stream) {
+  using namespace lcb;
+  if (!S || !packed || C < 1) return LCB_E_INVALID;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  hessian_pack_kernel<false><<<(unsigned)C, 256, 0, st>>>(S, const_cast<float*>(packed), C, 0.f);
+  LCB_CUDA_CHECK_LAUNCH("hessian_unpack");
+  dim3 grid((unsigned)((C + 31) / 32), (unsigned)((C + 31) / 32));
+  hessian_finalize_dev_kernel<<<grid, 256, 0, st>>>(S, C, packed + (lcb_hessian_packed_elems(C) - 1));
+  LCB_CUDA_CHECK_LAUNCH("hessian_finalize_dev");
+  return LCB_OK;
+}
 
 extern "C" int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C, int32_t x_dtype) {
   if (x_dtype == LCB_F32) return tokens * C * 4 + 512;  // bf16 hi + lo copies

@@ -48,6 +48,29 @@ def hessian_finalize(S, nsamples):
     return S
 
 
+def hessian_pack(S, count):
+    """The maintained half of S (upper 128-blocks) + this rank's batch count as one contiguous fp32 buffer: the payload of
+    the single all-reduce of a token-sharded Hessian (lcb_hessian_pack)."""
+    _need_cuda(S)
+    lib = _cabi.load()
+    C = S.shape[0]
+    packed = torch.empty(int(lib.lcb_hessian_packed_elems(C)), dtype=torch.float32, device=S.device)
+    with _on_device(S.device):
+        st = lib.lcb_hessian_pack(S.data_ptr(), packed.data_ptr(), C, float(count), _stream(S.device.index))
+    _cabi.check(st, 'lcb_hessian_pack')
+    return packed
+
+
+def hessian_unpack_finalize(S, packed):
+    """In place: S <- the all-reduced sums, then H = (2 / total count) * sym(S), the count read on the device."""
+    _need_cuda(S, packed)
+    lib = _cabi.load()
+    with _on_device(S.device):
+        st = lib.lcb_hessian_unpack_finalize(S.data_ptr(), packed.data_ptr(), S.shape[0], _stream(S.device.index))
+    _cabi.check(st, 'lcb_hessian_unpack_finalize')
+    return S
+
+
 def cholinv_upper(H, percdamp=0.0, splits=3, check=True):
     """In place: H <- upper Cholesky factor of inverse(H + percdamp * mean(diag H) * I) — the damping plus
     `cholesky -> cholesky_inverse -> cholesky(upper=True)` of GPTQ.process_hessian_and_weights (gptq.py:165-174) as one

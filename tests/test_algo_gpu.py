@@ -228,3 +228,33 @@ def test_patch_reference_gptq_contract():
     assert _rel(tmp.cpu(), tmp_o) < 2e-3
     assert len(obj.groups) == C // 128 and obj.groups[0]['scale'].shape == (R, 1) and obj.groups[1]['zero'].shape == (R, 1)
     assert _rel(torch.stack([g_['scale'].reshape(-1) for g_ in obj.groups]).cpu(), sc_o) < 2e-3
+
+
+def test_batched_block_forward_equals_per_sample():
+    """`forward_batch` samples per block forward (GPTQ: the hooks only accumulate sums over tokens): same outputs per
+    sample, same Hessian and batch count as one forward per sample."""
+    model = _tiny_llama(seed=9)
+    data = _calib(n=6, seed=10)
+    cfg = {'weight': W4, 'special': {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
+                                     'true_sequential': False}}
+    res = {}
+    for fb in (1, 4):
+        c = copy.deepcopy(cfg)
+        c['special'].update(forward_batch=fb, cuda_graph=False)
+        ad = algo.adapters.LlamaAdapter(copy.deepcopy(model))
+        inp = ad.collect_first_block_input(data)
+        a = algo.ALGO_REGISTRY['GPTQ'](ad, c, inp, None, {'calib': {'seq_len': 128}})
+        blk = a.blocks[0].to(DEV)
+        a.block_idx = 0
+        a.block_init(blk)
+        handles = a.register_hooks(a.model.get_block_linears(blk), {})
+        out = a.block_forward(blk)
+        for h in handles:
+            h.remove()
+        g = a.layers_cache['mlp.down_proj']
+        res[fb] = (torch.cat(out), g.hessian.S.clone(), g.hessian.nsamples)
+    assert res[1][2] == res[4][2] == 6
+    assert res[1][0].shape == res[4][0].shape
+    assert float((res[1][0].float() - res[4][0].float()).abs().max()) <= 2e-2 * float(res[1][0].float().abs().max())
+    S1, S4 = res[1][1].triu(), res[4][1].triu()
+    assert float((S1 - S4).abs().max() / S1.abs().max()) < 1e-2      # bf16 activations of two GEMM batchings

@@ -56,3 +56,32 @@ def test_awq_candidates_same_argmin(dtype, bit, sym, gs):
     ref = torch.tensor(losses, dtype=torch.float64)
     assert float(((got - ref).abs() / ref).max()) < 2e-3
     assert int(got.argmin()) == best_i
+
+
+def test_awq_search_unit_sharding_equals_single_rank(monkeypatch):
+    """(candidate, row tile) work units (SURVEY 8e, 8 ranks -> 2 row tiles x 20 candidates): the partial sums of the fake
+    ranks add up to the single-rank losses, and the selected candidate is the same."""
+    from lightcompress_b200.algo import awq as lcawq
+    from lightcompress_b200.algo import dist as lcdist
+    x, W = _case(512, 512, 384, torch.bfloat16, 9)
+    x, W = x.to(DEV), W.to(DEV)
+    wq = Q.IntegerQuantizer(4, False, 'per_group', group_size=128)
+    sc1, best1, losses1 = lcawq.awq_search_scale(x, W, wq, 'v2')
+    world = 8
+    parts = []
+
+    def fake_reduce(t):
+        parts.append(t.clone())
+        return t
+    monkeypatch.setattr(lcdist, 'reduce_sum', fake_reduce)
+    for r in range(world):
+        monkeypatch.setattr(lcdist, 'world', lambda r=r: (r, world))
+        nt, units = lcdist.shard_units(20)
+        assert nt == 2 and len(units) == 5
+        try:
+            lcawq.awq_search_scale(x, W, wq, 'v2')
+        except RuntimeError:
+            pass        # a single fake rank sees inf for the candidates it does not own
+    total = torch.stack(parts).sum(0) / float(512 * 384)
+    assert float(((total.cpu() - losses1) .abs() / losses1).max()) < 1e-6
+    assert int(total.argmin()) == best1

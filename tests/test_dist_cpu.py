@@ -55,6 +55,15 @@ def _worker(rank, world, port, q):
     out['best'] = lcdist.argmin_across_ranks([losses_all[i] for i in cands], cands, torch.device('cpu'))
     t = torch.tensor([float(rank), 5.0 - rank])
     out['max'] = lcdist.allreduce_max(t)
+    # (candidate, row tile) work units: every unit on exactly one rank, partial sums all-reduced
+    nt, units = lcdist.shard_units(20)
+    out['units'] = (nt, units)
+    sums = torch.zeros(20, dtype=torch.float64)
+    for n, tile in units:
+        sums[n] += (n + 1) * 10.0 + tile
+    out['sums'] = lcdist.reduce_sum(sums)
+    nt3, units3 = lcdist.shard_units(3)     # 3 candidates on 2 ranks: 2 row tiles, 3 units each
+    out['units3'] = (nt3, units3)
     # expert sharding: weight i on rank i mod world, results gathered on every rank (fp8 codes travel as bytes)
     from lightcompress_b200.algo import rtn_real_quantize_sharded
     weights = {f'experts.{i}.w': torch.full((4, 8), float(i + 1)) for i in range(5)}
@@ -92,6 +101,9 @@ def test_result_only_collectives_world2():
         assert res[r]['cands'] == list(range(r, 20, 2))
         assert res[r]['best'] == (0.0, 7)          # tie between 7 (rank 1) and 11 (rank 1)... lowest index wins
         assert torch.equal(res[r]['max'], torch.tensor([1.0, 5.0]))
+        assert res[r]['units'] == (1, [(n, 0) for n in range(r, 20, 2)])
+        assert torch.equal(res[r]['sums'], torch.tensor([(n + 1) * 10.0 for n in range(20)], dtype=torch.float64))
+        assert res[r]['units3'][0] == 2 and len(res[r]['units3'][1]) == 3
         assert res[r]['expert_calls'][:3 - r] == [float(i + 1) for i in range(r, 5, 2)]     # only its own experts
         assert sorted(res[r]['experts']) == [f'experts.{i}.w' for i in range(5)]
         for i in range(5):
@@ -106,4 +118,5 @@ def test_single_process_is_identity():
     S = torch.eye(3)
     assert lcdist.allreduce_hessian(S, 5) == 5 and torch.equal(S, torch.eye(3))
     assert lcdist.shard_candidates(4) == [0, 1, 2, 3]
+    assert lcdist.shard_units(3) == (1, [(0, 0), (1, 0), (2, 0)])
     assert lcdist.argmin_across_ranks([3.0, 1.0, 1.0], [0, 1, 2], torch.device('cpu')) == (1.0, 1)

@@ -69,3 +69,28 @@ def test_hessian_llama3_8b_shape_property():
     ref = 2.0 * (x.double().t() @ (x.double() @ v))          # (X^T X) v without forming X^T X
     got = S.double() @ v
     assert float((got - ref).abs().max() / ref.abs().max()) < 2e-5
+
+
+@pytest.mark.parametrize('C', [256, 200, 1024])
+def test_pack_allreduce_payload_roundtrip(C):
+    """lcb_hessian_pack / lcb_hessian_unpack_finalize: the maintained half of S + the batch count in one buffer; two
+    'ranks' summed by hand equal the single-rank finalize."""
+    g = torch.Generator(device=DEV).manual_seed(C)
+    xs = [torch.randn(96, C, device=DEV, generator=g).to(torch.bfloat16) for _ in range(4)]
+    S_all = torch.zeros(C, C, device=DEV)
+    for x in xs:
+        ops.hessian_accum(S_all, x)
+    H_ref = ops.hessian_finalize(S_all, 4)
+    packed = None
+    for r in range(2):
+        S = torch.zeros(C, C, device=DEV)
+        for x in xs[r::2]:
+            ops.hessian_accum(S, x)
+        p = ops.hessian_pack(S, 2)
+        packed = p if packed is None else packed + p       # what all_reduce(SUM) does
+    nb = (C + 127) // 128
+    expect = sum(min(128, C - 128 * b) * (C - 128 * b) for b in range(nb)) + 1
+    assert packed.numel() == expect and float(packed[-1]) == 4.0
+    H = ops.hessian_unpack_finalize(torch.zeros(C, C, device=DEV), packed)
+    assert float((H - H_ref).abs().max() / H_ref.abs().max()) < 1e-6
+    assert torch.equal(H, H.t())
