@@ -19,6 +19,7 @@
 // tree of per-thread partials). Here: even elements in order, odd elements in order, then one add. A different order
 // changes the fp32 sum by ~1e-7 relative, which matters only when that sum lies within that distance of a rounding
 // boundary of the tensor dtype (probability ~2^-15 per output).
+#include <stdlib.h>
 #include "tc_gemm.cuh"
 
 namespace lcb {
@@ -183,6 +184,187 @@ __global__ void __launch_bounds__(AC_ROWS) ac_literal_kernel(const T* __restrict
   }
 }
 
+// ---- the same arithmetic with the fp32 SUM on the tensor pipe -----------------------------------------------------------
+// The products still come from HMUL2 (rounded to the tensor dtype, as the reference rounds them); they are formed directly
+// in the A-fragment layout of mma.sync.m16n8k16 (rows = 16 weight rows, k = 16 columns of the group) and multiplied by a
+// B fragment of ones: D[m][*] += sum_k p[m][k], fp32 accumulation. That replaces, per packed pair, two unpack operations and
+// two FADDs by 1/4 of a warp-wide MMA: ~0.65 instead of ~2.5 issued instructions per product. The tensor core's fp32 sum
+// is one more summation ORDER (see the header: which order torch uses is not pinned either).
+// Warp: 16 rows x one group (<= 128 columns, a multiple of 16), weights held as A-side fragments in 32 registers; CTA: 8
+// warps = 128 rows sharing the token tiles. Token tiles sit in shared memory PERMUTED so that the 16 packed words a lane
+// needs for a token (columns 2t, 2t+1 and 8+2t, 8+2t+1 of every 16-column block; t = lane % 4) are 64 contiguous bytes.
+// Four tokens are in flight per iteration (four independent MMA chains); lane t of a quad finishes token t0 + t.
+template <typename T>
+struct MmaOnes;
+template <>
+struct MmaOnes<__nv_bfloat16> {
+  __device__ __forceinline__ static uint32_t mul(uint32_t a, uint32_t b) {
+    __nv_bfloat162 p = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&p);
+  }
+  __device__ __forceinline__ static void mma(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3) {
+    const uint32_t one = 0x3f803f80u;
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(one), "r"(one));
+  }
+};
+template <>
+struct MmaOnes<__half> {
+  __device__ __forceinline__ static uint32_t mul(uint32_t a, uint32_t b) {
+    __half2 p = __hmul2(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&p);
+  }
+  __device__ __forceinline__ static void mma(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3) {
+    const uint32_t one = 0x3c003c00u;
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(one), "r"(one));
+  }
+};
+
+constexpr int ACM_TOK = 32;   // tokens per shared-memory tile (8 KB at 128 columns)
+
+// grid (ceil(R / 128), C / gs), 256 threads. NKB = gs / 16 (compile time: 8 for group 128). Same contract as ac_literal_kernel.
+template <typename T, bool ORG, int NKB>
+__global__ void __launch_bounds__(256) ac_mma_kernel(const T* __restrict__ Wq, const T* __restrict__ x, T* __restrict__ org,
+                                                     const float* __restrict__ omax, const float* __restrict__ omin,
+                                                     float* __restrict__ min_err, T* __restrict__ best_max, T* __restrict__ best_min,
+                                                     int64_t R, int64_t C, int64_t T_rows, float ratio, float tokens, int clip_sym) {
+  constexpr int GS = NKB * 16, WPT = GS / 2;      // packed words per token row of the group
+  __shared__ __align__(16) uint32_t xs[2][ACM_TOK * WPT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int gid = lane >> 2, tid = lane & 3;
+  const int g = blockIdx.y;
+  const int64_t r0 = (int64_t)blockIdx.x * 128 + warp * 16;
+  const int64_t ra = r0 + gid, rb = r0 + gid + 8;
+  const uint32_t* Wp = reinterpret_cast<const uint32_t*>(Wq);
+  const uint32_t* xp = reinterpret_cast<const uint32_t*>(x);
+  // A-side weight fragments: (row ra | rb) x (words tid, 4 + tid of every 16-column block)
+  uint32_t wa0[NKB], wa1[NKB], wb0[NKB], wb1[NKB];
+#pragma unroll
+  for (int kb = 0; kb < NKB; ++kb) {
+    const int64_t cw = ((int64_t)g * GS + kb * 16) / 2 + tid;
+    wa0[kb] = ra < R ? Wp[ra * (C / 2) + cw] : 0u;
+    wa1[kb] = ra < R ? Wp[ra * (C / 2) + cw + 4] : 0u;
+    wb0[kb] = rb < R ? Wp[rb * (C / 2) + cw] : 0u;
+    wb1[kb] = rb < R ? Wp[rb * (C / 2) + cw + 4] : 0u;
+  }
+  auto stage = [&](int buf, int64_t t0) {
+    for (int i = threadIdx.x; i < ACM_TOK * WPT; i += 256) {
+      const int t = i / WPT, wd = i - t * WPT;         // word wd of the group's row: block kb = wd / 8, j = wd % 8
+      const int kb = wd >> 3, j = wd & 7;
+      uint32_t v = 0u;
+      if (t0 + t < T_rows) v = xp[(t0 + t) * (C / 2) + ((int64_t)g * GS) / 2 + wd];
+      xs[buf][t * WPT + (j & 3) * (2 * NKB) + kb * 2 + (j >> 2)] = v;
+    }
+  };
+  double sse_a = 0.0, sse_b = 0.0;
+  const int64_t ntile = (T_rows + ACM_TOK - 1) / ACM_TOK;
+  stage(0, 0);
+  __syncthreads();
+  for (int64_t it = 0; it < ntile; ++it) {
+    const int buf = (int)(it & 1);
+    const int64_t t0 = it * ACM_TOK;
+    if (it + 1 < ntile) stage(buf ^ 1, t0 + ACM_TOK);
+#pragma unroll 1
+    for (int q = 0; q < ACM_TOK; q += 4) {
+      if (t0 + q >= T_rows) break;                       // T_rows % 8 == 0: whole quads
+      float c[4][4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) c[u][0] = c[u][1] = c[u][2] = c[u][3] = 0.f;
+      uint32_t xf[4][2 * NKB];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t* src = &xs[buf][(q + u) * WPT + tid * (2 * NKB)];
+#pragma unroll
+        for (int k = 0; k < 2 * NKB; k += 4) {
+          if (2 * NKB - k >= 4) {
+            const uint4 v = *reinterpret_cast<const uint4*>(src + k);
+            xf[u][k] = v.x; xf[u][k + 1] = v.y; xf[u][k + 2] = v.z; xf[u][k + 3] = v.w;
+          } else {
+            const uint2 v = *reinterpret_cast<const uint2*>(src + k);
+            xf[u][k] = v.x; xf[u][k + 1] = v.y;
+          }
+        }
+      }
+#pragma unroll
+      for (int kb = 0; kb < NKB; ++kb) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint32_t x0 = xf[u][2 * kb], x1 = xf[u][2 * kb + 1];
+          MmaOnes<T>::mma(c[u], MmaOnes<T>::mul(wa0[kb], x0), MmaOnes<T>::mul(wb0[kb], x0), MmaOnes<T>::mul(wa1[kb], x1),
+                          MmaOnes<T>::mul(wb1[kb], x1));
+        }
+      }
+      // every column of D holds the row sum: lane `tid` of a quad finishes token t0 + q + tid for rows ra and rb
+      float oa = c[0][0], ob = c[0][2];
+      if (tid == 1) { oa = c[1][0]; ob = c[1][2]; }
+      if (tid == 2) { oa = c[2][0]; ob = c[2][2]; }
+      if (tid == 3) { oa = c[3][0]; ob = c[3][2]; }
+      oa = TI<T>::rd(oa);
+      ob = TI<T>::rd(ob);
+      const int64_t t = t0 + q + tid;
+      if (ORG) {
+        if (ra < R) TI<T>::store1(org + ((int64_t)g * R + ra) * T_rows + t, oa);
+        if (rb < R) TI<T>::store1(org + ((int64_t)g * R + rb) * T_rows + t, ob);
+      } else {
+        if (ra < R) {
+          const float d = TI<T>::rd(__fsub_rn(oa, TI<T>::load1(org + ((int64_t)g * R + ra) * T_rows + t)));
+          sse_a += (double)TI<T>::rd(__fmul_rn(d, d));
+        }
+        if (rb < R) {
+          const float d = TI<T>::rd(__fsub_rn(ob, TI<T>::load1(org + ((int64_t)g * R + rb) * T_rows + t)));
+          sse_b += (double)TI<T>::rd(__fmul_rn(d, d));
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (!ORG) {
+    sse_a += __shfl_xor_sync(0xffffffffu, sse_a, 1);
+    sse_a += __shfl_xor_sync(0xffffffffu, sse_a, 2);
+    sse_b += __shfl_xor_sync(0xffffffffu, sse_b, 1);
+    sse_b += __shfl_xor_sync(0xffffffffu, sse_b, 2);
+    if (tid == 0) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int64_t r = h ? rb : ra;
+        if (r >= R) continue;
+        const int64_t u = r * gridDim.y + g;
+        const float err = TI<T>::rd(__fdiv_rn((float)(h ? sse_b : sse_a), tokens));
+        if (err < min_err[u]) {
+          const float mxv = TI<T>::rd(__fmul_rn(omax[u], ratio));
+          const float mnv = clip_sym ? -mxv : TI<T>::rd(__fmul_rn(omin[u], ratio));
+          min_err[u] = err;
+          TI<T>::store1(best_max + u, mxv);
+          TI<T>::store1(best_min + u, mnv);
+        }
+      }
+    }
+  }
+}
+
+template <typename T, bool ORG>
+int launch_ac(const T* Wq, const T* x, T* org, const float* omax, const float* omin, float* min_err, T* bmax, T* bmin, int64_t R,
+              int64_t C, int64_t T_rows, int gs, float ratio, float tokens, int clip_sym, cudaStream_t st) {
+  const unsigned ng = (unsigned)(C / gs);
+  const dim3 grid((unsigned)((R + 127) / 128), ng);
+  const bool mma_ok = (C % 2 == 0) && (T_rows % 8 == 0) && (getenv("LCB_AUTOCLIP_NO_MMA") == nullptr);
+  if (mma_ok && gs == 128) {
+    ac_mma_kernel<T, ORG, 8><<<grid, 256, 0, st>>>(Wq, x, org, omax, omin, min_err, bmax, bmin, R, C, T_rows, ratio, tokens, clip_sym);
+  } else if (mma_ok && gs == 64) {
+    ac_mma_kernel<T, ORG, 4><<<grid, 256, 0, st>>>(Wq, x, org, omax, omin, min_err, bmax, bmin, R, C, T_rows, ratio, tokens, clip_sym);
+  } else if (mma_ok && gs == 32) {
+    ac_mma_kernel<T, ORG, 2><<<grid, 256, 0, st>>>(Wq, x, org, omax, omin, min_err, bmax, bmin, R, C, T_rows, ratio, tokens, clip_sym);
+  } else {   // other group sizes (per_channel rows, groups of 8 / 16 / 24 ...): the CUDA-core sum, same arithmetic
+    ac_literal_kernel<T, ORG><<<grid, AC_ROWS, 0, st>>>(Wq, x, org, omax, omin, min_err, bmax, bmin, R, C, T_rows, gs, ratio, tokens,
+                                                        clip_sym);
+  }
+  LCB_CUDA_CHECK_LAUNCH("autoclip_literal");
+  return LCB_OK;
+}
+
 inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
 template <typename T>
@@ -207,19 +389,18 @@ int autoclip_typed(const void* W, const void* x, void* best_max, void* best_min,
   ac_init_kernel<T><<<(int)((nu * 32 + 255) / 256), 256, 0, st>>>((const T*)W, (T*)best_max, (T*)best_min, omax, omin, min_err,
                                                                   nu, (int)gs, clip_sym);
   LCB_CUDA_CHECK_LAUNCH("ac_init");
-  const dim3 grid((unsigned)((R + AC_ROWS - 1) / AC_ROWS), (unsigned)ng);
-  ac_literal_kernel<T, true><<<grid, AC_ROWS, 0, st>>>((const T*)W, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max,
-                                                       (T*)best_min, R, C, T_rows, (int)gs, 1.f, (float)tokens, clip_sym);
-  LCB_CUDA_CHECK_LAUNCH("ac_literal_org");
+  int rc = launch_ac<T, true>((const T*)W, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max, (T*)best_min, R, C, T_rows,
+                              (int)gs, 1.f, (float)tokens, clip_sym, st);
+  if (rc != LCB_OK) return rc;
   lcb_quant_spec sp = *spec;
   for (int i_s = 0; i_s < n_steps; ++i_s) {
     const float ratio = (float)(1.0 - (double)i_s / (double)n_grid);
     sp.clip_ratio = clip_sym ? -ratio : ratio;
-    int rc = lcb_fakequant(W, Q, nullptr, nullptr, R, C, 1, gs, &sp, 1, fqws, st);
+    rc = lcb_fakequant(W, Q, nullptr, nullptr, R, C, 1, gs, &sp, 1, fqws, st);
     if (rc != LCB_OK) return rc;
-    ac_literal_kernel<T, false><<<grid, AC_ROWS, 0, st>>>((const T*)Q, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max,
-                                                          (T*)best_min, R, C, T_rows, (int)gs, ratio, (float)tokens, clip_sym);
-    LCB_CUDA_CHECK_LAUNCH("ac_literal_step");
+    rc = launch_ac<T, false>((const T*)Q, (const T*)x, (T*)org, omax, omin, min_err, (T*)best_max, (T*)best_min, R, C, T_rows,
+                             (int)gs, ratio, (float)tokens, clip_sym, st);
+    if (rc != LCB_OK) return rc;
   }
   return LCB_OK;
 }

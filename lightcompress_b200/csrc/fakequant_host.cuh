@@ -28,6 +28,22 @@ static SpecD make_specd(const lcb_quant_spec* s) {
   return d;
 }
 
+// <<<grid, block, 0, st>>> with the programmatic-stream-serialization attribute (see pdl_enter in fq_group.cuh)
+template <typename... KArgs, typename... Args>
+static void launch_pdl(void (*kernel)(KArgs...), int grid, int block, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 static int grid_for(int64_t work_ctas, int ctas_per_sm) {
   int64_t cap = (int64_t)kNumSMs * ctas_per_sm;
   return (int)(work_ctas < cap ? (work_ctas < 1 ? 1 : work_ctas) : cap);
@@ -87,7 +103,7 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
     int chain = CHAIN_ANY_OUT;
     if (sp.out_mode == LCB_OUT_FAKE) chain = (KINDC == 0) ? fs.chain : CHAIN_F32;
 #define LCB_LAUNCH_GROUP_C(NVc, CH)                                                                             \
-  fq_group_kernel<T, NVc, KINDC, CH><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, lanes, sp, fs)
+  launch_pdl(fq_group_kernel<T, NVc, KINDC, CH>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, lanes, sp, fs)
 #define LCB_LAUNCH_GROUP(NVc)                                                                                   \
   {                                                                                                             \
     if (chain == CHAIN_ANY_OUT) LCB_LAUNCH_GROUP_C(NVc, CHAIN_ANY_OUT);                                         \
@@ -116,7 +132,7 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
     if (sp.out_mode == LCB_OUT_FAKE) chain = (KINDC == 0) ? fs.chain : CHAIN_F32;
     const int grid = grid_for((n_units + (8 / w) - 1) / (8 / w), 8);
 #define LCB_LAUNCH_WROW_C(CH, Wc) \
-  fq_wrow_kernel<T, KINDC, CH, Wc><<<grid, 256, 0, st>>>(in, out, scales, zeros, n_units, (int)unit_len, sp, fs)
+  launch_pdl(fq_wrow_kernel<T, KINDC, CH, Wc>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, sp, fs)
 #define LCB_LAUNCH_WROW(CH)                      \
   {                                              \
     if (w == 2) LCB_LAUNCH_WROW_C(CH, 2);        \
@@ -350,7 +366,7 @@ static int fakequant_multi_typed(const void* const* ins, void* const* outs, cons
   const FastSpec fs = make_fastspec<T>(sp);
   const int grid = grid_for((chunks + 7) / 8, 16);
 #define LCB_LAUNCH_MULTI(NVc, CH) \
-  fq_group_multi_kernel<T, NVc, 0, CH><<<grid, 256, 0, st>>>(md, (int)uc, lanes, sp, fs)
+  launch_pdl(fq_group_multi_kernel<T, NVc, 0, CH>, grid, 256, st, md, (int)uc, lanes, sp, fs)
 #define LCB_LAUNCH_MULTI_NV(CH)              \
   {                                          \
     if (nvt == 1) LCB_LAUNCH_MULTI(1, CH);   \

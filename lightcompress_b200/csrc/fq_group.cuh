@@ -289,11 +289,21 @@ __device__ __forceinline__ void fq_group_chunk(const T* __restrict__ in, void* _
   }
 }
 
+// Programmatic dependent launch: the kernel lets its successor in the stream be scheduled right away
+// (launch_dependents) and waits for its predecessor to COMPLETE and flush (wait) before touching memory — ordinary stream
+// semantics, but the successor's launch latency and CTA rasterisation overlap this kernel's tail. Back-to-back quantizer
+// calls (one per linear at deploy time, one per linear per forward for activations) are a few microseconds each.
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 template <typename T, int NV, int KINDC, int CHAIN>
 __global__ void __launch_bounds__(256)
     fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
                     void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
   constexpr int U = NV >= 8 ? 1 : 8 / NV;
+  pdl_enter();
   const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int64_t upw = (int64_t)U * (32 / lanes);
@@ -316,6 +326,7 @@ struct MultiDesc {
 template <typename T, int NV, int KINDC, int CHAIN>
 __global__ void __launch_bounds__(256)
     fq_group_multi_kernel(const __grid_constant__ MultiDesc md, int unit_len, int lanes, SpecD sp, FastSpec fs) {
+  pdl_enter();
   const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int64_t chunks = md.chunk_start[md.n];
@@ -339,6 +350,7 @@ __global__ void __launch_bounds__(256)
   constexpr int RPC = 8 / W;  // rows per CTA per iteration
   using R = Range<T>;
   __shared__ typename R::P slot[2][RPC][W];
+  pdl_enter();
   const int nvec = unit_len / VEC;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int rsub = warp / W, wsub = warp % W;

@@ -142,7 +142,7 @@ def test_gptq_graph_replayed_forward_equals_eager(monkeypatch):
     for graph in (True, False):
         q = copy.deepcopy(model)
         cfg = {'weight': W4, 'special': {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
-                                         'true_sequential': True, 'cuda_graph': graph}}
+                                         'true_sequential': True, 'cuda_graph': graph, 'forward_batch': 1}}
         n_used = len(used)
         a = _run('GPTQ', cfg, q, data)
         assert (len(used) > n_used) == graph

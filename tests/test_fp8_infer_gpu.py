@@ -192,9 +192,12 @@ def test_block_wise_forward_and_module(bias):
     ref = fo.block_wise_fp8_forward_func(x, m.weight.cpu(), m.weight_scale_inv.cpu(), 128,
                                          None if not bias else m.bias.cpu())
     assert y.dtype == torch.bfloat16 and y.shape == (3, 40, 640)
+    # the CPU oracle quantizes the activation with IEEE divisions, the kernel with div.full.f32 like the reference's Triton
+    # kernel (bit-exact against THAT composition in tests/test_ref_kernels_gpu.py): a few activation codes sit one e4m3
+    # step apart, so the outputs agree to fp8 accuracy, not to an output ulp
     d = (y.float() - ref.float()).abs()
-    assert bool((d <= 2.0 ** -7 * ref.float().abs() + 1e-3 * float(ref.float().abs().max())).all())
-    assert float((d > 0).float().mean()) < 0.02
+    assert float(d.norm() / ref.float().norm()) < 5e-3
+    assert bool((d <= 0.05 * float(ref.float().abs().max())).all())
     # and the quantised linear tracks the float one to fp8 accuracy
     full = lin.float().cpu()(x.float())
     assert float((y.float() - full).norm() / full.norm()) < 0.06

@@ -29,20 +29,24 @@ def timed(cls, name):
 method = sys.argv[1] if len(sys.argv) > 1 else 'gptq'
 dev = torch.device('cuda:0')
 from lightcompress_b200.algo import algos  # noqa: E402
+from lightcompress_b200.algo import gptq as lcgptq  # noqa: E402
 for c, n in ((bw.BaseBlockwiseQuantization, 'block_forward'), (algos.GPTQ, 'subset_transform'),
-             (algos.Awq, 'subset_transform'), (bw.BaseBlockwiseQuantization, 'rehook_next_subset')):
+             (algos.Awq, 'subset_transform'), (bw.BaseBlockwiseQuantization, 'rehook_next_subset'),
+             (bw.BaseBlockwiseQuantization, '_forward_fake_quant'), (lcgptq.HessianState, 'factor'),
+             (lcgptq.HessianState, 'finalize'), (algos.GPTQ, 'w_qdq')):
     timed(c, n)
 if method == 'awq':
     from lightcompress_b200.algo import autoclip
     timed(autoclip, 'auto_clip_block')
 if method == 'gptq':
-    sp = {'actorder': False, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
-    bb.run('GPTQ', dev, 2, 2048, sp)
+    sp = {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
+    bb.run('GPTQ', dev, 4, 2048, sp, True)
     acc.clear()
-    t = bb.run('GPTQ', dev, 128, 2048, sp)
+    t = bb.run('GPTQ', dev, 128, 2048, sp, True)
 else:
     sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
     bb.run('Awq', dev, 2, 512, sp)
     acc.clear()
     t = bb.run('Awq', dev, 128, 512, sp)
-print('wall', t, dict(acc))
+print('wall', round(t, 4), {k: round(v, 4) for k, v in acc.items()})
+# nested: block_forward is inside rehook_next_subset / _forward_fake_quant; factor / finalize / w_qdq inside the others
