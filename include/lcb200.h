@@ -281,6 +281,16 @@ int lcb_linear_mse(const void* x, const void* w, const void* org_out, double* lo
                    int32_t dtype, void* stream);
 
 /*
+ * out[t, r] = rd(sum_c x[t, c] * w[r, c] (+ bias[r]))  — torch.nn.functional.linear on 16-bit tensors, fp32 accumulation
+ * on tcgen05, one rounding to the tensor dtype. The projections INSIDE the inspect modules of Awq.search_scale_subset
+ * (awq.py:110-126: the whole attention / MLP module is run for every candidate) go through this entry point, so that the
+ * candidate loop holds no library GEMM. x [T, C], w [R, C], out [T, R] row-major contiguous; bias NULL or [R].
+ * C % 8 == 0, R % 8 == 0, 16-byte aligned bases.
+ */
+int lcb_linear(const void* x, const void* w, const void* bias, void* out, int64_t T, int64_t R, int64_t C, int32_t dtype,
+               void* stream);
+
+/*
  * AWQ scale search over n_cand candidates for a subset whose inspect module is the linear itself (awq.py:202-248):
  *   Wq = fake_quant(W * s_n[None, :]);  x_n = x / s_n;  loss[n] += sum (org_out - x_n Wq^T)^2      n = 0 .. n_cand-1
  * via lcb_scale_cols + lcb_fakequant + lcb_linear_mse. cand_scales [n_cand, C] in the tensor dtype (awq.py:100-107

@@ -56,6 +56,7 @@ SIGNATURES = {
     'lcb_cholinv_workspace_bytes': (_c_i64, [_c_i64, _c_i32]),
     'lcb_scale_cols': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_linear_mse': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_vp]),
+    'lcb_linear': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_vp]),
     'lcb_awq_candidates': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32,
                                           _c_i32, ctypes.POINTER(QuantSpec), _c_vp, _c_vp]),
     'lcb_awq_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i64, _c_i32]),

@@ -167,7 +167,7 @@ class Awq(BaseBlockwiseQuantization):
             scale, best, _ = lcawq.awq_search_scale(x, inspect.weight.data, self.wquantizer, self.trans_version)
         else:
             scale, best, _ = lcawq.awq_search_scale_module(x, layers, inspect, self.wquantizer, kwargs,
-                                                           self.trans_version)
+                                                           self.trans_version, own_gemm=self.special.get('own_gemm', True))
         self.best_index[(self.block_idx, next(iter(layers_dict)))] = best
         prefix = getattr(self.model, 'block_name_prefix', 'model.layers')
         for n in layers_dict:

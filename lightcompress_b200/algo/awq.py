@@ -81,10 +81,42 @@ def awq_search_scale(x, weight, wquantizer, version='v2', org_out=None, n_grid=N
     return best_scales, best, losses.cpu()
 
 
+class own_linears(object):
+    """While active, every 16-bit nn.Linear inside `module` computes its F.linear on the tcgen05 contraction
+    (ops.linear = lcb_linear) instead of the library GEMM: the inspect module of a multi-linear subset (the whole
+    attention / MLP, awq.py:110-126) keeps its own forward — rotary embedding, softmax(QK^T)V (torch's SDPA: a library
+    call, stated as such), activation — and only the projections change hands."""
+
+    def __init__(self, module):
+        self.mods = [m for m in module.modules()
+                     if type(m) is torch.nn.Linear and m.weight.is_cuda and m.weight.dtype in (torch.bfloat16, torch.float16)
+                     and m.in_features % 8 == 0 and m.out_features % 8 == 0]
+
+    @staticmethod
+    def _forward(m, inp):
+        if inp.dtype != m.weight.dtype or not inp.is_cuda:
+            return torch.nn.functional.linear(inp, m.weight, m.bias)
+        return ops.linear(inp, m.weight, m.bias)
+
+    def __enter__(self):
+        import functools
+        for m in self.mods:
+            m.forward = functools.partial(self._forward, m)    # instance attribute: shadows nn.Linear.forward
+        return self
+
+    def __exit__(self, *exc):
+        for m in self.mods:
+            m.__dict__.pop('forward', None)
+        return False
+
+
 @torch.no_grad()
-def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, version='v2', n_grid=N_GRID):
+def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, version='v2', n_grid=N_GRID, own_gemm=True):
     """awq.py:179-278 for any inspect module (one batch). `layers`: the nn.Linear modules that share the input x.
     Weights are restored from an on-device copy (the reference reloads a CPU state dict every candidate)."""
+    if own_gemm:
+        with own_linears(inspect_module):
+            return awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs, version, n_grid, own_gemm=False)
     kwargs = kwargs or {}
 
     def fwd(inp):

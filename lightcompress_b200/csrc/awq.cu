@@ -89,6 +89,14 @@ extern "C" int lcb_linear_mse(const void* x, const void* w, const void* org_out,
                               reinterpret_cast<cudaStream_t>(stream));
 }
 
+extern "C" int lcb_linear(const void* x, const void* w, const void* bias, void* out, int64_t T, int64_t R, int64_t C,
+                          int32_t dtype, void* stream) {
+  using namespace lcb;
+  if (!x || !w || !out) return LCB_E_INVALID;
+  if (dtype != LCB_BF16 && dtype != LCB_F16) return LCB_E_UNSUPPORTED;
+  return tc_linear_launch(dtype == LCB_F16 ? 0 : 1, x, w, bias, out, T, R, C, C, C, R, reinterpret_cast<cudaStream_t>(stream));
+}
+
 extern "C" int64_t lcb_awq_workspace_bytes(int64_t T, int64_t R, int64_t C, int32_t n_cand) {
   (void)n_cand;
   return 2 * lcb::align_up(R * C * 2, 256) + lcb::align_up(T * C * 2, 256) + lcb_fakequant_workspace_bytes() + 1024;

@@ -97,6 +97,7 @@ int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tr
   p.ld_org = 0;
   p.org_fmt = fmt;
   p.loss = nullptr;
+  p.bias = nullptr;
 
   const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   bool ok = true;
@@ -162,6 +163,7 @@ int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org,
   p.ld_org = ldo;
   p.org_fmt = fmt;
   p.loss = loss;
+  p.bias = nullptr;
   const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   bool ok = true;
   for (int s = 0; s < MAX_SEG; ++s) {
@@ -175,6 +177,54 @@ int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org,
   }
   const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
   return launch_variant<true, true, false, false, EPI_MSE>(maps, p, grid, st);
+}
+
+int tc_linear_launch(int fmt, const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
+                     int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st) {
+  using namespace tcg;
+  if (M <= 0 || N <= 0) return LCB_OK;
+  if (K <= 0) return LCB_E_INVALID;
+  if (M > (1 << 30) || N > (1 << 30) || K > (1 << 30)) return LCB_E_SHAPE;
+  if ((ldx % 8) || (ldw % 8) || (ldo % 8) || (N % 8) || (reinterpret_cast<uintptr_t>(x) & 15) ||
+      (reinterpret_cast<uintptr_t>(w) & 15) || (reinterpret_cast<uintptr_t>(out) & 15) ||
+      (bias && (reinterpret_cast<uintptr_t>(bias) & 3)))
+    return LCB_E_ALIGN;
+  Maps maps;
+  Params p;
+  p.M = (int)M;
+  p.N = (int)N;
+  p.K = (int)K;
+  p.nblk_i = (int)((M + BM - 1) / BM);
+  p.nblk_j = (int)((N + BN - 1) / BN);
+  p.n_tiles = p.nblk_i * p.nblk_j;
+  p.nsplit = 1;  // the output is rounded in the epilogue: no split-K
+  p.kb_per_split = (int)((K + BK - 1) / BK);
+  p.n_seg = 1;
+  p.n_grp = 1;
+  p.kb_grp = 0;
+  p.org_grp_stride = 0;
+  p.rowsse = nullptr;
+  p.tri_b = 0;
+  p.idesc = tc::idesc_f16(fmt, BM, BN, 0, 0);
+  p.org = out;
+  p.ld_org = ldo;
+  p.org_fmt = fmt;
+  p.loss = nullptr;
+  p.bias = bias;
+  const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  bool ok = make_tmap_2d(&maps.a[0], x, dt16, 2, M, K, ldx * 2, BM, BK) &&   // [M, K]: box 128 rows x 64 k
+            make_tmap_2d(&maps.b[0], w, dt16, 2, N, K, ldw * 2, BN, BK);     // [N, K]: box 256 rows x 64 k
+  if (!ok) {
+    set_last_error("cuTensorMapEncodeTiled", cudaErrorInvalidValue);
+    return LCB_E_CUDA;
+  }
+  for (int s = 1; s < MAX_SEG; ++s) {
+    maps.a[s] = maps.a[0];
+    maps.b[s] = maps.b[0];
+  }
+  maps.d = maps.a[0];  // unused by this epilogue
+  const int grid = p.n_tiles < kNumSMs ? p.n_tiles : kNumSMs;
+  return launch_variant<true, true, false, false, EPI_STORE16>(maps, p, grid, st);
 }
 
 int tc_grouped_rowsse_launch(int fmt, int store, const void* w, const void* x, void* org, double* rowsse, int64_t R,
@@ -208,6 +258,7 @@ int tc_grouped_rowsse_launch(int fmt, int store, const void* w, const void* x, v
   p.org_grp_stride = R * T;
   p.org_fmt = fmt;
   p.loss = nullptr;
+  p.bias = nullptr;
   p.rowsse = rowsse;
   const CUtensorMapDataType dt16 = fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   bool ok = make_tmap_2d(&maps.a[0], w, dt16, 2, R, C, C * 2, BM, BK) &&   // [R, C]: box 128 rows x 64 k

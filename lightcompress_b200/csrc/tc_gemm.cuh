@@ -52,6 +52,7 @@ struct Params {
   int64_t ld_org;
   int org_fmt;       // 0 = fp16, 1 = bf16
   double* loss;
+  const void* bias;  // EPI_STORE16: optional [N] bias of the output dtype, added in fp32 before the one rounding
 };
 
 struct Maps {
@@ -327,6 +328,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) gemm_kernel(const __grid_constant
             if (EPI == EPI_MSE) tile_sum += p.org_fmt == 1 ? mse_row32<1>(v, org_row, ncols) : mse_row32<0>(v, org_row, ncols);
             if (EPI == EPI_ROWSSE) tile_sum += p.org_fmt == 1 ? sse2_row32<1>(v, org_row, ncols) : sse2_row32<0>(v, org_row, ncols);
             if (EPI == EPI_STORE16) {
+              if (p.bias) {
+                const uint8_t* bp = reinterpret_cast<const uint8_t*>(p.bias) + (int64_t)col0 * 2;
+#pragma unroll
+                for (int c2 = 0; c2 < 16; ++c2) {
+                  if (2 * c2 < ncols) {
+                    const float2 b2 = p.org_fmt == 1 ? unpack16x2<1>(*reinterpret_cast<const uint32_t*>(bp + c2 * 4))
+                                                     : unpack16x2<0>(*reinterpret_cast<const uint32_t*>(bp + c2 * 4));
+                    v[2 * c2] = __float_as_uint(__fadd_rn(__uint_as_float(v[2 * c2]), b2.x));
+                    v[2 * c2 + 1] = __float_as_uint(__fadd_rn(__uint_as_float(v[2 * c2 + 1]), b2.y));
+                  }
+                }
+              }
               if (p.org_fmt == 1) store16_row32<1>(v, org_row, ncols); else store16_row32<0>(v, org_row, ncols);
             }
           }
@@ -398,6 +411,11 @@ int tc_gemm_launch_ex(bool a_kmajor, bool b_kmajor, bool syrk, bool neg, bool tr
 // Awq.calculate_loss (awq.py:134-145) without writing the output. x [M, K], w [N, K], org [M, N], all 16-bit row-major.
 int tc_linear_mse_launch(int fmt, const void* x, const void* w, const void* org, double* loss, int64_t M, int64_t N,
                          int64_t K, int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st);
+
+// out[t, r] = rd16(sum_k x[t, k] * w[r, k] (+ bias[r])) — F.linear on 16-bit tensors (the projections inside the inspect
+// modules of Awq.search_scale_subset, awq.py:110-126). x [M, K], w [N, K], out [M, N] row-major; bias NULL or [N].
+int tc_linear_launch(int fmt, const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
+                     int64_t ldx, int64_t ldw, int64_t ldo, cudaStream_t st);
 
 // Grouped product for AutoClip (auto_clip.py:133-156): for every group g of `gs` input channels,
 //   out_g[r, t] = sum_{c in g} w[r, c] * x[t, c]          w [R, C], x [T, C] 16-bit row-major, C = n_grp * gs, gs % 64 == 0

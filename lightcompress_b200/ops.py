@@ -190,6 +190,29 @@ def linear_mse(x, w, org_out, loss=None):
     return loss
 
 
+def linear(x, w, bias=None):
+    """torch.nn.functional.linear(x, w, bias) for 16-bit tensors on the tcgen05 contraction (lcb_linear): fp32
+    accumulation, one rounding. x [..., C], w [R, C] of the same dtype; bias None or [R]."""
+    _need_cuda(x, w)
+    C = x.shape[-1]
+    x2 = x.reshape(-1, C)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    w = w if w.is_contiguous() else w.contiguous()
+    assert x2.dtype == w.dtype and w.shape[1] == C
+    R = w.shape[0]
+    out = torch.empty((x2.shape[0], R), dtype=x.dtype, device=x.device)
+    b = None
+    if bias is not None:
+        b = bias.to(x.dtype).contiguous()
+    lib = _cabi.load()
+    with _on_device(x.device):
+        st = lib.lcb_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, out.data_ptr(),
+                            x2.shape[0], R, C, _DT[x.dtype], _stream(x.device.index))
+    _cabi.check(st, 'lcb_linear')
+    return out.reshape(*x.shape[:-1], R)
+
+
 def awq_candidates(W, x, org_out, cand_scales, wquantizer):
     """Losses (mean squared error, float64 [n_cand]) of every AWQ scale candidate for a subset whose inspect module is
     the linear itself (awq.py:202-248). cand_scales: [n_cand, C] in the tensor dtype."""

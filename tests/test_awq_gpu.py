@@ -85,3 +85,36 @@ def test_awq_search_unit_sharding_equals_single_rank(monkeypatch):
     total = torch.stack(parts).sum(0) / float(512 * 384)
     assert float(((total.cpu() - losses1) .abs() / losses1).max()) < 1e-6
     assert int(total.argmin()) == best1
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize('T,C,R,bias', [(300, 512, 384, False), (1024, 1024, 520, True), (77, 256, 8, True),
+                                        (4096, 4096, 1024, False)])
+def test_linear_matches_torch(dtype, T, C, R, bias):
+    """lcb_linear = F.linear on tcgen05: fp32 accumulation, ONE rounding to the tensor dtype (also after the bias)."""
+    x, W = _case(T, C, R, dtype, 3)
+    b = (torch.randn(R, generator=torch.Generator().manual_seed(4)) * 0.1).to(dtype) if bias else None
+    ref32 = x.double() @ W.double().t() + (b.double() if bias else 0.0)
+    got = ops.linear(x.to(DEV), W.to(DEV), None if b is None else b.to(DEV)).cpu()
+    assert got.dtype == dtype and got.shape == (T, R)
+    ulp = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    err = (got.double() - ref32).abs()
+    # one rounding of an fp32-accumulated sum: half an ulp of the result + the fp32 accumulation error
+    assert bool((err <= ulp * ref32.abs() * 1.01 + 1e-4 * ref32.abs().max()).all())
+    lib = torch.nn.functional.linear(x.to(DEV), W.to(DEV), None if b is None else b.to(DEV)).cpu()
+    assert float((got != lib).float().mean()) < 0.02      # the library rounds the same sums: isolated one-ulp flips only
+    x3 = x.to(DEV).reshape(1, T, C)
+    assert ops.linear(x3, W.to(DEV)).shape == (1, T, R)
+
+
+def test_own_linears_swaps_and_restores():
+    from lightcompress_b200.algo import awq as lcawq
+    mlp = torch.nn.Sequential(torch.nn.Linear(256, 512, bias=True), torch.nn.SiLU(), torch.nn.Linear(512, 256, bias=False))
+    mlp = mlp.to(torch.bfloat16).to(DEV)
+    x = torch.randn(64, 256, device=DEV).to(torch.bfloat16)
+    ref = mlp(x)
+    with lcawq.own_linears(mlp) as o:
+        assert len(o.mods) == 2 and all('forward' in m.__dict__ for m in o.mods)
+        got = mlp(x)
+    assert all('forward' not in m.__dict__ for m in mlp.modules())
+    assert float((got.float() - ref.float()).abs().max()) <= 2e-2 * float(ref.float().abs().max())
