@@ -7,5 +7,6 @@ from .awq import awq_search_scale, awq_search_scale_module, get_act_scale, get_s
 from .blockwise import ALGO_REGISTRY, RTN, BaseBlockwiseQuantization, SmoothQuant, make_quantizer  # noqa: F401
 from .gptq import GPTQLayer  # noqa: F401
 from .patch import patch_autoclipper, patch_fp8_inference, patch_reference  # noqa: F401
+from .realquant import REALQUANT_LINEAR_MAP, AutoawqRealQuantLinear, VllmRealQuantLinear  # noqa: F401
 from .rtn import rtn_quantize, rtn_real_quantize, rtn_real_quantize_sharded  # noqa: F401
 from .smoothquant import ActMax, smoothquant_scale  # noqa: F401

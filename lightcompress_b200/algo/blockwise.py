@@ -28,6 +28,11 @@ class Register(dict):
 ALGO_REGISTRY = Register()
 
 
+def _vllm_cls():
+    from .realquant import VllmRealQuantLinear
+    return VllmRealQuantLinear
+
+
 class _StopForward(Exception):
     """Raised by the re-hook pre-hooks once every layer of the next subset has seen its input: the rest of the block
     forward (whose output nobody reads, base_bq.py:505-526) is not computed."""
@@ -377,18 +382,25 @@ class BaseBlockwiseQuantization(object):
         for name in layers_dict:
             input_feat[name] = [ops.scale_cols(x, scale.to(x.dtype), div=True) for x in input_feat[name]]
 
-    # ---- deploy (base_bq.py:899-1006, fake_quant only) ------------------------------------------------------------------
+    # ---- deploy (base_bq.py:933-962) ------------------------------------------------------------------------------------
     @torch.no_grad()
     def deploy(self, quant_format='fake_quant'):
+        """'fake_quant': every block linear keeps its class and gets the fake-quantized weight (+ the activation
+        fake-quant in front when w+a) — what EffcientFakeQuantLinear computes. '<backend>_quant' (vllm / lightllm / sgl /
+        lightx2v / autoawq / mlcllm): every block linear is REPLACED by the backend's real-quant module holding codes,
+        scales (and zero-points), quantized by `w_q` and packed on the GPU (algo/realquant.py)."""
+        from .realquant import REALQUANT_LINEAR_MAP
         if quant_format == 'origin_float':
             return
-        if quant_format != 'fake_quant':
-            raise NotImplementedError('real-quant export formats are out of scope (SURVEY.md §8f N3); use '
-                                      'wquantizer.real_quant_weight_dynamic per layer')
+        if quant_format in REALQUANT_LINEAR_MAP:
+            return self._deploy_real(REALQUANT_LINEAR_MAP[quant_format])
+        if quant_format not in ('fake_quant', 'fake_quant_wo_kv'):
+            raise NotImplementedError(f"Quant format '{quant_format}' is not implemented.")
         for block in self.blocks:
             block.to(self.dev)
             linears = list(self.model.get_block_linears(block).values())
-            if type(self).w_qdq is BaseBlockwiseQuantization.w_qdq:
+            if type(self).w_qdq is BaseBlockwiseQuantization.w_qdq and not any(
+                    hasattr(m, 'buf_upbound_factor') or hasattr(m, 'buf_lowbound_factor') for m in linears):
                 # plain dynamic w_qdq: all linears of the block in one launch (lcb_fakequant_multi)
                 for m, q in zip(linears, self.wquantizer.fake_quant_weights_dynamic([m.weight.data for m in linears])):
                     m.weight.data = q
@@ -398,6 +410,28 @@ class BaseBlockwiseQuantization(object):
             if not self.w_only:
                 for m in linears:
                     m.register_forward_pre_hook(self._act_hook)
+
+    def _deploy_real(self, cls):
+        """model.replace_module_all(cls, {'w_q': ..., 'quant_config': ...}) (base_model.py:371-411)."""
+        w_q = functools.partial(self.w_q, wquantizer=self.wquantizer)
+        for block in self.blocks:
+            block.to(self.dev)
+            named = self.model.get_block_linears(block)
+            plain = type(self).w_q is BaseBlockwiseQuantization.w_q and hasattr(self.wquantizer, 'real_quant_weights_dynamic')
+            pre = {}
+            if plain and issubclass(cls, _vllm_cls()):
+                # dynamic w_q of every linear of the block at once: FP8 per_block expert matrices go 16 per launch
+                mods = [m for m in named.values() if not getattr(m, 'no_quant', False)
+                        and m.weight.dtype != torch.float8_e4m3fn]
+                for m, res in zip(mods, self.wquantizer.real_quant_weights_dynamic([m.weight.data for m in mods])):
+                    pre[m] = res
+            for name, m in named.items():
+                if getattr(m, 'no_quant', False):
+                    continue
+                new = cls.new(m, (lambda mod, r=pre.get(m): r) if m in pre else w_q, self.quant_config)
+                parent_name, _, child = name.rpartition('.')
+                parent = block.get_submodule(parent_name) if parent_name else block
+                setattr(parent, child, new)
 
     def _act_hook(self, module, args):
         return (self.a_qdq(args[0], module, self.aquantizer),) + tuple(args[1:])
