@@ -498,7 +498,17 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
+    # the platform ceiling of that leg: the same bytes as plain pinned copies both ways at once, no kernel
+    sys.path.insert(0, os.path.join(ROOT, 'tools'))
+    import memcpy_ceiling
+    sync()
+    ceil_s, ceil_n = memcpy_ceiling.measure(dev, total_mb=(numel * 2) >> 20, chunk_mb=16, reps=3)
+    t = torch.tensor([ceil_s], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ceiling = 2 * ceil_n * world / float(t.item()) / 1e9
     e2e = {'value': alg_bytes * world / (e2e_ms * 1e-3) / 1e9, 'unit': 'GB/s', 'h2d_bytes_per_step': numel * 2,
+           'raw_copy_ceiling_GBps': ceiling, 'frac_of_raw_copy_ceiling': alg_bytes * world / (e2e_ms * 1e-3) / 1e9 / ceiling,
            'd2h_bytes_per_step': numel * 2, 'ms_per_step': e2e_ms, 'api': 'lightcompress_b200.host.HostFakeQuant.run',
            'checked': bool(torch.equal(hout[0].view(torch.int16), q.fake_quant_weight_dynamic(ws[0]).cpu().view(torch.int16)))}
 

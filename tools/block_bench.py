@@ -8,6 +8,8 @@ GPTQ: 128 samples x 2048 tokens, w4a16 g128, actorder + true_sequential + quant_
 AWQ : 128 samples x 512 tokens, w4a16 g128, trans v2 + weight_clip (awq_w_only.yml).
 The time covers everything `block_opt` does for the block: the hooked forward(s), Hessians / searches, factorisations,
 updates, scale application, clipping — including the attention / MLP module forwards the searches need (torch ops).
+The model holds TWO such blocks and the SECOND one is the reported number: the steady state of a 32-block run, where the
+caching allocator already owns the workspaces (the first block pays their cudaMalloc; both are printed).
 """
 import json
 import os
@@ -22,10 +24,10 @@ from lightcompress_b200 import algo  # noqa: E402
 W4 = {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128}
 
 
-def one_block_llama(dev, seed=0):
+def one_block_llama(dev, seed=0, n_blocks=2):
     from transformers import LlamaConfig, LlamaForCausalLM
     torch.manual_seed(seed)
-    cfg = LlamaConfig(vocab_size=1024, hidden_size=4096, intermediate_size=14336, num_hidden_layers=1,
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=4096, intermediate_size=14336, num_hidden_layers=n_blocks,
                       num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=4096)
     with torch.device(dev):
         m = LlamaForCausalLM(cfg).to(torch.bfloat16).eval()
@@ -40,16 +42,22 @@ def run(method, dev, samples, seq, special, quant_out=False):
     inp = ad.collect_first_block_input(data)
     a = algo.ALGO_REGISTRY[method](ad, {'weight': dict(W4), 'special': special, 'quant_out': quant_out}, inp, None,
                                    {'calib': {'seq_len': seq}})
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
+    times = []
+    opt = a.block_opt
+
+    def timed_block_opt(block):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        opt(block)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+    a.block_opt = timed_block_opt
     a.run_block_loop()
-    torch.cuda.synchronize()
-    t = time.perf_counter() - t0
-    w = model.model.layers[0].mlp.down_proj.weight
+    w = model.model.layers[-1].mlp.down_proj.weight
     assert torch.isfinite(w.float()).all()
     del a, ad, model, data, inp
     torch.cuda.empty_cache()
-    return t
+    return times
 
 
 def main(argv=None, emit=True):
@@ -61,12 +69,14 @@ def main(argv=None, emit=True):
     if 'gptq' in which:
         sp = {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
         run('GPTQ', dev, 4, 2048, sp, True)      # warm-up: attributes, allocator, cuBLAS handles of the module forwards
-        res['gptq_s_per_block'] = run('GPTQ', dev, samples, 2048, sp, True)
+        t = run('GPTQ', dev, samples, 2048, sp, True)
+        res['gptq_s_per_block'], res['gptq_s_first_block'] = t[-1], t[0]
         res['gptq_config'] = f'{samples} x 2048 tokens, w4a16 g128, actorder, true_sequential, quant_out (gptq_w_only.yml)'
     if 'awq' in which:
         sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
         run('Awq', dev, 2, 512, sp)
-        res['awq_s_per_block'] = run('Awq', dev, samples, 512, sp)
+        t = run('Awq', dev, samples, 512, sp)
+        res['awq_s_per_block'], res['awq_s_first_block'] = t[-1], t[0]
         res['awq_config'] = f'{samples} x 512 tokens, w4a16 g128, trans v2 + AutoClip'
     if emit:
         print(json.dumps(res), flush=True)

@@ -48,5 +48,5 @@ else:
     bb.run('Awq', dev, 2, 512, sp)
     acc.clear()
     t = bb.run('Awq', dev, 128, 512, sp)
-print('wall', round(t, 4), {k: round(v, 4) for k, v in acc.items()})
+print('wall per block', [round(v, 4) for v in t], '(phase sums cover BOTH blocks)', {k: round(v, 4) for k, v in acc.items()})
 # nested: block_forward is inside rehook_next_subset / _forward_fake_quant; factor / finalize / w_qdq inside the others
