@@ -33,6 +33,26 @@ def _vllm_cls():
     return VllmRealQuantLinear
 
 
+class _ChildCache(object):
+    """Outputs of a block's DIRECT children (norms, attention, MLP), kept per forward chunk across the passes that
+    `true_sequential` + `quant_out` make over one block (base_bq.py:438-449, 505-526: up to five forwards of the same
+    calibration data through the same block). A child whose parameters did not change since its outputs were recorded,
+    and before which — in execution order — every child was itself reused, sees bit-identical inputs and would recompute
+    bit-identical outputs: its forward is replaced by a lookup for that pass. A child that is recomputed invalidates every
+    child after it. No model knowledge: the children, their order and their outputs are whatever the block executes."""
+
+    def __init__(self, block, data):
+        self.block_id, self.data_id, self.n = id(block), id(data), len(data)
+        self.order = []          # child names in execution order, as discovered
+        self.out = {}            # name -> {chunk index: output}
+        self.sig = {}            # name -> parameter signature the outputs were recorded under
+        self.calls = {}          # name -> forwards seen in the current chunk (a child invoked twice is never reused)
+
+    @staticmethod
+    def signature(mod):
+        return tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in list(mod.parameters()) + list(mod.buffers()))
+
+
 class _StopForward(Exception):
     """Raised by the re-hook pre-hooks once every layer of the next subset has seen its input: the rest of the block
     forward (whose output nobody reads, base_bq.py:505-526) is not computed."""
@@ -76,6 +96,9 @@ class BaseBlockwiseQuantization(object):
         self._capturing = False
         self._on_replay = []
         self._uniform = None
+        self._child_cache = False        # _ChildCache of the block being calibrated (False: none yet)
+        self._hooked_modules = set()     # modules whose input hooks must fire in the running pass
+        self._done_q = {}                # module -> its fake-quantized weight, computed once per block
         if self.input:
             for kw in self.input['kwargs']:   # blockwise_optimization.py:20-25
                 kw.pop('use_cache', None)
@@ -152,21 +175,75 @@ class BaseBlockwiseQuantization(object):
     def _block_forward_batched(self, block, data, may_stop):
         """`forward_batch` samples per block forward: the same per-token arithmetic in fewer, larger GEMMs (the keyword
         tensors — position ids / embeddings, masks — are identical for every sample, so they broadcast over the batch).
-        Outputs are handed back per sample (views), in order."""
+        Outputs are handed back per sample (views), in order. Children of the block whose outputs an earlier pass over
+        the same data already produced under the same parameters are looked up instead of recomputed (_ChildCache)."""
         kw = self.input['kwargs'][0]
         out = []
         B = self.forward_batch
-        for i in range(0, len(data), B):
-            part = data[i:i + B]
-            x = part[0] if len(part) == 1 else torch.cat(part, 0)
-            try:
-                y = block(x, **kw)
-            except _StopForward:
-                if not may_stop:
-                    raise
-                continue
-            y = y[0] if isinstance(y, tuple) else y
-            out.extend(y.split([p.shape[0] for p in part], 0))
+        n_chunks = (len(data) + B - 1) // B
+        cache = self._child_cache if self.special.get('reuse_child_outputs', True) else None
+        if cache is not None and (cache is False or cache.block_id != id(block) or cache.data_id != id(data)
+                                  or cache.n != len(data)):
+            cache = self._child_cache = _ChildCache(block, data)
+        children = dict(block.named_children())
+        handles, stubbed = [], []
+        state = {'chunk': 0}
+        if cache is not None:
+            hooked = self._hooked_modules
+            reuse = []
+            for name in cache.order:
+                child = children.get(name)
+                ok = (child is not None and len(cache.out.get(name, {})) == n_chunks
+                      and cache.sig.get(name) == _ChildCache.signature(child)
+                      and not any(m in hooked for m in child.modules()))
+                if not ok:
+                    break
+                reuse.append(name)
+            for name in list(cache.out):
+                if name not in reuse:
+                    del cache.out[name]        # recomputed (or not reached) in this pass: stale from here on
+            for name in reuse:
+                def lookup(*a, _o=cache.out[name], **k):
+                    return _o[state['chunk']]
+                children[name].forward = lookup
+                stubbed.append(children[name])
+
+            def pre(mod, args, name):
+                if name not in cache.order:
+                    cache.order.append(name)
+                cache.calls[name] = cache.calls.get(name, 0) + 1
+
+            def post(mod, args, output, name):
+                if cache.calls.get(name, 0) == 1:
+                    cache.out.setdefault(name, {})[state['chunk']] = output
+                    cache.sig[name] = _ChildCache.signature(mod)
+                else:
+                    cache.out.pop(name, None)
+            for name, child in children.items():
+                if name in reuse:
+                    continue
+                handles.append(child.register_forward_pre_hook(functools.partial(pre, name=name)))
+                handles.append(child.register_forward_hook(functools.partial(post, name=name)))
+        try:
+            for ci, i in enumerate(range(0, len(data), B)):
+                part = data[i:i + B]
+                x = part[0] if len(part) == 1 else torch.cat(part, 0)
+                state['chunk'] = ci
+                if cache is not None:
+                    cache.calls = {}
+                try:
+                    y = block(x, **kw)
+                except _StopForward:
+                    if not may_stop:
+                        raise
+                    continue
+                y = y[0] if isinstance(y, tuple) else y
+                out.extend(y.split([p.shape[0] for p in part], 0))
+        finally:
+            for h in handles:
+                h.remove()
+            for child in stubbed:
+                child.__dict__.pop('forward', None)
         return out
 
     def _block_forward_graph(self, block, data, may_stop):
@@ -234,6 +311,7 @@ class BaseBlockwiseQuantization(object):
         block = block.to(self.dev)
         named_linears = self.model.get_block_linears(block)
         input_feat = defaultdict(list)
+        self._child_cache, self._done_q = False, {}
         if not self.data_free:
             self.block_init(block)
             if self.quant_out and self.true_sequential:
@@ -252,6 +330,7 @@ class BaseBlockwiseQuantization(object):
             self.block_transform(block, input_feat, self.input['kwargs'])
             if self.quant_out:               # base_bq.py:438-449: the next block sees the fake-quantized block's output
                 self.input['data'] = self._forward_fake_quant(block, named_linears)
+            self._child_cache, self._done_q = False, {}
         else:
             self.block_transform(block, input_feat, None)
 
@@ -262,7 +341,9 @@ class BaseBlockwiseQuantization(object):
         saved = {n: m.weight.data for n, m in linears.items()}
         handles = []
         for n, m in linears.items():
-            m.weight.data = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            if m not in self._done_q:
+                self._done_q[m] = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            m.weight.data = self._done_q[m]
             if not self.w_only:
                 handles.append(m.register_forward_pre_hook(self._act_hook))
         hooks, self.graph_safe_hooks = self.graph_safe_hooks, self.w_only
@@ -299,7 +380,9 @@ class BaseBlockwiseQuantization(object):
         mdt = getattr(self, 'model_dtype', None)
         handles = []
         for n, m in self._done_layers.items():
-            m.weight.data = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            if m not in self._done_q:    # FakeQuantLinear caches tmp_weight on its first forward too (module_utils.py:722-725)
+                self._done_q[m] = self.w_qdq(m, self.wquantizer).to(mdt or m.weight.dtype)
+            m.weight.data = self._done_q[m]
             if not self.w_only:                      # FakeQuantLinear.forward applies a_qdq too (module_utils.py:712-737)
                 handles.append(m.register_forward_pre_hook(self._act_hook))
         hooks, self.graph_safe_hooks = self.graph_safe_hooks, self.graph_safe_hooks and self.w_only
@@ -329,9 +412,11 @@ class BaseBlockwiseQuantization(object):
 
         pending.update(layers)
         handles = [m.register_forward_pre_hook(functools.partial(pre_hook, name=n)) for n, m in layers.items()]
+        self._hooked_modules = set(layers.values())
         try:
             self.block_forward(block, may_stop=True)
         finally:
+            self._hooked_modules = set()
             for h in handles:
                 h.remove()
         return feat

@@ -258,3 +258,23 @@ def test_batched_block_forward_equals_per_sample():
     assert float((res[1][0].float() - res[4][0].float()).abs().max()) <= 2e-2 * float(res[1][0].float().abs().max())
     S1, S4 = res[1][1].triu(), res[4][1].triu()
     assert float((S1 - S4).abs().max() / S1.abs().max()) < 1e-2      # bf16 activations of two GEMM batchings
+
+
+def test_child_output_reuse_changes_nothing():
+    """The shipped GPTQ recipe (act-order, true_sequential, quant_out) makes five passes over a block; norms / attention
+    whose parameters did not change since an earlier pass are looked up instead of recomputed (_ChildCache). Same deployed
+    weights and same block outputs, bit for bit, as with the lookup disabled."""
+    model = _tiny_llama(seed=12)
+    data = _calib(n=8, seed=13)
+    outs = {}
+    for reuse in (True, False):
+        q = copy.deepcopy(model)
+        cfg = {'weight': W4, 'quant_out': True,
+               'special': {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
+                           'true_sequential': True, 'forward_batch': 4, 'reuse_child_outputs': reuse}}
+        a = _run('GPTQ', cfg, q, data)
+        outs[reuse] = (torch.cat([m.weight.data.float().flatten() for blk in a.blocks
+                                  for m in a.model.get_block_linears(blk).values()]),
+                       torch.cat([t.float().flatten() for t in a.input['data']]))
+    assert torch.equal(outs[True][0], outs[False][0])
+    assert torch.equal(outs[True][1], outs[False][1])
