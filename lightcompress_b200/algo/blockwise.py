@@ -34,23 +34,51 @@ def _vllm_cls():
 
 
 class _ChildCache(object):
-    """Outputs of a block's DIRECT children (norms, attention, MLP), kept per forward chunk across the passes that
-    `true_sequential` + `quant_out` make over one block (base_bq.py:438-449, 505-526: up to five forwards of the same
-    calibration data through the same block). A child whose parameters did not change since its outputs were recorded,
-    and before which — in execution order — every child was itself reused, sees bit-identical inputs and would recompute
-    bit-identical outputs: its forward is replaced by a lookup for that pass. A child that is recomputed invalidates every
-    child after it. No model knowledge: the children, their order and their outputs are whatever the block executes."""
+    """Outputs of a block's modules (norms, attention, MLP, and the modules inside them), kept per forward chunk across
+    the passes that `true_sequential` + `quant_out` make over one block (base_bq.py:438-449, 505-526: up to five forwards
+    of the same calibration data through the same block). A module whose parameters did not change since its outputs
+    were recorded, and before which — in execution order, at every enclosing level — every module was itself reused, sees
+    bit-identical inputs and would recompute bit-identical outputs: its forward is replaced by a lookup for that pass.
+    The first module of a level that cannot be reused is entered and the same rule applies to ITS children (its input is
+    still identical); everything after it is recomputed and re-recorded. No model knowledge: the modules, their order
+    and their outputs are whatever the block executes. Outputs are references to tensors the forward produces anyway;
+    keeping them alive costs memory, bounded by `budget` bytes for the modules below the block's direct children."""
 
-    def __init__(self, block, data):
+    def __init__(self, block, data, budget):
         self.block_id, self.data_id, self.n = id(block), id(data), len(data)
-        self.order = []          # child names in execution order, as discovered
+        self.order = {}          # parent name ('' = the block) -> child names (dotted) in execution order, as discovered
         self.out = {}            # name -> {chunk index: output}
         self.sig = {}            # name -> parameter signature the outputs were recorded under
-        self.calls = {}          # name -> forwards seen in the current chunk (a child invoked twice is never reused)
+        self.calls = {}          # name -> forwards seen in the current chunk (a module invoked twice is never reused)
+        self.bytes = {}          # name -> bytes its recorded outputs keep alive
+        self.own = {'': _ChildCache.own_signature(block)}   # name -> own_signature at recording time
+        self.budget = budget
+        self.deep = True
 
     @staticmethod
     def signature(mod):
         return tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in list(mod.parameters()) + list(mod.buffers()))
+
+    @staticmethod
+    def own_signature(mod):
+        """the module's OWN tensors (not its descendants'): what the code BETWEEN its children may read"""
+        return tuple((t.data_ptr(), t._version, tuple(t.shape))
+                     for t in list(mod.parameters(recurse=False)) + list(mod.buffers(recurse=False)))
+
+    @staticmethod
+    def nbytes(o):
+        if torch.is_tensor(o):
+            return o.numel() * o.element_size()
+        if isinstance(o, (tuple, list)):
+            return sum(_ChildCache.nbytes(v) for v in o)
+        return 0
+
+    def drop(self, name):
+        self.out.pop(name, None)
+        self.bytes.pop(name, None)
+
+    def over_budget(self):
+        return sum(v for k, v in self.bytes.items() if '.' in k) > self.budget
 
 
 class _StopForward(Exception):
@@ -184,46 +212,64 @@ class BaseBlockwiseQuantization(object):
         cache = self._child_cache if self.special.get('reuse_child_outputs', True) else None
         if cache is not None and (cache is False or cache.block_id != id(block) or cache.data_id != id(data)
                                   or cache.n != len(data)):
-            cache = self._child_cache = _ChildCache(block, data)
-        children = dict(block.named_children())
+            cache = self._child_cache = _ChildCache(block, data, int(self.special.get('reuse_budget_gb', 64)) << 30)
         handles, stubbed = [], []
         state = {'chunk': 0}
         if cache is not None:
+            modules = dict(block.named_modules())
+            modules.pop('', None)
             hooked = self._hooked_modules
-            reuse = []
-            for name in cache.order:
-                child = children.get(name)
-                ok = (child is not None and len(cache.out.get(name, {})) == n_chunks
-                      and cache.sig.get(name) == _ChildCache.signature(child)
-                      and not any(m in hooked for m in child.modules()))
-                if not ok:
+            reuse = set()
+
+            def plan(parent):
+                """stub the reusable prefix of `parent`'s children; enter the first one that is not reusable"""
+                pmod = block if parent == '' else modules.get(parent)
+                if pmod is None or cache.own.get(parent) != _ChildCache.own_signature(pmod):
+                    return     # the parent's own tensors changed: what flows between its children may have changed too
+                for name in cache.order.get(parent, ()):
+                    mod = modules.get(name)
+                    ok = (mod is not None and len(cache.out.get(name, {})) == n_chunks
+                          and cache.sig.get(name) == _ChildCache.signature(mod)
+                          and not any(m in hooked for m in mod.modules()))
+                    if ok:
+                        reuse.add(name)
+                        continue
+                    if mod is not None and cache.deep:
+                        plan(name)
                     break
-                reuse.append(name)
+            plan('')
+
+            def inside_reused(name):
+                return any(name.startswith(r + '.') for r in reuse)
             for name in list(cache.out):
-                if name not in reuse:
-                    del cache.out[name]        # recomputed (or not reached) in this pass: stale from here on
+                if name not in reuse and not inside_reused(name):
+                    cache.drop(name)           # recomputed (or not reached) in this pass: stale from here on
             for name in reuse:
                 def lookup(*a, _o=cache.out[name], **k):
                     return _o[state['chunk']]
-                children[name].forward = lookup
-                stubbed.append(children[name])
+                modules[name].forward = lookup
+                stubbed.append(modules[name])
 
             def pre(mod, args, name):
-                if name not in cache.order:
-                    cache.order.append(name)
+                parent = name.rpartition('.')[0]
+                lst = cache.order.setdefault(parent, [])
+                if name not in lst:
+                    lst.append(name)
                 cache.calls[name] = cache.calls.get(name, 0) + 1
 
             def post(mod, args, output, name):
-                if cache.calls.get(name, 0) == 1:
+                if cache.calls.get(name, 0) == 1 and (cache.deep or '.' not in name):
                     cache.out.setdefault(name, {})[state['chunk']] = output
                     cache.sig[name] = _ChildCache.signature(mod)
+                    cache.own[name] = _ChildCache.own_signature(mod)
+                    cache.bytes[name] = cache.bytes.get(name, 0) + _ChildCache.nbytes(output)
                 else:
-                    cache.out.pop(name, None)
-            for name, child in children.items():
-                if name in reuse:
+                    cache.drop(name)
+            for name, mod in modules.items():
+                if name in reuse or inside_reused(name) or not (cache.deep or '.' not in name):
                     continue
-                handles.append(child.register_forward_pre_hook(functools.partial(pre, name=name)))
-                handles.append(child.register_forward_hook(functools.partial(post, name=name)))
+                handles.append(mod.register_forward_pre_hook(functools.partial(pre, name=name)))
+                handles.append(mod.register_forward_hook(functools.partial(post, name=name)))
         try:
             for ci, i in enumerate(range(0, len(data), B)):
                 part = data[i:i + B]
@@ -239,6 +285,10 @@ class BaseBlockwiseQuantization(object):
                     continue
                 y = y[0] if isinstance(y, tuple) else y
                 out.extend(y.split([p.shape[0] for p in part], 0))
+                if cache is not None and cache.deep and cache.over_budget():
+                    cache.deep = False         # too much memory kept alive: keep only the block's direct children
+                    for name in [k for k in cache.out if '.' in k]:
+                        cache.drop(name)
         finally:
             for h in handles:
                 h.remove()

@@ -227,7 +227,7 @@ constexpr int ACM_TOK = 32;   // tokens per shared-memory tile (8 KB at 128 colu
 
 // grid (ceil(R / 128), C / gs), 256 threads. NKB = gs / 16 (compile time: 8 for group 128). Same contract as ac_literal_kernel.
 template <typename T, bool ORG, int NKB>
-__global__ void __launch_bounds__(256) ac_mma_kernel(const T* __restrict__ Wq, const T* __restrict__ x, T* __restrict__ org,
+__global__ void __launch_bounds__(256, 4) ac_mma_kernel(const T* __restrict__ Wq, const T* __restrict__ x, T* __restrict__ org,
                                                      const float* __restrict__ omax, const float* __restrict__ omin,
                                                      float* __restrict__ min_err, T* __restrict__ best_max, T* __restrict__ best_min,
                                                      int64_t R, int64_t C, int64_t T_rows, float ratio, float tokens, int clip_sym) {
