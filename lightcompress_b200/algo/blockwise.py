@@ -256,12 +256,12 @@ class BaseBlockwiseQuantization(object):
                 if name not in lst:
                     lst.append(name)
                 cache.calls[name] = cache.calls.get(name, 0) + 1
+                cache.own[name] = _ChildCache.own_signature(mod)    # at ENTRY: a pass may stop inside this module
 
             def post(mod, args, output, name):
                 if cache.calls.get(name, 0) == 1 and (cache.deep or '.' not in name):
                     cache.out.setdefault(name, {})[state['chunk']] = output
                     cache.sig[name] = _ChildCache.signature(mod)
-                    cache.own[name] = _ChildCache.own_signature(mod)
                     cache.bytes[name] = cache.bytes.get(name, 0) + _ChildCache.nbytes(output)
                 else:
                     cache.drop(name)
