@@ -213,6 +213,8 @@ class BaseBlockwiseQuantization(object):
         if cache is not None and (cache is False or cache.block_id != id(block) or cache.data_id != id(data)
                                   or cache.n != len(data)):
             cache = self._child_cache = _ChildCache(block, data, int(self.special.get('reuse_budget_gb', 64)) << 30)
+            cache.deep = self.special.get('reuse_child_outputs', True) != 'direct'
+
         handles, stubbed = [], []
         state = {'chunk': 0}
         if cache is not None:
@@ -285,15 +287,15 @@ class BaseBlockwiseQuantization(object):
                     continue
                 y = y[0] if isinstance(y, tuple) else y
                 out.extend(y.split([p.shape[0] for p in part], 0))
-                if cache is not None and cache.deep and cache.over_budget():
-                    cache.deep = False         # too much memory kept alive: keep only the block's direct children
-                    for name in [k for k in cache.out if '.' in k]:
-                        cache.drop(name)
         finally:
             for h in handles:
                 h.remove()
             for child in stubbed:
                 child.__dict__.pop('forward', None)
+            if cache is not None and cache.deep and cache.over_budget():
+                cache.deep = False             # too much memory kept alive: keep only the block's direct children
+                for name in [k for k in cache.out if '.' in k]:
+                    cache.drop(name)
         return out
 
     def _block_forward_graph(self, block, data, may_stop):

@@ -267,20 +267,17 @@ def test_child_output_reuse_changes_nothing():
     model = _tiny_llama(seed=12)
     data = _calib(n=8, seed=13)
     outs = {}
-    from lightcompress_b200.algo import blockwise as bw
-    looked_up = []
-    orig_plan_holder = {}
-    for reuse in (True, 'direct-only', False):
+    for reuse in (True, 'direct', 'budget0', False):
         q = copy.deepcopy(model)
         cfg = {'weight': W4, 'quant_out': True,
                'special': {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128,
-                           'true_sequential': True, 'forward_batch': 4, 'reuse_child_outputs': bool(reuse),
-                           'reuse_budget_gb': 0 if reuse == 'direct-only' else 64}}
+                           'true_sequential': True, 'forward_batch': 4,
+                           'reuse_child_outputs': True if reuse == 'budget0' else reuse,
+                           'reuse_budget_gb': 0 if reuse == 'budget0' else 64}}
         a = _run('GPTQ', cfg, q, data)
         outs[reuse] = (torch.cat([m.weight.data.float().flatten() for blk in a.blocks
                                   for m in a.model.get_block_linears(blk).values()]),
                        torch.cat([t.float().flatten() for t in a.input['data']]))
-    for mode in (True, 'direct-only'):
+    for mode in (True, 'direct', 'budget0'):     # every level / the block's direct children only / memory budget exceeded
         assert torch.equal(outs[mode][0], outs[False][0]), mode
         assert torch.equal(outs[mode][1], outs[False][1]), mode
-    del bw, looked_up, orig_plan_holder
