@@ -363,6 +363,17 @@ def sharded_extras(torch, dist, dev, world, rank):
                                             'TFLOPs_aggregate': 20 * 2.0 * T * R * C / (ms * 1e-3) / 1e12}
         del x, W, org
         torch.cuda.empty_cache()
+    # AutoClip v1 of one linear, output channels dealt over the ranks, one all_gather of the ranges
+    from lightcompress_b200.algo.autoclip import auto_clip_layer_sharded
+    g = torch.Generator(device=dev).manual_seed(8)
+    xc = torch.randn(512, 4096, device=dev, generator=g).to(torch.bfloat16)
+    Wc = (torch.randn(14336, 4096, device=dev, generator=g) * 0.02).to(torch.bfloat16)
+    auto_clip_layer_sharded(Wc, xc, wq, False, 512)
+    ms, (bmx, bmn) = timed(lambda: auto_clip_layer_sharded(Wc, xc, wq, False, 512))
+    res['autoclip_gate_proj_14336x4096'] = {'ms': ms, 'rows_per_rank': 14336 // world if 14336 % (world * 16) == 0 else 14336,
+                                            'tokens': 512, 'checksum': float(bmx.float().sum())}
+    del xc, Wc, bmx, bmn
+    torch.cuda.empty_cache()
     # configs[4]: the 66 x 3 expert matrices of a DeepSeek-V2-Lite MoE block, FP8 E4M3 per-block real quant, expert e on rank
     # e mod world (rank-local results: a checkpoint writer takes them from the rank that owns the expert)
     from lightcompress_b200.algo import rtn_real_quantize_sharded

@@ -38,21 +38,46 @@ def apply_clip(weight, min_val, max_val, clip_sym):
 
 
 @torch.no_grad()
-def auto_clip_block(named_linears, input_feat, wquantizer, clip_sym, n_sample_token=None, record=None):
-    """AutoClipper.run (auto_clip.py:44-82): every linear except q/k-like ones; ranges averaged over the ranks."""
+def auto_clip_layer_sharded(w, x, wquantizer, clip_sym, n_sample_token=None, search=None):
+    """auto_clip_layer with the OUTPUT CHANNELS dealt over the ranks (every (channel, group) is searched
+    independently, auto_clip.py:108-114 already batches channels): rank r searches rows [r R / world, (r + 1) R / world) on
+    identical data, one all_gather of the two [R / world, n_group, 1] results. Falls back to the full search on every rank
+    when the rows do not split into multiples of 16. `search` is injectable for the CPU tests of the host logic."""
+    import torch.distributed as dist
+    search = search or auto_clip_layer
+    rank, ws = lcdist.world()
+    R = w.shape[0]
+    if ws == 1 or R % (ws * 16):
+        return search(w, x, wquantizer, clip_sym, n_sample_token=n_sample_token)
+    rt = R // ws
+    mx, mn = search(w[rank * rt:(rank + 1) * rt].contiguous(), x, wquantizer, clip_sym, n_sample_token=n_sample_token)
+    both = torch.stack([mx, mn]).contiguous()
+    parts = [torch.empty_like(both) for _ in range(ws)]
+    dist.all_gather(parts, both)
+    return torch.cat([p[0] for p in parts], 0), torch.cat([p[1] for p in parts], 0)
+
+
+@torch.no_grad()
+def auto_clip_block(named_linears, input_feat, wquantizer, clip_sym, n_sample_token=None, record=None, shard_rows=True):
+    """AutoClipper.run (auto_clip.py:44-82): every linear except q/k-like ones. world > 1: the calibration data is the
+    same on every rank (like the AWQ candidate search) and the output channels are sharded (`shard_rows`); with
+    shard_rows=False every rank searches on ITS data and the ranges are averaged, as the reference does (:72-76)."""
     rank, ws = lcdist.world()
     for n, m in named_linears.items():
         if any(s in n for s in _SKIP):
             continue
         feats = input_feat[n]
         x = feats[0] if len(feats) == 1 else torch.cat(feats)
-        max_val, min_val = auto_clip_layer(m.weight.data, x, wquantizer, clip_sym, n_sample_token=n_sample_token)
-        if ws > 1:
-            import torch.distributed as dist
-            dist.all_reduce(max_val, op=dist.ReduceOp.SUM)
-            max_val /= ws
-            dist.all_reduce(min_val, op=dist.ReduceOp.SUM)
-            min_val /= ws
+        if ws > 1 and shard_rows:
+            max_val, min_val = auto_clip_layer_sharded(m.weight.data, x, wquantizer, clip_sym, n_sample_token)
+        else:
+            max_val, min_val = auto_clip_layer(m.weight.data, x, wquantizer, clip_sym, n_sample_token=n_sample_token)
+            if ws > 1:
+                import torch.distributed as dist
+                dist.all_reduce(max_val, op=dist.ReduceOp.SUM)
+                max_val /= ws
+                dist.all_reduce(min_val, op=dist.ReduceOp.SUM)
+                min_val /= ws
         if record is not None:
             record[n] = (max_val, min_val)
         apply_clip(m.weight, min_val, max_val, clip_sym)

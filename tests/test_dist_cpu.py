@@ -64,6 +64,16 @@ def _worker(rank, world, port, q):
     out['sums'] = lcdist.reduce_sum(sums)
     nt3, units3 = lcdist.shard_units(3)     # 3 candidates on 2 ranks: 2 row tiles, 3 units each
     out['units3'] = (nt3, units3)
+    # AutoClip: output channels dealt over the ranks, results gathered (the search itself is injected)
+    from lightcompress_b200.algo.autoclip import auto_clip_layer_sharded
+    w = torch.arange(64 * 8, dtype=torch.float32).reshape(64, 8)
+    seen = []
+
+    def fake_search(w_, x_, q_, sym_, n_sample_token=None):
+        seen.append(tuple(w_.shape))
+        return w_.amax(1).reshape(-1, 1, 1), w_.amin(1).reshape(-1, 1, 1)
+    out['clip'] = auto_clip_layer_sharded(w, None, None, False, search=fake_search)
+    out['clip_rows'] = seen
     # expert sharding: weight i on rank i mod world, results gathered on every rank (fp8 codes travel as bytes)
     from lightcompress_b200.algo import rtn_real_quantize_sharded
     weights = {f'experts.{i}.w': torch.full((4, 8), float(i + 1)) for i in range(5)}
@@ -104,6 +114,9 @@ def test_result_only_collectives_world2():
         assert res[r]['units'] == (1, [(n, 0) for n in range(r, 20, 2)])
         assert torch.equal(res[r]['sums'], torch.tensor([(n + 1) * 10.0 for n in range(20)], dtype=torch.float64))
         assert res[r]['units3'][0] == 2 and len(res[r]['units3'][1]) == 3
+        w = torch.arange(64 * 8, dtype=torch.float32).reshape(64, 8)
+        assert res[r]['clip_rows'] == [(32, 8)]                      # half the rows per rank
+        assert torch.equal(res[r]['clip'][0].reshape(-1), w.amax(1)) and torch.equal(res[r]['clip'][1].reshape(-1), w.amin(1))
         assert res[r]['expert_calls'][:3 - r] == [float(i + 1) for i in range(r, 5, 2)]     # only its own experts
         assert sorted(res[r]['experts']) == [f'experts.{i}.w' for i in range(5)]
         for i in range(5):
