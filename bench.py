@@ -341,7 +341,8 @@ def sharded_extras(torch, dist, dev, world, rank):
                 ops.hessian_accum(S1, xs[i & 1])
             H1 = ops.hessian_finalize(S1, batches)
             rec['max_rel_diff_vs_single_rank'] = float((H - H1).abs().max() / H1.abs().max())
-            assert rec['max_rel_diff_vs_single_rank'] < 1e-6, rec
+            # two fp32 summation orders over 262 144 tokens: the bar the tests hold H to against an fp64 product
+            assert rec['max_rel_diff_vs_single_rank'] < 2e-5, rec
             del S1, H1
         res[f'hessian_C{C}'] = rec
         del H, xs
