@@ -348,7 +348,8 @@ def sharded_extras(torch, dist, dev, world, rank):
         del H, xs
         torch.cuda.empty_cache()
     wq = IntegerQuantizer(4, False, 'per_group', group_size=128)
-    for name, R, C, T in (('llama3_8b_o_proj', 4096, 4096, 8192), ('llama3_70b_o_proj', 8192, 8192, 8192)):
+    # T = 128 samples x 512 tokens, the calibration set of awq_w_only.yml
+    for name, R, C, T in (('llama3_8b_o_proj', 4096, 4096, 65536), ('llama3_70b_o_proj', 8192, 8192, 65536)):
         g = torch.Generator(device=dev).manual_seed(7)      # identical data on every rank
         x = (torch.randn(T, C, device=dev, generator=g) * torch.exp(torch.randn(C, device=dev, generator=g))).to(torch.bfloat16)
         W = (torch.randn(R, C, device=dev, generator=g) * 0.02).to(torch.bfloat16)
@@ -427,6 +428,7 @@ def main():
     ap.add_argument('--impl', default='ours')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-extras', action='store_true')
+    ap.add_argument('--sharded-only', action='store_true', help='of the extras, run only the `sharded` block')
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)
@@ -514,7 +516,7 @@ def main():
     sys.path.insert(0, os.path.join(ROOT, 'tools'))
     import memcpy_ceiling
     sync()
-    ceil_s, ceil_n = memcpy_ceiling.measure(dev, total_mb=(numel * 2) >> 20, chunk_mb=16, reps=3)
+    ceil_s, ceil_n = memcpy_ceiling.measure(dev, total_mb=(numel * 2) >> 20, chunk_mb=16, reps=3, barrier=sync)
     t = torch.tensor([ceil_s], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -541,7 +543,7 @@ def main():
                       'parallelism': f'layers/blocks sharded x{world}, no collective'},
            'clocks': clocks, 'e2e': e2e, 'gpu_launches': args.steps, 'roofline': roofline}
 
-    if rank == 0 and world == 1 and not args.no_extras:   # single-GPU side numbers; at N > 1 every rank leaves together
+    if rank == 0 and world == 1 and not args.no_extras and not args.sharded_only:   # single-GPU side numbers; at N > 1 every rank leaves together
         for _ in range(3):
             step_per_tensor()
         sync()
@@ -575,7 +577,7 @@ def main():
             del ws, hin, hout
         torch.cuda.empty_cache()
         out['sharded'] = sharded_extras(torch, dist, dev, world, rank)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.sharded_only:
         out['cpu_baseline'] = cpu_baseline()[0]
     if rank == 0:
         print(json.dumps(out), flush=True)

@@ -49,12 +49,11 @@ def awq_search_scale(x, weight, wquantizer, version='v2', org_out=None, n_grid=N
     Multi-GPU: the (candidate, row tile) units are dealt round-robin over the ranks on identical data — the squared error
     is a sum over output rows and the fake-quant units lie inside a row, so a row tile is an independent piece of a
     candidate's loss; ONE all-reduce(SUM) of the n_grid partial sums, then every rank takes the same argmin (first
-    minimum: the strict `<` of the sequential search, awq.py:245) and looks its scales up — one host sync in total."""
+    minimum: the strict `<` of the sequential search, awq.py:245) and computes that candidate's scales — one host sync."""
     if org_out is None:
         org_out = torch.nn.functional.linear(x, weight)
     x_mean = get_act_scale(x) if x_mean is None else x_mean
     w_max = get_weight_scale([weight], wquantizer) if version == 'v1' else None
-    cands = torch.stack([get_scales(x_mean, w_max, n / n_grid, version) for n in range(n_grid)])
     R = weight.shape[0]
     T = x.numel() // x.shape[-1]
     n_tiles, units = lcdist.shard_units(n_grid)
@@ -63,19 +62,21 @@ def awq_search_scale(x, weight, wquantizer, version='v2', org_out=None, n_grid=N
     sums = torch.zeros(n_grid, dtype=torch.float64, device=x.device)
     rt = R // n_tiles
     o2 = org_out.reshape(-1, R)
+    mine = sorted({n for n, _ in units})          # only this rank's candidates are materialised
+    cand_of = {n: get_scales(x_mean, w_max, n / n_grid, version) for n in mine}
     for tile in sorted({t for _, t in units}):
         idx = [n for n, t in units if t == tile]
         w_t = weight[tile * rt:(tile + 1) * rt]
         o_t = o2 if n_tiles == 1 else o2[:, tile * rt:(tile + 1) * rt].contiguous()
-        part = ops.awq_candidates(w_t, x, o_t, cands[idx], wquantizer) * float(T * rt)      # mean -> sum over the tile
-        sums.index_add_(0, torch.as_tensor(idx, device=x.device), part)
+        part = ops.awq_candidates(w_t, x, o_t, torch.stack([cand_of[n] for n in idx]), wquantizer) * float(T * rt)
+        sums.index_add_(0, torch.tensor(idx, device=x.device), part)                        # mean -> sum over the tile
     lcdist.reduce_sum(sums)
     losses = sums / float(T * R)
     keyed = torch.where(torch.isfinite(losses), losses, torch.full_like(losses, float('inf')))
     ar = torch.arange(n_grid, device=x.device)
     best_t = torch.where(keyed == keyed.min(), ar, torch.full_like(ar, n_grid)).min().clamp(max=n_grid - 1)   # FIRST minimum
-    best_scales = cands.index_select(0, best_t.reshape(1))[0]
     best = int(best_t.item())
+    best_scales = cand_of[best] if best in cand_of else get_scales(x_mean, w_max, best / n_grid, version)
     if not bool(torch.isfinite(losses[best])):
         raise RuntimeError('awq_search_scale: every candidate loss is NaN / inf')
     return best_scales, best, losses.cpu()

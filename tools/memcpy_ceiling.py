@@ -13,7 +13,10 @@ import sys
 import torch
 
 
-def measure(dev, total_mb=436, chunk_mb=16, reps=5, both=True):
+def measure(dev, total_mb=436, chunk_mb=16, reps=5, both=True, barrier=None):
+    """`barrier` (a callable) runs after the buffers exist and the copies are warm, right before the clock starts: with
+    several ranks the pinned allocations (hundreds of ms, serialised by the OS) would otherwise stagger the ranks and the
+    copies of different GPUs would not contend."""
     n = total_mb << 20
     c = chunk_mb << 20
     hin = torch.empty(n, dtype=torch.uint8).pin_memory()
@@ -31,6 +34,8 @@ def measure(dev, total_mb=436, chunk_mb=16, reps=5, both=True):
                     hout[o:o + c].copy_(dout[o:o + c], non_blocking=True)
     once()
     torch.cuda.synchronize(dev)
+    if barrier is not None:
+        barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     cur = torch.cuda.current_stream(dev)
     e0.record(cur)
@@ -59,9 +64,11 @@ def main():
         dist.init_process_group('nccl', device_id=dev)
     res = {}
     for name, both in (('h2d_only', False), ('h2d_and_d2h', True)):
-        if world > 1:
-            dist.barrier()
-        t, n = measure(dev, mb, chunk, both=both)
+        def bar():
+            if world > 1:
+                dist.barrier()
+                torch.cuda.synchronize(dev)
+        t, n = measure(dev, mb, chunk, both=both, barrier=bar)
         tt = torch.tensor([t], device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
