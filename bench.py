@@ -196,6 +196,9 @@ def extras(torch, dev, tf_peak, tf_burst, hbm_peak):
     res['awq_candidate'] = {'T': T, 'R': C, 'C': C, 'ms': t * 1e3, 'TFLOPs': 2.0 * T * C * C / t / 1e12,
                             'frac_of_bf16_burst_peak': 2.0 * T * C * C / t / 1e12 / tf_burst}
     res.update(hbm_extras(torch, dev, hbm_peak))
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
     import block_bench   # END TO END through ALGO_REGISTRY on one Llama-3-8B-sized decoder block (hooked forwards included)
     bb = block_bench.main(['gptq', 'awq'], emit=False)
     if 'gptq_s_per_block' in bb:   # 2 T sum C^2 = 160.6 TFLOP of Hessian work per block (GEMM convention)

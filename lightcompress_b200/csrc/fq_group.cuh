@@ -149,10 +149,61 @@ __device__ __noinline__ void quant_store_vec_generic(uint4 raw, UnitQ u, SpecD s
   quant_store_vec<T, T, KINDC>(f, u, sp, out, e0);
 }
 
+// FP8 fake-quant of a packed pair of 16-bit values (FloatQuantizer per_group / per_token activations, quant.py:1061-1081):
+// q = rd_T(x / s) (+ 0: the reference's `+ zeros` turns -0 into +0), fp8 RNE with saturation, decode, * s, rd_T.
+// Same operations as fq_elem_fast_fp8, two elements per conversion instruction: cvt.rn.{bf16x2,f16x2}.f32 packs the pair,
+// one packed add applies the +0, cvt.rn.satfinite.e4m3x2 / e5m2x2 encodes both, cvt.rn.f16x2.e4m3x2 decodes both.
+template <typename T>
+__device__ __forceinline__ uint32_t fq2_fp8_fake(uint32_t w, const UnitQ& u, bool e5) {
+  float x0, x1;
+  if (TI<T>::ID == LCB_BF16) {
+    x0 = __uint_as_float(w << 16);
+    x1 = __uint_as_float(w & 0xffff0000u);
+  } else {
+    const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    x0 = t.x;
+    x1 = t.y;
+  }
+  float q0 = __fmul_rn(x0, u.r), q1 = __fmul_rn(x1, u.r);
+  q0 = __fmaf_rn(__fmaf_rn(-u.s, q0, x0), u.r, q0);   // == RN(x / s) (Markstein step on the correctly rounded reciprocal)
+  q1 = __fmaf_rn(__fmaf_rn(-u.s, q1, x1), u.r, q1);
+  uint16_t c;
+  if (TI<T>::ID == LCB_BF16) {
+    __nv_bfloat162 p = __floats2bfloat162_rn(q0, q1);
+    p = __hadd2(p, __floats2bfloat162_rn(0.f, 0.f));
+    const uint32_t pw = *reinterpret_cast<const uint32_t*>(&p);
+    const float r0 = __uint_as_float(pw << 16), r1 = __uint_as_float(pw & 0xffff0000u);
+    if (e5) asm("cvt.rn.satfinite.e5m2x2.f32 %0, %1, %2;" : "=h"(c) : "f"(r1), "f"(r0));
+    else asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(c) : "f"(r1), "f"(r0));
+  } else {
+    __half2 p = __floats2half2_rn(q0, q1);
+    p = __hadd2(p, __floats2half2_rn(0.f, 0.f));
+    const uint32_t pw = *reinterpret_cast<const uint32_t*>(&p);
+    if (e5) asm("cvt.rn.satfinite.e5m2x2.f16x2 %0, %1;" : "=h"(c) : "r"(pw));
+    else asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(c) : "r"(pw));
+  }
+  uint32_t h;
+  if (e5) asm("cvt.rn.f16x2.e5m2x2 %0, %1;" : "=r"(h) : "h"(c));
+  else asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h) : "h"(c));
+  const float2 v = __half22float2(*reinterpret_cast<const __half2*>(&h));
+  const float o0 = __fmul_rn(v.x, u.s_out), o1 = __fmul_rn(v.y, u.s_out);
+  if (TI<T>::ID == LCB_BF16) {
+    const __nv_bfloat162 o = __floats2bfloat162_rn(o0, o1);
+    return *reinterpret_cast<const uint32_t*>(&o);
+  }
+  const __half2 o = __floats2half2_rn(o0, o1);
+  return *reinterpret_cast<const uint32_t*>(&o);
+}
+
 // fp32 fast chain, LCB_OUT_FAKE only, inline (fp32 tensors; fp8 fake-quant)
 template <typename T, int KINDC>
 __device__ __forceinline__ uint4 quant_vec_fast_f32(const uint4& raw, const UnitQ& u, int kind) {
   constexpr int VEC = TI<T>::VEC;
+  if (KINDC == 1 && sizeof(T) == 2) {
+    const bool e5 = kind == LCB_KIND_FP8_E5M2;
+    return make_uint4(fq2_fp8_fake<T>(raw.x, u, e5), fq2_fp8_fake<T>(raw.y, u, e5), fq2_fp8_fake<T>(raw.z, u, e5),
+                      fq2_fp8_fake<T>(raw.w, u, e5));
+  }
   float f[VEC], val[VEC], code;
   TI<T>::unpack(raw, f);
 #pragma unroll

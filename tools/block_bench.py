@@ -21,6 +21,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from lightcompress_b200 import algo  # noqa: E402
 
+MEM = {}
 W4 = {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128}
 
 
@@ -52,7 +53,12 @@ def run(method, dev, samples, seq, special, quant_out=False):
         torch.cuda.synchronize()
         times.append(time.perf_counter() - t0)
     a.block_opt = timed_block_opt
+    torch.cuda.reset_peak_memory_stats()
     a.run_block_loop()
+    st = torch.cuda.memory_stats()
+    MEM[method] = {'peak_allocated_GB': round(torch.cuda.max_memory_allocated() / 2**30, 1),
+                   'reserved_GB': round(torch.cuda.memory_reserved() / 2**30, 1),
+                   'cudaMalloc_calls': int(st.get('num_device_alloc', 0)), 'alloc_retries': int(st.get('num_alloc_retries', 0))}
     w = model.model.layers[-1].mlp.down_proj.weight
     assert torch.isfinite(w.float()).all()
     del a, ad, model, data, inp
@@ -71,12 +77,14 @@ def main(argv=None, emit=True):
         run('GPTQ', dev, 4, 2048, sp, True)      # warm-up: attributes, allocator, cuBLAS handles of the module forwards
         t = run('GPTQ', dev, samples, 2048, sp, True)
         res['gptq_s_per_block'], res['gptq_s_first_block'] = t[-1], t[0]
+        res['gptq_memory'] = MEM.get('GPTQ')
         res['gptq_config'] = f'{samples} x 2048 tokens, w4a16 g128, actorder, true_sequential, quant_out (gptq_w_only.yml)'
     if 'awq' in which:
         sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
         run('Awq', dev, 2, 512, sp)
         t = run('Awq', dev, samples, 512, sp)
         res['awq_s_per_block'], res['awq_s_first_block'] = t[-1], t[0]
+        res['awq_memory'] = MEM.get('Awq')
         res['awq_config'] = f'{samples} x 512 tokens, w4a16 g128, trans v2 + AutoClip'
     if emit:
         print(json.dumps(res), flush=True)
