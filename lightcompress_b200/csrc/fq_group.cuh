@@ -350,7 +350,7 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 template <typename T, int NV, int KINDC, int CHAIN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
     fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
                     void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
   constexpr int U = NV >= 8 ? 1 : 8 / NV;
