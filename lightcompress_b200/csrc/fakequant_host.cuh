@@ -136,11 +136,18 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
     const int grid = grid_for((n_units + (8 / w) - 1) / (8 / w), 8);
 #define LCB_LAUNCH_WROW_C(CH, Wc) \
   launch_pdl(fq_wrow_kernel<T, KINDC, CH, Wc>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, sp, fs)
-#define LCB_LAUNCH_WROW(CH)                      \
-  {                                              \
-    if (w == 2) LCB_LAUNCH_WROW_C(CH, 2);        \
-    else if (w == 4) LCB_LAUNCH_WROW_C(CH, 4);   \
-    else LCB_LAUNCH_WROW_C(CH, 8);               \
+  // 8 warps per row: 6 or 7 vectors per lane when that covers the row (14336 16-bit elements = 7 x 256 vectors: no idle
+  // load slots; 8 per lane would leave 12.5 % of them empty)
+  const int nv8 = (int)((nvec + 255) / 256);
+#define LCB_LAUNCH_WROW(CH)                                                                                                     \
+  {                                                                                                                             \
+    if (w == 2) LCB_LAUNCH_WROW_C(CH, 2);                                                                                       \
+    else if (w == 4) LCB_LAUNCH_WROW_C(CH, 4);                                                                                  \
+    else if (nv8 == 7)                                                                                                          \
+      launch_pdl(fq_wrow_kernel<T, KINDC, CH, 8, 7>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, sp, fs);   \
+    else if (nv8 == 6)                                                                                                          \
+      launch_pdl(fq_wrow_kernel<T, KINDC, CH, 8, 6>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, sp, fs);   \
+    else LCB_LAUNCH_WROW_C(CH, 8);                                                                                              \
   }
     if (chain == CHAIN_F32) LCB_LAUNCH_WROW(CHAIN_F32)
     else if (TI<T>::ID == LCB_BF16 && KINDC == 0 && chain == CHAIN_BF16_SMALL) {

@@ -392,12 +392,11 @@ __global__ void __launch_bounds__(256)
 // Rows longer than one warp's registers (2048 < elements <= 16384 for 16-bit types): W warps share a row, NV = 8 vectors
 // per lane, cross-warp range through shared memory and ONE named barrier per row (slots double-buffered by iteration).
 // CTA = 8 warps = 8 / W rows at a time. Same element chains as the sub-warp kernel.
-template <typename T, int KINDC, int CHAIN, int W>
+template <typename T, int KINDC, int CHAIN, int W, int NV = 8>
 __global__ void __launch_bounds__(256)
     fq_wrow_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, void* __restrict__ zeros,
                    int64_t n_units, int unit_len, SpecD sp, FastSpec fs) {
   constexpr int VEC = TI<T>::VEC;
-  constexpr int NV = 8;
   constexpr int RPC = 8 / W;  // rows per CTA per iteration
   using R = Range<T>;
   __shared__ typename R::P slot[2][RPC][W];
