@@ -133,7 +133,7 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
     const FastSpec fs = make_fastspec<T>(sp);
     int chain = CHAIN_ANY_OUT;
     if (sp.out_mode == LCB_OUT_FAKE) chain = (KINDC == 0) ? fs.chain : CHAIN_F32;
-    const int grid = grid_for((n_units + (8 / w) - 1) / (8 / w), 8);
+    const int grid = grid_for((n_units + (8 / w) - 1) / (8 / w), w == 8 ? 9 : 8);   // whole waves: 3 (W = 8) / 2 CTAs per SM
 #define LCB_LAUNCH_WROW_C(CH, Wc) \
   launch_pdl(fq_wrow_kernel<T, KINDC, CH, Wc>, grid, 256, st, in, out, scales, zeros, n_units, (int)unit_len, sp, fs)
   // 8 warps per row: 6 or 7 vectors per lane when that covers the row (14336 16-bit elements = 7 x 256 vectors: no idle

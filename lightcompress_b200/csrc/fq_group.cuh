@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(256)
 // per lane, cross-warp range through shared memory and ONE named barrier per row (slots double-buffered by iteration).
 // CTA = 8 warps = 8 / W rows at a time. Same element chains as the sub-warp kernel.
 template <typename T, int KINDC, int CHAIN, int W, int NV = 8>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
     fq_wrow_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, void* __restrict__ zeros,
                    int64_t n_units, int unit_len, SpecD sp, FastSpec fs) {
   constexpr int VEC = TI<T>::VEC;
