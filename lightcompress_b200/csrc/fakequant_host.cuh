@@ -98,9 +98,9 @@ static int launch_dynamic_1d(const T* in, void* out, void* scales, void* zeros, 
     const int u = nvt >= 8 ? 1 : 8 / nvt;
     const FastSpec fs = make_fastspec<T>(sp);
     const int64_t units_per_cta = (int64_t)8 * u * (32 / lanes);
-    // grid = 2 x the resident CTAs (80 registers x 256 threads: 3 CTAs / SM): a grid-stride loop over whole waves has no
-    // partial last wave (148 x 16 CTAs = 5.33 waves cost 2.4 % on the Llama-3-8B block; sweep in profiles/README.md)
-    static const int group_cps = [] { const char* e = getenv("LCB_GROUP_CTAS_PER_SM"); return e ? atoi(e) : 6; }();
+    // grid = 2 x the resident CTAs (launch bound: 64 registers x 256 threads = 4 CTAs / SM): a grid-stride loop over whole
+    // waves has no partial last wave (148 x 16 CTAs on 3 resident = 5.33 waves cost 2.4 % on the Llama-3-8B block)
+    static const int group_cps = [] { const char* e = getenv("LCB_GROUP_CTAS_PER_SM"); return e ? atoi(e) : 8; }();
     const int grid = grid_for((n_units + units_per_cta - 1) / units_per_cta, group_cps);
     // chain compiled into the kernel: the packed 16-bit chains and the inline fp32 chain serve LCB_OUT_FAKE only
     int chain = CHAIN_ANY_OUT;
@@ -374,7 +374,7 @@ static int fakequant_multi_typed(const void* const* ins, void* const* outs, cons
   const int64_t chunks = md.chunk_start[n];
   if (chunks == 0) return LCB_OK;
   const FastSpec fs = make_fastspec<T>(sp);
-  static const int multi_cps = [] { const char* e = getenv("LCB_GROUP_CTAS_PER_SM"); return e ? atoi(e) : 6; }();
+  static const int multi_cps = [] { const char* e = getenv("LCB_GROUP_CTAS_PER_SM"); return e ? atoi(e) : 8; }();
   const int grid = grid_for((chunks + 7) / 8, multi_cps);
 #define LCB_LAUNCH_MULTI(NVc, CH) \
   launch_pdl(fq_group_multi_kernel<T, NVc, 0, CH>, grid, 256, st, md, (int)uc, lanes, sp, fs)

@@ -350,7 +350,7 @@ __device__ __forceinline__ void pdl_enter() {
 }
 
 template <typename T, int NV, int KINDC, int CHAIN>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 4)
     fq_group_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales,
                     void* __restrict__ zeros, int64_t n_units, int unit_len, int lanes, SpecD sp, FastSpec fs) {
   constexpr int U = NV >= 8 ? 1 : 8 / NV;
@@ -375,7 +375,7 @@ struct MultiDesc {
 };
 
 template <typename T, int NV, int KINDC, int CHAIN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
     fq_group_multi_kernel(const __grid_constant__ MultiDesc md, int unit_len, int lanes, SpecD sp, FastSpec fs) {
   pdl_enter();
   const int64_t warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -393,7 +393,8 @@ __global__ void __launch_bounds__(256)
 // per lane, cross-warp range through shared memory and ONE named barrier per row (slots double-buffered by iteration).
 // CTA = 8 warps = 8 / W rows at a time. Same element chains as the sub-warp kernel.
 template <typename T, int KINDC, int CHAIN, int W, int NV = 8>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, W == 8 ? 3 : 2)   // 8 warps per row = one row per CTA: a third CTA per SM is a third
+                                                         // row in flight (+18 %); 2 / 4 warps per row lose 3 % to spills at 3
     fq_wrow_kernel(const T* __restrict__ in, void* __restrict__ out, void* __restrict__ scales, void* __restrict__ zeros,
                    int64_t n_units, int unit_len, SpecD sp, FastSpec fs) {
   constexpr int VEC = TI<T>::VEC;
