@@ -311,14 +311,34 @@ int64_t lcb_awq_workspace_bytes(int64_t T, int64_t R, int64_t C, int32_t n_cand)
  * W [R, C], x [T_rows, C] (the sampled tokens, auto_clip.py:131-133) row-major in spec->dtype (bf16 / f16); rows
  * tokens .. T_rows-1 of x must be zero (padding to a multiple of 8); `tokens` is the divisor of the mean.
  * best_max / best_min: [R, C / group] in the tensor dtype (group_size <= 0: one group per row). spec: the weight
- * quantizer (dynamic, LCB_OUT_FAKE, math_dtype == dtype). The per-step output is never materialised: the grouped
- * tcgen05 product reduces the squared error over tokens in its epilogue.
+ * quantizer (dynamic, LCB_OUT_FAKE, math_dtype == dtype). The per-step output is never materialised: products rounded to
+ * the tensor dtype as the reference rounds them (HMUL2), summed in fp32 on the tensor pipe (mma.sync with a ones operand),
+ * the squared error reduced over tokens in registers.
  * workspace: lcb_autoclip_workspace_bytes(R, C, T_rows, group_size).
  */
 int lcb_autoclip_search(const void* W, const void* x, void* best_max, void* best_min, int64_t R, int64_t C, int64_t T_rows,
                         int64_t tokens, int32_t group_size, int32_t n_grid, int32_t n_steps, int32_t clip_sym,
                         const lcb_quant_spec* spec, void* workspace, void* stream);
 int64_t lcb_autoclip_workspace_bytes(int64_t R, int64_t C, int64_t T_rows, int64_t group_size);
+
+/*
+ * The same search taken apart, for the cases where the per-step weights are not "clamp then dynamic fake-quant":
+ * clip_version 'v2' (auto_clip.py:258-274: logit / sigmoid bounds -> get_qparams -> fake_quant_weight_static) and w+a
+ * configs (auto_clip.py:164, 276-281: the candidate outputs use the fake-quantized inputs, org_out the plain ones).
+ * The host owns the buffers and the loop; the per-step weights come from lcb_fakequant (static qparams).
+ *   lcb_autoclip_init: org_max / org_min fp32 [R, C / group] (clip_sym: org_max = |w|.amax), best_max / best_min (tensor
+ *       dtype) = org, min_err fp32 = 1e9 rounded to the tensor dtype (auto_clip.py:116-125).
+ *   lcb_autoclip_step: is_org != 0: org[g, r, t] = (x * W).sum(-1) (tensor dtype, [C / group, R, T_rows]; the bounds and
+ *       best_* pointers may be NULL). is_org == 0: W = this step's fake-quantized weights, x = the (fake-quantized) inputs:
+ *       err = mean_t ((x * W).sum(-1) - org)^2 with the reference's roundings; where err < min_err: min_err = err,
+ *       best_max = org_max * ratio, best_min = clip_sym ? -best_max : org_min * ratio (auto_clip.py:154-179).
+ * Shapes / padding rules as lcb_autoclip_search.
+ */
+int lcb_autoclip_init(const void* W, void* best_max, void* best_min, float* org_max, float* org_min, float* min_err,
+                      int64_t R, int64_t C, int32_t group_size, int32_t clip_sym, int32_t dtype, void* stream);
+int lcb_autoclip_step(const void* Wq, const void* x, void* org, const float* org_max, const float* org_min, float* min_err,
+                      void* best_max, void* best_min, int64_t R, int64_t C, int64_t T_rows, int64_t tokens,
+                      int32_t group_size, float ratio, int32_t clip_sym, int32_t is_org, int32_t dtype, void* stream);
 
 /*
  * Real-quant export packers (the reference packs with numpy on the host / a Python loop per column).

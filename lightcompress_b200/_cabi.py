@@ -63,6 +63,9 @@ SIGNATURES = {
     'lcb_autoclip_search': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32,
                                            _c_i32, _c_i32, ctypes.POINTER(QuantSpec), _c_vp, _c_vp]),
     'lcb_autoclip_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i64, _c_i64]),
+    'lcb_autoclip_init': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp]),
+    'lcb_autoclip_step': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i64,
+                                         _c_i32, _c_f, _c_i32, _c_i32, _c_i32, _c_vp]),
     'lcb_pack_rows': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_awq_gemm_pack': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_col_absstat': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),

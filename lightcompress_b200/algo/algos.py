@@ -128,7 +128,13 @@ class Awq(BaseBlockwiseQuantization):
         self.trans_version = sp.get('trans_version', 'v2')
         self.weight_clip = sp.get('weight_clip', False)
         self.clip_sym = sp.get('clip_sym', self.wquantizer.sym)
+        self.clip_version = sp.get('clip_version', 'v1')
+        if self.weight_clip and self.clip_version == 'v2':     # base_blockwise_quantization.py:228-230
+            assert self.wquantizer.calib_algo == 'learnable', "clip_version v2 needs weight calib_algo: learnable"
+        self.save_clip = sp.get('save_clip', False)
+        self.weight_clips = {}  # block -> {'<layer>.weight_quantizer.upbound_factor' | 'lowbound_factor': cpu tensor | None}
         self.true_sequential = False
+        self.awq_bs = sp.get('awq_bs', None)
         self.best_index = {}   # (block, first layer name) -> selected candidate, for parity reports
         self.act_scales = {}   # '<prefix>.<block>.<layer>' -> applied scale (awq.py:365-368, kept whether or not save_scale)
         self.clips = {}        # (block, layer name) -> (best_max_val, best_min_val) of AutoClip
@@ -139,12 +145,19 @@ class Awq(BaseBlockwiseQuantization):
             super().block_transform(block, input_feat, block_kwargs)
         if self.weight_clip:
             from .autoclip import auto_clip_block
-            rec = {}
+            rec, factors = {}, {}
             auto_clip_block(self.model.get_block_linears(block), input_feat, self.wquantizer, self.clip_sym,
                             n_sample_token=(self.config or {}).get('calib', {}).get('seq_len', None)
-                            if isinstance(self.config, dict) else None, record=rec)
+                            if isinstance(self.config, dict) else None, record=rec, clip_version=self.clip_version,
+                            aquantizer=None if self.w_only else self.aquantizer, padding_mask=self.padding_mask,
+                            factors=factors)
             for n, v in rec.items():
                 self.clips[(self.block_idx, n)] = v
+            if self.save_clip:                                    # auto_clip.py:219-229
+                for n, (up, low) in factors.items():
+                    d = self.weight_clips.setdefault(self.block_idx, {})
+                    d[f'{n}.weight_quantizer.upbound_factor'] = up.cpu()
+                    d[f'{n}.weight_quantizer.lowbound_factor'] = None if low is None else low.cpu()
 
     @torch.no_grad()
     def subset_transform(self, subset, input_feat, subset_kwargs):   # awq.py:300-372
@@ -159,15 +172,23 @@ class Awq(BaseBlockwiseQuantization):
                                                                layers[0].in_features * 3):
             return   # GQA v -> o: "Cannot apply scale" unless do_gqa_trans (not covered)
         xs = input_feat[subset['input'][0]]
-        x = xs[0] if len(xs) == 1 else torch.cat(xs, 0)
         inspect = subset['inspect']
-        kwargs = subset_kwargs[0] if isinstance(subset_kwargs, list) and subset_kwargs else (subset_kwargs or {})
-        if isinstance(inspect, nn.Linear) and len(layers) == 1 and inspect is layers[0] and inspect.bias is None \
-                and self.w_only and x.dtype in (torch.bfloat16, torch.float16):
-            scale, best, _ = lcawq.awq_search_scale(x, inspect.weight.data, self.wquantizer, self.trans_version)
+        own = self.special.get('own_gemm', True)
+        if len(xs) != 1 or self.padding_mask or self.awq_bs is not None:
+            # several batches / awq_bs chunks / padding masks: the reference loop as written (awq.py:179-278)
+            scale, best = lcawq.awq_search_scale_general(xs, layers, inspect, self.wquantizer, subset_kwargs, self.trans_version,
+                                                         aquantizer=None if self.w_only else self.aquantizer,
+                                                         padding_mask=self.padding_mask, awq_bs=self.awq_bs,
+                                                         n_samples=self.n_samples, own_gemm=own)
         else:
-            scale, best, _ = lcawq.awq_search_scale_module(x, layers, inspect, self.wquantizer, kwargs,
-                                                           self.trans_version, own_gemm=self.special.get('own_gemm', True))
+            x = xs[0]
+            kwargs = subset_kwargs[0] if isinstance(subset_kwargs, list) and subset_kwargs else (subset_kwargs or {})
+            if isinstance(inspect, nn.Linear) and len(layers) == 1 and inspect is layers[0] and inspect.bias is None \
+                    and self.w_only and x.dtype in (torch.bfloat16, torch.float16):
+                scale, best, _ = lcawq.awq_search_scale(x, inspect.weight.data, self.wquantizer, self.trans_version)
+            else:
+                scale, best, _ = lcawq.awq_search_scale_module(x, layers, inspect, self.wquantizer, kwargs, self.trans_version,
+                                                               own_gemm=own, aquantizer=None if self.w_only else self.aquantizer)
         self.best_index[(self.block_idx, next(iter(layers_dict)))] = best
         prefix = getattr(self.model, 'block_name_prefix', 'model.layers')
         for n in layers_dict:

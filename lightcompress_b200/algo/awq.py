@@ -112,12 +112,14 @@ class own_linears(object):
 
 
 @torch.no_grad()
-def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, version='v2', n_grid=N_GRID, own_gemm=True):
+def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, version='v2', n_grid=N_GRID, own_gemm=True,
+                            aquantizer=None):
     """awq.py:179-278 for any inspect module (one batch). `layers`: the nn.Linear modules that share the input x.
-    Weights are restored from an on-device copy (the reference reloads a CPU state dict every candidate)."""
+    Weights are restored from an on-device copy (the reference reloads a CPU state dict every candidate).
+    `aquantizer` (w+a configs): the scaled input is fake-quantized before the forward (awq.py:166-177, 228-229)."""
     if own_gemm:
         with own_linears(inspect_module):
-            return awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs, version, n_grid, own_gemm=False)
+            return awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs, version, n_grid, False, aquantizer)
     kwargs = kwargs or {}
 
     def fwd(inp):
@@ -134,10 +136,99 @@ def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, 
         scales = get_scales(x_mean, w_max, n / n_grid, version)
         for m, w0 in zip(layers, saved):
             m.weight.data = wquantizer.fake_quant_weight_dynamic(ops.scale_cols(w0, scales))
-        out = fwd(ops.scale_cols(x, scales, div=True))
+        x_tmp = ops.scale_cols(x, scales, div=True)
+        if aquantizer is not None:
+            x_tmp = aquantizer.fake_quant_act_dynamic(x_tmp)
+        out = fwd(x_tmp)
         losses.append((org_out - out).float().pow(2).mean())   # stays on the device: one sync after the loop
         for m, w0 in zip(layers, saved):
             m.weight.data = w0
     losses = torch.stack(losses).tolist() if losses else []
     _, best = lcdist.argmin_across_ranks(losses, mine, x.device)
     return get_scales(x_mean, w_max, best / n_grid, version), best, losses
+
+
+@torch.no_grad()
+def awq_search_scale_general(inputs, layers, inspect_module, wquantizer, subset_kwargs, version='v2', aquantizer=None,
+                             padding_mask=None, awq_bs=None, n_samples=None, n_grid=N_GRID, own_gemm=True):
+    """Awq.search_scale_subset (awq.py:179-278) LITERALLY, for everything the single-batch paths above do not cover:
+    several input batches (the running `loss_mean` is compared inside the batch loop, and `best_scales` is the running
+    `scales_mean` at that moment: awq.py:240-248, reproduced as written), `awq_bs` chunking of a batch (:74-85, 110-145,
+    166-177), padding masks (:233-235), w+a. Every rank searches on ITS data; the rank with the smallest error broadcasts
+    its scales (:255-273). Compute: lcb_scale_cols, the fused fake-quant kernels, lcb_linear for the module's projections.
+    Returns (best_scales, best_index)."""
+    import torch.distributed as dist
+    if own_gemm:
+        with own_linears(inspect_module):
+            return awq_search_scale_general(inputs, layers, inspect_module, wquantizer, subset_kwargs, version, aquantizer,
+                                            padding_mask, awq_bs, n_samples, n_grid, own_gemm=False)
+    bs = inputs[0].shape[0] if awq_bs is None else awq_bs
+
+    def chunks(t):
+        return [t[k * bs:(k + 1) * bs] for k in range(t.shape[0] // bs)]
+
+    def act_scale(x):                                   # get_act_scale (:74-85)
+        if x.shape[0] == bs:
+            return get_act_scale(x)
+        means = [get_act_scale(c) for c in chunks(x)]
+        return sum(means) / len(means)
+
+    def forward(x, kw):                                 # inspect_module_forward (:110-126)
+        outs = []
+        for c in ([x] if x.shape[0] == bs else chunks(x)):
+            o = inspect_module(c, **kw)
+            outs.append(o[0] if isinstance(o, tuple) else o)
+        return outs[0] if len(outs) == 1 else torch.cat(outs, dim=0)
+
+    def loss_of(org, out):                              # calculate_loss (:134-145)
+        if out.shape[0] == bs:
+            return (org - out).float().pow(2).mean().item()
+        parts = [(a - b).float().pow(2).mean().item() for a, b in zip(chunks(org), chunks(out))]
+        return sum(parts) / len(parts)
+
+    w_max = get_weight_scale([m.weight.data for m in layers], wquantizer) if version == 'v1' else None
+    saved = [m.weight.data.clone() for m in layers]
+    best_error, best_scales, best_n = float('inf'), None, -1
+    org_cache = {}
+    for n in range(n_grid):
+        loss_mean, scales_mean = 0, 0
+        for i, x in enumerate(inputs):
+            kw = subset_kwargs[i] if isinstance(subset_kwargs, list) else (subset_kwargs or {})
+            if i not in org_cache:
+                org_cache[i] = forward(x, kw)
+            org_out = org_cache[i]
+            scales = get_scales(act_scale(x), w_max, n / n_grid, version)
+            for m, w0 in zip(layers, saved):
+                m.weight.data = wquantizer.fake_quant_weight_dynamic(ops.scale_cols(w0, scales))
+            x_tmp = ops.scale_cols(x, scales, div=True)
+            if aquantizer is not None:                   # fake_quantize_input (:166-177)
+                if bs == x_tmp.shape[0]:
+                    x_tmp = aquantizer.fake_quant_act_dynamic(x_tmp)
+                else:
+                    x_tmp = torch.stack([aquantizer.fake_quant_act_dynamic(x_tmp[k]) for k in range(x_tmp.shape[0])])
+            out = forward(x_tmp, kw)
+            if padding_mask and org_out.shape[1] == padding_mask[i].shape[-1]:
+                mask = padding_mask[i].unsqueeze(dim=-1).to(org_out.device)
+                org_out, out = org_out * mask, out * mask
+            loss = loss_of(org_out, out)
+            ns = x.shape[0] if len(inputs) == 1 else n_samples
+            loss_mean += x.shape[0] * 1.0 / ns * loss
+            scales_mean += x.shape[0] * 1.0 / ns * scales
+            for m, w0 in zip(layers, saved):
+                m.weight.data = w0
+            if loss_mean < best_error:
+                best_error, best_scales, best_n = loss_mean, scales_mean, n
+    rank, ws = lcdist.world()
+    if ws > 1:                                           # awq.py:255-273
+        dev = inputs[0].device
+        err = torch.tensor([best_error], device=dev)
+        dist.all_reduce(err, op=dist.ReduceOp.MIN)
+        who = torch.tensor([rank if abs(best_error - err.item()) < 1e-5 else -1], device=dev)
+        dist.all_reduce(who, op=dist.ReduceOp.MAX)
+        src = int(who.item())
+        if rank != src:
+            best_scales = torch.zeros_like(best_scales)
+        dist.broadcast(best_scales, src=src)
+    if best_scales is None:
+        raise RuntimeError('awq_search_scale_general: every candidate loss is NaN / inf')
+    return best_scales, best_n

@@ -174,15 +174,24 @@ def _autoclip_layer(orig):
     def auto_clip_layer(self, block_idx, layer_name, w, inputs, n_grid=20, max_shrink=0.5, n_sample_token=512, eps=0.0):
         wq = as_lcb_quantizer(self.wquantizer)
         gs = wq.group_size if wq.granularity == 'per_group' else w.shape[1]
-        ok = (self.clip_version == 'v1' and self.w_only and len(inputs) == 1 and not self.padding_mask and w.dim() == 2
+        v1 = self.clip_version == 'v1'
+        ok = ((v1 or (self.clip_version == 'v2' and wq.granularity == 'per_channel' and (self.w_only or eps == 0.0)))
+              and len(inputs) == 1 and not self.padding_mask and w.dim() == 2
               and type(wq).__name__ == 'IntegerQuantizer' and wq.granularity in ('per_group', 'per_channel')
               and w.dtype in (torch.bfloat16, torch.float16) and inputs[0].dtype == w.dtype
               and w.shape[1] % gs == 0 and gs % 8 == 0 and (gs <= 128 or gs % 128 == 0) and w.shape[0] % 64 == 0)
+        aq = None
+        if ok and not self.w_only:
+            aq = as_lcb_quantizer(self.aquantizer)
+            ok = type(aq).__name__ == 'IntegerQuantizer' and aq.granularity == 'per_token'
         if not ok:
             return orig(self, block_idx, layer_name, w, inputs, n_grid, max_shrink, n_sample_token, eps)
-        from .autoclip import auto_clip_layer as lcb_layer
+        from . import autoclip as lcac
         x = inputs[0].to(w.device)
-        return lcb_layer(w.data if hasattr(w, 'data') else w, x, wq, self.clip_sym, n_grid, max_shrink, n_sample_token)
+        wd = w.data if hasattr(w, 'data') else w
+        if v1 and aq is None:
+            return lcac.auto_clip_layer(wd, x, wq, self.clip_sym, n_grid, max_shrink, n_sample_token)
+        return lcac.auto_clip_layer_general(wd, x, wq, self.clip_sym, self.clip_version, aq, n_grid, max_shrink, n_sample_token)
     return auto_clip_layer
 
 

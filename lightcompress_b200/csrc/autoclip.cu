@@ -435,3 +435,55 @@ extern "C" int lcb_autoclip_search(const void* W, const void* x, void* best_max,
     return autoclip_typed<__nv_bfloat16>(W, x, best_max, best_min, R, C, T_rows, tokens, gs, n_grid, n_steps, clip_sym, spec, ws, st);
   return autoclip_typed<__half>(W, x, best_max, best_min, R, C, T_rows, tokens, gs, n_grid, n_steps, clip_sym, spec, ws, st);
 }
+
+// ---- the search taken apart (clip_version 'v2' and w+a configs: the host composes the per-step weights itself) ---------------
+// lcb_autoclip_init : org_max / org_min per (row, group) in fp32, best_* = org_*, min_err = 1e9 (auto_clip.py:116-125)
+// lcb_autoclip_step : is_org != 0: org[g, r, t] = (x * w).sum(-1) (auto_clip.py:151); else the candidate pass: err of
+//                     (xq * Wq).sum(-1) against org, best_* / min_err updated where err < min_err (auto_clip.py:154-179).
+extern "C" int lcb_autoclip_init(const void* W, void* best_max, void* best_min, float* org_max, float* org_min, float* min_err,
+                                 int64_t R, int64_t C, int32_t group_size, int32_t clip_sym, int32_t dtype, void* stream) {
+  using namespace lcb;
+  if (!W || !best_max || !best_min || !org_max || !org_min || !min_err) return LCB_E_INVALID;
+  if (R < 1 || C < 1) return LCB_E_INVALID;
+  if (dtype != LCB_BF16 && dtype != LCB_F16) return LCB_E_UNSUPPORTED;
+  const int64_t gs = group_size > 0 ? group_size : C;
+  if (C % gs) return LCB_E_SHAPE;
+  const int64_t nu = R * (C / gs);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int grid = (int)((nu * 32 + 255) / 256);
+  if (dtype == LCB_BF16)
+    ac_init_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)W, (__nv_bfloat16*)best_max, (__nv_bfloat16*)best_min,
+                                                        org_max, org_min, min_err, nu, (int)gs, clip_sym);
+  else
+    ac_init_kernel<__half><<<grid, 256, 0, st>>>((const __half*)W, (__half*)best_max, (__half*)best_min, org_max, org_min, min_err,
+                                                 nu, (int)gs, clip_sym);
+  LCB_CUDA_CHECK_LAUNCH("ac_init");
+  return LCB_OK;
+}
+
+extern "C" int lcb_autoclip_step(const void* Wq, const void* x, void* org, const float* org_max, const float* org_min,
+                                 float* min_err, void* best_max, void* best_min, int64_t R, int64_t C, int64_t T_rows,
+                                 int64_t tokens, int32_t group_size, float ratio, int32_t clip_sym, int32_t is_org, int32_t dtype,
+                                 void* stream) {
+  using namespace lcb;
+  if (!Wq || !x || !org) return LCB_E_INVALID;
+  if (!is_org && (!org_max || !org_min || !min_err || !best_max || !best_min)) return LCB_E_INVALID;
+  if (R < 1 || C < 1 || T_rows < 1 || tokens < 1 || tokens > T_rows) return LCB_E_INVALID;
+  if (dtype != LCB_BF16 && dtype != LCB_F16) return LCB_E_UNSUPPORTED;
+  const int64_t gs = group_size > 0 ? group_size : C;
+  if (C % gs) return LCB_E_SHAPE;
+  if (gs % 8 || (gs > 128 && gs % 128) || T_rows % 8) return LCB_E_UNSUPPORTED;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == LCB_BF16) {
+    using T = __nv_bfloat16;
+    return is_org ? launch_ac<T, true>((const T*)Wq, (const T*)x, (T*)org, org_max, org_min, min_err, (T*)best_max, (T*)best_min, R, C,
+                                       T_rows, (int)gs, 1.f, (float)tokens, clip_sym, st)
+                  : launch_ac<T, false>((const T*)Wq, (const T*)x, (T*)org, org_max, org_min, min_err, (T*)best_max, (T*)best_min, R,
+                                        C, T_rows, (int)gs, ratio, (float)tokens, clip_sym, st);
+  }
+  using T = __half;
+  return is_org ? launch_ac<T, true>((const T*)Wq, (const T*)x, (T*)org, org_max, org_min, min_err, (T*)best_max, (T*)best_min, R, C,
+                                     T_rows, (int)gs, 1.f, (float)tokens, clip_sym, st)
+                : launch_ac<T, false>((const T*)Wq, (const T*)x, (T*)org, org_max, org_min, min_err, (T*)best_max, (T*)best_min, R, C,
+                                      T_rows, (int)gs, ratio, (float)tokens, clip_sym, st);
+}

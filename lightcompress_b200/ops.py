@@ -243,6 +243,77 @@ def awq_candidates(W, x, org_out, cand_scales, wquantizer):
     return loss / float(T * R)
 
 
+def _autoclip_geometry(W, wquantizer):
+    g = wquantizer.granularity
+    if g == 'per_group':
+        gs = wquantizer.group_size
+    elif g == 'per_channel':
+        gs = 0
+    else:
+        raise NotImplementedError(f'autoclip: weight granularity {g}')
+    return gs, (W.shape[1] // gs if gs > 0 else 1)
+
+
+def autoclip_pad_tokens(x2):
+    """[tokens, C] -> ([T_rows, C] contiguous with T_rows = tokens rounded up to 8, zero rows appended; tokens)."""
+    tokens, C = x2.shape
+    T_rows = -(-tokens // 8) * 8
+    if T_rows != tokens:   # zero rows add nothing to the squared error; the mean still divides by `tokens`
+        xp = torch.zeros((T_rows, C), dtype=x2.dtype, device=x2.device)
+        xp[:tokens] = x2
+        x2 = xp
+    return x2.contiguous(), tokens
+
+
+class AutoClipState(object):
+    """Buffers of one taken-apart AutoClip search (lcb_autoclip_init / lcb_autoclip_step): the host composes the weights
+    of every shrink step itself (clip_version 'v2', w+a)."""
+
+    def __init__(self, W, wquantizer, clip_sym, T_rows, tokens):
+        _need_cuda(W)
+        if W.dtype not in (torch.bfloat16, torch.float16):
+            raise TypeError(f'autoclip: W is {W.dtype}')
+        self.W = W.contiguous()
+        self.R, self.C = W.shape
+        self.gs, self.ng = _autoclip_geometry(W, wquantizer)
+        self.clip_sym, self.T_rows, self.tokens = bool(clip_sym), int(T_rows), int(tokens)
+        dev, nu = W.device, self.R * self.ng
+        self.best_max = torch.empty((self.R, self.ng, 1), dtype=W.dtype, device=dev)
+        self.best_min = torch.empty((self.R, self.ng, 1), dtype=W.dtype, device=dev)
+        self.org_max = torch.empty(nu, dtype=torch.float32, device=dev)
+        self.org_min = torch.empty(nu, dtype=torch.float32, device=dev)
+        self.min_err = torch.empty(nu, dtype=torch.float32, device=dev)
+        self.org = torch.empty((self.ng, self.R, self.T_rows), dtype=W.dtype, device=dev)
+        lib = _cabi.load()
+        with _on_device(dev):
+            st = lib.lcb_autoclip_init(self.W.data_ptr(), self.best_max.data_ptr(), self.best_min.data_ptr(),
+                                       self.org_max.data_ptr(), self.org_min.data_ptr(), self.min_err.data_ptr(), self.R, self.C,
+                                       self.gs, 1 if clip_sym else 0, _DT[W.dtype], _stream(dev.index))
+        _cabi.check(st, 'lcb_autoclip_init')
+
+    def _step(self, Wq, x, ratio, is_org):
+        _need_cuda(Wq, x)
+        if Wq.dtype != self.W.dtype or x.dtype != self.W.dtype or tuple(Wq.shape) != (self.R, self.C) \
+                or tuple(x.shape) != (self.T_rows, self.C):
+            raise ValueError(f'autoclip step: Wq {tuple(Wq.shape)} {Wq.dtype}, x {tuple(x.shape)} {x.dtype}')
+        Wq, x = Wq.contiguous(), x.contiguous()
+        lib = _cabi.load()
+        with _on_device(Wq.device):
+            st = lib.lcb_autoclip_step(Wq.data_ptr(), x.data_ptr(), self.org.data_ptr(), self.org_max.data_ptr(),
+                                       self.org_min.data_ptr(), self.min_err.data_ptr(), self.best_max.data_ptr(),
+                                       self.best_min.data_ptr(), self.R, self.C, self.T_rows, self.tokens, self.gs, float(ratio),
+                                       1 if self.clip_sym else 0, 1 if is_org else 0, _DT[Wq.dtype], _stream(Wq.device.index))
+        _cabi.check(st, 'lcb_autoclip_step')
+
+    def original(self, x):
+        """org_out = (x * w).sum(-1) on the plain inputs (auto_clip.py:151)."""
+        self._step(self.W, x, 1.0, True)
+
+    def candidate(self, Wq, xq, ratio):
+        """One shrink step: Wq = this step's fake-quantized weights, xq = the (fake-quantized) inputs (auto_clip.py:154-179)."""
+        self._step(Wq, xq, ratio, False)
+
+
 def autoclip_search(W, x, wquantizer, clip_sym, n_grid=20, max_shrink=0.5):
     """AutoClip v1 search of one linear (auto_clip.py:84-191): returns (best_max_val, best_min_val), each [R, n_group, 1]
     in W.dtype. W [R, C] bf16 / f16; x [tokens, C] = the sampled tokens (auto_clip.py:131-133) in the same dtype."""
@@ -252,21 +323,9 @@ def autoclip_search(W, x, wquantizer, clip_sym, n_grid=20, max_shrink=0.5):
     x2 = x.reshape(-1, C)
     if x2.dtype != W.dtype:
         raise TypeError(f'autoclip_search: x is {x2.dtype}, W is {W.dtype}')
-    tokens = x2.shape[0]
-    T_rows = -(-tokens // 8) * 8
-    if T_rows != tokens:   # zero rows add nothing to the squared error; the mean still divides by `tokens`
-        xp = torch.zeros((T_rows, C), dtype=x2.dtype, device=x2.device)
-        xp[:tokens] = x2
-        x2 = xp
-    x2 = x2.contiguous()
-    g = wquantizer.granularity
-    if g == 'per_group':
-        gs = wquantizer.group_size
-    elif g == 'per_channel':
-        gs = 0
-    else:
-        raise NotImplementedError(f'autoclip_search: weight granularity {g}')
-    ng = C // gs if gs > 0 else 1
+    x2, tokens = autoclip_pad_tokens(x2)
+    T_rows = x2.shape[0]
+    gs, ng = _autoclip_geometry(W, wquantizer)
     qmin, qmax = wquantizer._qrange()
     spec = wquantizer._spec(W.dtype, W.dtype, W.dtype, _cabi.OUT_FAKE, qmin, qmax, 1.0, 1.0, _DT[W.dtype] + 1)
     lib = _cabi.load()

@@ -296,6 +296,71 @@ def test_awq_vs_reference_pipeline(mtype, clip):
         assert min(same.values()) > 0.995, same
 
 
+A8 = {'bit': 8, 'symmetric': True, 'granularity': 'per_token'}
+W8_LEARNABLE = {'bit': 8, 'symmetric': False, 'granularity': 'per_channel', 'group_size': -1, 'calib_algo': 'learnable'}
+A8_ASYM = {'bit': 8, 'symmetric': False, 'granularity': 'per_token', 'calib_algo': 'minmax'}
+
+
+@pytest.mark.parametrize('name,calib_spec,weight,act,special', [
+    # several calibration batches (calib.bs != -1): the in-loop best-so-far comparison of awq.py:240-248
+    ('multi_batch', (4, 4), W4, None, dict(AWQ_SP, weight_clip=False)),
+    ('multi_batch_clip', (4, 4), W4, None, dict(AWQ_SP)),
+    # awq_bs: one batch of 16 samples searched in chunks of 4 (awq.py:74-85, 110-145)
+    ('awq_bs', (1, 16), W4, None, dict(AWQ_SP, weight_clip=False, awq_bs=4)),
+    # w+a: the scaled input is fake-quantized before the inspect forward (awq.py:166-177, 226-227)
+    ('w4a8', (1, 16), W4, A8, dict(AWQ_SP, weight_clip=False)),
+    ('w4a8_clip_v1', (1, 16), W4, A8, dict(AWQ_SP)),
+    ('w4a8_awq_bs', (1, 16), W4, A8, dict(AWQ_SP, weight_clip=False, awq_bs=8)),
+    # configs/quantization/combination/awq_comb_omni/w8a8/step_1_awq.yml: per_channel learnable weights, clip v2, w+a
+    ('w8a8_clip_v2', (1, 16), W8_LEARNABLE, A8_ASYM, dict(AWQ_SP, clip_version='v2', save_clip=True,
+                                                          clip_path='/tmp/lcb_ref_clips')),
+    ('w6a6_clip_v2_sym', (1, 16), dict(W8_LEARNABLE, bit=6, symmetric=True), dict(A8_ASYM, bit=6),
+     dict(AWQ_SP, clip_version='v2', clip_sym=True)),
+])
+def test_awq_general_vs_reference_pipeline(name, calib_spec, weight, act, special):
+    model = tiny_llama(seed=3, kv_heads=2)
+    calib, ev = tokens(calib_spec[0], 64, 201, batch=calib_spec[1]), tokens(24, 128, 202)
+    q = {'method': 'Awq', 'weight': weight, 'special': special}
+    if act is not None:
+        q['act'] = act
+    ref_clips = {}
+    ref, ropt = run_reference(model, 'Llama', q, calib, patch=_record_clips(ref_clips))
+    _record_clips(None)(rh.activate('cuda'))
+    got, gopt = run_product(model, 'Llama', q, calib)
+    assert set(ropt.act_scales) == set(gopt.act_scales), (sorted(ropt.act_scales), sorted(gopt.act_scales))
+    worst = 0.0
+    for k, s_ref in ropt.act_scales.items():
+        s_got = gopt.act_scales[k].float()
+        worst = max(worst, float(((s_ref.float().to(DEV) - s_got).abs() / s_ref.float().to(DEV).abs()).max()))
+    print(f'[AWQ {name}] selected candidate per subset: {gopt.best_index}; worst relative scale difference {worst:.2e}')
+    assert worst < 2e-2          # the same candidate (adjacent ratios differ by far more than this)
+    if special.get('weight_clip', False):
+        agree = []
+        for (bi, n), (mx, mn) in ref_clips.items():
+            gmx, gmn = gopt.clips[(bi, n)]
+            agree.append(float(((mx.to(DEV) == gmx) & (mn.to(DEV) == gmn)).float().mean()))
+        print(f'[AWQ {name}] AutoClip range agreement per layer: min {min(agree):.4f} mean {sum(agree) / len(agree):.4f}')
+        assert min(agree) > 0.97, agree
+        if special.get('clip_version') == 'v2':      # the learnable bounds live in module buffers; the weight is untouched
+            rclips = ropt.auto_clipper.weight_clips
+            if special.get('save_clip'):
+                assert set(rclips) == set(gopt.weight_clips)
+                for bi in rclips:
+                    assert set(rclips[bi]) == set(gopt.weight_clips[bi])
+                    for k, v in rclips[bi].items():
+                        g = gopt.weight_clips[bi][k]
+                        assert (v is None) == (g is None), k
+                        if v is not None:
+                            same_f = float((v == g).float().mean())
+                            assert same_f > 0.97, (k, same_f)
+    same, rel, lp = compare(ref, got, model, ev, f'AWQ {name}')
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    if not special.get('weight_clip', False):
+        assert min(same.values()) > 0.995, same
+    else:
+        assert min(same.values()) > 0.97, same
+
+
 # ---- SmoothQuant w8a8 ------------------------------------------------------------------------------------------------
 def test_smoothquant_vs_reference_pipeline():
     model = tiny_llama(seed=5)
@@ -388,3 +453,24 @@ def test_patch_reference_on_the_real_classes(method, mode):
         return
     assert abs(lp['got'] - lp['ref']) <= BAR, lp
     assert min(same.values()) > 0.5 and max(rel.values()) < 0.2, (same, rel)
+
+
+@pytest.mark.parametrize('mode', ['swap', 'swap+patch'])
+def test_patch_reference_awq_comb_omni_step1(mode):
+    """awq_comb_omni/w8a8/step_1_awq.yml on the reference's own classes: w+a search, AutoClip v2 (learnable bounds)."""
+    mods = rh.activate('cuda')
+    model = tiny_llama(seed=3, kv_heads=2)
+    calib, ev = tokens(1, 64, 201, batch=16), tokens(24, 128, 202)
+    q = {'method': 'Awq', 'weight': W8_LEARNABLE, 'act': A8_ASYM, 'special': dict(AWQ_SP, clip_version='v2')}
+    ref, _ = run_reference(model, 'Llama', q, calib)
+    try:
+        patched, popt = run_reference(model, 'Llama', q, calib,
+                                      patch={'swap': _swap_classes, 'swap+patch': _swap_and_patch}[mode])
+    finally:
+        _unpatch_all(mods)
+    same, rel, lp = compare(ref, patched, model, ev, f'INTEGRATION 3 [{mode}] awq_comb_omni step 1')
+    assert abs(lp['got'] - lp['ref']) <= BAR, lp
+    if mode == 'swap':
+        assert min(same.values()) == 1.0, same
+    else:
+        assert min(same.values()) > 0.97, same
