@@ -212,6 +212,19 @@ int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, const float* b_
 int lcb_hessian_accum(float* S, const void* X, int64_t tokens, int64_t C, int32_t x_dtype, void* workspace,
                       void* stream);
 int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C, int32_t x_dtype);
+/*
+ * Allocation-free variant of lcb_hessian_accum for f32 X. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). Same arithmetic, kernels and S contract as lcb_hessian_accum(S, X, tokens, C, LCB_F32, workspace, stream); the
+ * bf16 hi / lo split buffers live in a 16 MiB static __device__ array inside the library (held by every GPU that loads
+ * it until exit) instead of a caller workspace. The call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine). Limit: tokens * C <= LCB_HESSIAN_NOALLOC_MAX_ELEMS (e.g. 1024 tokens x 4096 channels); beyond it
+ * the call returns LCB_E_SHAPE with the reason in lcb_last_error() and launches nothing - split the tokens over several
+ * calls (S is a running sum). Every call on one GPU shares the array: calls that overlap on the GPU (different streams
+ * or threads) race; calls ordered on one stream do not. Nothing in the array has to start at zero.
+ */
+#define LCB_HESSIAN_NOALLOC_MAX_ELEMS (4ll << 20)
+int lcb_hessian_accum_f32_noalloc(float* S, const float* X, int64_t tokens, int64_t C, void* stream);
 /* H = scale * sym(S) in place: scales the upper blocks and mirrors them into the lower ones. scale = 2 / nsamples. */
 int lcb_hessian_finalize(float* S, int64_t C, double scale, void* stream);
 /*

@@ -218,3 +218,57 @@ extern "C" int lcb_hessian_finalize(float* S, int64_t C, double scale, void* str
   LCB_CUDA_CHECK_LAUNCH("hessian_finalize");
   return LCB_OK;
 }
+
+// ---- allocation-free variant of the fp32 path (no counterpart in the reference)
+// Callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it) get the bf16
+// hi / lo split buffers from a file-scope device array instead of a caller workspace. Every GPU that loads the library
+// holds the array until exit; every call shares it, so calls that overlap on one GPU (two streams, two threads) race.
+// Nothing in it has to start at zero: split_f32_kernel writes each element the GEMM reads before the GEMM reads it.
+namespace lcb {
+namespace {
+constexpr int64_t kNoAllocMaxElems = LCB_HESSIAN_NOALLOC_MAX_ELEMS;                       // tokens * C of one call
+static __device__ __align__(256) unsigned char g_hessian_scratch[kNoAllocMaxElems * 4];  // bf16 hi + bf16 lo = 16 MiB
+
+// In host code g_hessian_scratch is only a stand-in for the symbol, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_hessian_scratch_addr[kMaxDevices];
+
+int hessian_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_last_error("lcb_hessian_accum_f32_noalloc: cudaGetDevice", e);
+    return LCB_E_CUDA;
+  }
+  const bool cached = dev >= 0 && dev < kMaxDevices;
+  void* p = cached ? g_hessian_scratch_addr[dev].load(std::memory_order_acquire) : nullptr;
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_hessian_scratch);
+    if (e != cudaSuccess || !p) {
+      set_last_error("lcb_hessian_accum_f32_noalloc: cudaGetSymbolAddress(g_hessian_scratch)", e);
+      return LCB_E_CUDA;
+    }
+    if (cached) g_hessian_scratch_addr[dev].store(p, std::memory_order_release);  // racing threads store the same address
+  }
+  *out = p;
+  return LCB_OK;
+}
+}  // namespace
+}  // namespace lcb
+
+extern "C" int lcb_hessian_accum_f32_noalloc(float* S, const float* X, int64_t tokens, int64_t C, void* stream) {
+  using namespace lcb;
+  if (!S || !X || tokens < 0 || C < 1) return LCB_E_INVALID;
+  if (tokens == 0) return LCB_OK;
+  if (tokens > kNoAllocMaxElems || C > kNoAllocMaxElems || tokens * C > kNoAllocMaxElems) {
+    set_last_error("lcb_hessian_accum_f32_noalloc: tokens * C exceeds LCB_HESSIAN_NOALLOC_MAX_ELEMS (4194304); "
+                   "split the tokens over several calls or use lcb_hessian_accum with a workspace",
+                   cudaErrorInvalidValue);
+    return LCB_E_SHAPE;
+  }
+  void* scratch = nullptr;
+  const int rc = hessian_scratch_for_current_device(&scratch);
+  if (rc != LCB_OK) return rc;
+  return lcb_hessian_accum(S, X, tokens, C, LCB_F32, scratch, stream);
+}
