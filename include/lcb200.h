@@ -158,7 +158,7 @@ int lcb_fakequant_multi(const void* const* ins, void* const* outs, const int64_t
 
 /*
  * Dynamic FP8 per_block (128 x 128, fp32 math and scales: weight_cast_to_fp8 / FloatQuantizer per_block, quant.py:34-43,
- * 1043-1221) of up to 16 bf16 / f16 weights in ONE launch — the expert matrices of a MoE block. spec->out_mode is
+ * 1043-1221) of up to 64 bf16 / f16 weights in ONE launch — the expert matrices of a MoE block. spec->out_mode is
  * LCB_OUT_FAKE (outs[i]: spec->dtype) or LCB_OUT_FP8 (outs[i]: one byte per element); scales may be NULL, or an array whose
  * entries are NULL or fp32 [ceil(rows/128) * ceil(cols/128)]. cols[i] % 8 == 0 (16-byte row pitch for TMA). Same
  * arithmetic as lcb_fakequant. Returns LCB_E_UNSUPPORTED outside that envelope (callers then loop over lcb_fakequant).

@@ -557,7 +557,7 @@ class BaseBlockwiseQuantization(object):
             plain = type(self).w_q is BaseBlockwiseQuantization.w_q and hasattr(self.wquantizer, 'real_quant_weights_dynamic')
             pre = {}
             if plain and issubclass(cls, _vllm_cls()):
-                # dynamic w_q of every linear of the block at once: FP8 per_block expert matrices go 16 per launch
+                # dynamic w_q of every linear of the block at once: FP8 per_block expert matrices go 64 per launch
                 mods = [m for m in named.values() if not getattr(m, 'no_quant', False)
                         and m.weight.dtype != torch.float8_e4m3fn]
                 for m, res in zip(mods, self.wquantizer.real_quant_weights_dynamic([m.weight.data for m in mods])):

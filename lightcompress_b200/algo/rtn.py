@@ -32,7 +32,7 @@ def rtn_real_quantize_sharded(named_weights, wquantizer, quantize=None, gather=T
     out = {}
     mine = [n for i, n in enumerate(names) if i % ws == rank]
     if quantize is None and hasattr(wquantizer, 'real_quant_weights_dynamic'):
-        # FP8 per_block experts: 16 weights per launch (lcb_fakequant_block_fp8_multi); otherwise the same per-tensor calls
+        # FP8 per_block experts: 64 weights per launch (lcb_fakequant_block_fp8_multi); otherwise the same per-tensor calls
         out.update(zip(mine, wquantizer.real_quant_weights_dynamic([named_weights[n] for n in mine])))
     else:
         quantize = quantize or wquantizer.real_quant_weight_dynamic

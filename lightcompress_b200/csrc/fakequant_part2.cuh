@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(256)
 
 // Several weights in ONE launch (the expert matrices of a MoE block: 2.9 M elements each for DeepSeek-V2-Lite, ~1 us of
 // kernel against ~10 us of host work per call). Tiles of all tensors are laid end to end.
-constexpr int kMaxBlockMulti = 16;
+constexpr int kMaxBlockMulti = 64;   // 64 x (128 B tensor map + 48 B) = 11 KB of kernel parameters (limit 32 KB)
 struct BlockMultiDesc {
   CUtensorMap tm[kMaxBlockMulti];
   void* out[kMaxBlockMulti];
@@ -382,8 +382,10 @@ struct BlockMultiDesc {
 };
 template <typename T, int E5M2, int OUT_CODES>
 __global__ void __launch_bounds__(256) fq_block2d_fp8_tma_multi_kernel(const __grid_constant__ BlockMultiDesc md, SpecD sp) {
-  int t = 0;
-  while (t + 1 < md.n && (int64_t)blockIdx.x >= md.tile_start[t + 1]) ++t;   // CTA-uniform
+  int t = 0;   // last tensor whose first tile is <= blockIdx.x (CTA-uniform binary search; empty tensors own no tile)
+#pragma unroll
+  for (int step = kMaxBlockMulti / 2; step > 0; step >>= 1)
+    if (t + step < md.n && (int64_t)blockIdx.x >= md.tile_start[t + step]) t += step;
   block2d_fp8_tma_tile<T, E5M2, OUT_CODES>(&md.tm[t], md.out[t], md.scales[t], md.rows[t], md.cols[t],
                                            (int64_t)blockIdx.x - md.tile_start[t], sp);
 }

@@ -624,7 +624,9 @@ class BaseQuantizer(object):
         import ctypes
         ws = list(weights)
         if self._block_fp8_multi_ok(ws):
-            return self._block_fp8_multi(ws, _cabi.OUT_FAKE)
+            res = self._block_fp8_multi(ws, _cabi.OUT_FAKE)
+            if res is not None:
+                return res
         ok = (len(ws) > 0 and self.granularity == 'per_group' and self.calib_algo == 'minmax'
               and all(w.is_cuda and w.is_contiguous() and w.dtype == ws[0].dtype and w.device == ws[0].device
                       and w.dim() >= 1 and w.shape[-1] >= self.group_size and w.shape[-1] % self.group_size == 0
@@ -655,48 +657,96 @@ class BaseQuantizer(object):
         return outs_all
 
     def _block_fp8_multi_ok(self, ws):
+        """the quantizer-side half of the multi-tensor envelope; the per-tensor half is checked by _block_fp8_multi's scan"""
         return (len(ws) > 0 and self.granularity == 'per_block' and self._kind() != _cabi.KIND_INT
                 and self.calib_algo != 'hqq' and self.calib_algo != 'mse' and getattr(self, 'block_size', 0) == 128
-                and all(w.is_cuda and w.dim() == 2 and w.is_contiguous() and w.dtype == ws[0].dtype
-                        and w.device == ws[0].device and w.shape[1] % 8 == 0 for w in ws)
-                and ws[0].dtype in (torch.bfloat16, torch.float16))
+                and ws[0].is_cuda and ws[0].dtype in (torch.bfloat16, torch.float16))
 
     def _block_fp8_multi(self, ws, out_mode):
-        """FP8 per_block (128 x 128) dynamic quant of a list of 16-bit weights, 16 per launch
-        (lcb_fakequant_block_fp8_multi). out_mode OUT_FAKE -> [fake weights]; OUT_FP8 -> [(codes, scales, None)]."""
+        """FP8 per_block (128 x 128) dynamic quant of a list of 16-bit weights, 64 per launch
+        (lcb_fakequant_block_fp8_multi). out_mode OUT_FAKE -> [fake weights]; OUT_FP8 -> [(codes, scales, None)];
+        None when a weight is outside the envelope (the caller then loops over the per-tensor entry).
+
+        A MoE block hands over ~200 small matrices (1.4 us of HBM traffic each), so the host side is the cost. One scan
+        over the list (shape, layout, address); outputs of equal shape are slices of ONE allocation (rows of a
+        `[n, pitch]` pool: two allocator calls per distinct shape instead of two per weight — the slices keep their pool
+        alive until the last one is dropped, which is what a deployed model does anyway), their addresses follow from
+        the pool's base address, so every launch is issued BEFORE the per-weight tensor objects are created: the GPU
+        works while Python builds the 2 x n views."""
         import ctypes
         lib = _cabi._lib or _cabi.load()
-        dt = ws[0].dtype
+        dt, dev = ws[0].dtype, ws[0].device
+        real = out_mode == _cabi.OUT_FP8
+        n_all = len(ws)
+        rows, cols, in_ptr = [0] * n_all, [0] * n_all, [0] * n_all
+        by_shape = {}
+        for i, w in enumerate(ws):
+            sh = w.shape
+            if len(sh) != 2 or sh[1] % 8 or w.dtype != dt or w.device != dev or not w.is_contiguous():
+                return None
+            rows[i], cols[i] = sh
+            in_ptr[i] = w.data_ptr()
+            by_shape.setdefault(sh, []).append(i)
         qmin, qmax = self._qrange()
         spec = self._spec(dt, torch.float32, torch.float32, out_mode, qmin, qmax, 1.0, 1.0, _DT[torch.float32] + 1)
-        res = []
-        real = out_mode == _cabi.OUT_FP8
-        with _on_device(ws[0].device):
-            for i0 in range(0, len(ws), 16):
-                part = ws[i0:i0 + 16]
-                n = len(part)
-                outs = [torch.empty(w.shape, dtype=torch.uint8 if real else dt, device=w.device) for w in part]
-                scs = [torch.empty(((w.shape[0] + 127) // 128, (w.shape[1] + 127) // 128), dtype=torch.float32,
-                                   device=w.device) for w in part] if real else None
-                ins_a = (ctypes.c_void_p * n)(*[w.data_ptr() for w in part])
-                outs_a = (ctypes.c_void_p * n)(*[o.data_ptr() for o in outs])
-                scs_a = (ctypes.c_void_p * n)(*[t.data_ptr() for t in scs]) if real else None
-                rows_a = (ctypes.c_int64 * n)(*[w.shape[0] for w in part])
-                cols_a = (ctypes.c_int64 * n)(*[w.shape[1] for w in part])
-                st = lib.lcb_fakequant_block_fp8_multi(ins_a, outs_a, scs_a, rows_a, cols_a, n, spec,
-                                                       _stream(ws[0].device.index))
-                if st == -3:   # LCB_E_UNSUPPORTED: outside the multi-tensor envelope
-                    if real:
-                        res.extend(self.real_quant_weight_dynamic(w) for w in part)
-                    else:
-                        res.extend(self.fake_quant_weight_dynamic(w) for w in part)
+
+        def pool_of(k, shape, dtype, view_dtype=None):
+            """k tensors of `shape` carved out of one allocation, each starting on a 256-byte boundary (the kernel wants
+            16-byte aligned outputs; a [1, 8] matrix of bytes is 8 bytes long). Returns (2-D pool view, base, step)."""
+            n = shape[0] * shape[1]
+            es = 1 if dtype == torch.uint8 else (4 if dtype == torch.float32 else 2)
+            pitch = -(-n * es // 256) * 256 // es
+            pool = torch.empty((k, pitch), dtype=dtype, device=dev)
+            base = pool.data_ptr()
+            if view_dtype is not None:
+                pool = pool.view(view_dtype)
+            return pool[:, :n].unflatten(1, (shape[0], shape[1])), base, pitch * es
+
+        out_ptr, sc_ptr = [0] * n_all, [0] * n_all
+        pools = []
+        for sh, idx in by_shape.items():
+            k = len(idx)
+            pool, base, step = pool_of(k, sh, torch.uint8 if real else dt, self._fp8_dtype() if real else None)
+            for j, i in enumerate(idx):
+                out_ptr[i] = base + j * step
+            spool = None
+            if real:
+                spool, base, step = pool_of(k, ((sh[0] + 127) // 128, (sh[1] + 127) // 128), torch.float32)
+                for j, i in enumerate(idx):
+                    sc_ptr[i] = base + j * step
+            pools.append((idx, pool, spool))
+        stream = _stream(dev.index)
+        per_launch = 64
+        redo = []
+        with _on_device(dev):
+            for i0 in range(0, n_all, per_launch):
+                i1 = min(n_all, i0 + per_launch)
+                n = i1 - i0
+                ins_a = (ctypes.c_void_p * n)(*in_ptr[i0:i1])
+                outs_a = (ctypes.c_void_p * n)(*out_ptr[i0:i1])
+                scs_a = (ctypes.c_void_p * n)(*sc_ptr[i0:i1]) if real else None
+                rows_a = (ctypes.c_int64 * n)(*rows[i0:i1])
+                cols_a = (ctypes.c_int64 * n)(*cols[i0:i1])
+                st = lib.lcb_fakequant_block_fp8_multi(ins_a, outs_a, scs_a, rows_a, cols_a, n, spec, stream)
+                if st == -3:   # LCB_E_UNSUPPORTED: outside the multi-tensor envelope -> the per-tensor entry, same results
+                    redo.extend(range(i0, i1))
                     continue
                 _cabi.check(st, 'lcb_fakequant_block_fp8_multi')
-                if real:
-                    res.extend((o.view(self._fp8_dtype()), sc, None) for o, sc in zip(outs, scs))
-                else:
-                    res.extend(outs)
-        return res
+        outs, scs = [None] * n_all, [None] * n_all
+        for idx, pool, spool in pools:
+            for i, o in zip(idx, pool.unbind(0)):
+                outs[i] = o
+            if spool is not None:
+                for i, sc in zip(idx, spool.unbind(0)):
+                    scs[i] = sc
+        for i in redo:
+            if real:
+                outs[i], scs[i], _ = self.real_quant_weight_dynamic(ws[i])
+            else:
+                outs[i] = self.fake_quant_weight_dynamic(ws[i])
+        if real:
+            return [(o, sc, None) for o, sc in zip(outs, scs)]
+        return outs
 
     def fake_quant_weight_clipped(self, weight, ratio, clip_sym=False):
         """AutoClipper.fake_quantize_weight, clip_version 'v1' (auto_clip.py:258-260) at one shrink step:
@@ -854,10 +904,12 @@ class FloatQuantizer(BaseQuantizer):
 
     def real_quant_weights_dynamic(self, weights):
         """Extension (not in the reference API): real_quant_weight_dynamic of a list of weights — FP8 per_block weights go
-        16 per launch (the expert matrices of a MoE block); anything else loops. Same results as the per-tensor calls."""
+        64 per launch (the expert matrices of a MoE block); anything else loops. Same results as the per-tensor calls."""
         ws = list(weights)
         if self.bit in ['e4m3', 'e5m2'] and self._block_fp8_multi_ok(ws):
-            return self._block_fp8_multi(ws, _cabi.OUT_FP8)
+            res = self._block_fp8_multi(ws, _cabi.OUT_FP8)
+            if res is not None:
+                return res
         return [self.real_quant_weight_dynamic(w) for w in ws]
 
     def real_quant_weight_static(self, weight, args):

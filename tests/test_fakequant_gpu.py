@@ -193,10 +193,11 @@ def test_per_block_fp8_nonfinite_tile_takes_the_literal_chain():
 @pytest.mark.parametrize('bit', ['e4m3', 'e5m2'])
 @pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16])
 def test_block_fp8_multi_launch_equals_single_launches(bit, dtype):
-    """lcb_fakequant_block_fp8_multi (16 weights per launch: MoE experts) == the per-tensor calls, bit for bit."""
+    """lcb_fakequant_block_fp8_multi (64 weights per launch: MoE experts; outputs of equal shape share one allocation) ==
+    the per-tensor calls, bit for bit."""
     torch.manual_seed(9)
-    shapes = [(1408, 2048), (2048, 1408), (576, 2048), (130, 72), (128, 128), (1, 8), (300, 264)] * 3    # 21 -> two launches
-    ws = [(torch.randn(s, device=DEV) * (0.02 * (i + 1))).to(dtype) for i, s in enumerate(shapes)]
+    shapes = [(1408, 2048), (2048, 1408), (576, 2048), (130, 72), (128, 128), (1, 8), (300, 264)] * 11    # 77 -> two launches (64 + 13)
+    ws = [(torch.randn(s, device=DEV) * (0.02 * (i % 9 + 1))).to(dtype) for i, s in enumerate(shapes)]
     ws[4][5, 7] = float('inf')     # one tile on the literal chain
     q = Q.FloatQuantizer(bit, True, 'per_block', block_size=128, use_qtorch=True)
     for w, m in zip(ws, q.fake_quant_weights_dynamic(ws)):

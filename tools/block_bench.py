@@ -5,7 +5,8 @@ Llama-3-8B dimensions (hidden 4096, inter 14336, 32 heads / 8 KV heads) — BASE
 
 GPTQ: 128 samples x 2048 tokens, w4a16 g128, actorder + true_sequential + quant_out — the shipped recipe verbatim
       (configs/quantization/methods/GPTQ/gptq_w_only.yml:25-38).
-AWQ : 128 samples x 512 tokens, w4a16 g128, trans v2 + weight_clip (awq_w_only.yml).
+AWQ : 128 samples x 512 tokens in ONE batch (`bs: -1`), w4a16 g128, trans v2 + weight_clip (awq_w_only.yml). Several
+      batches would take the reference's literal per-batch loop (awq.py:240-248) instead: 20 x n_batches module forwards.
 The time covers everything `block_opt` does for the block: the hooked forward(s), Hessians / searches, factorisations,
 updates, scale application, clipping — including the attention / MLP module forwards the searches need (torch ops).
 The model holds TWO such blocks and the SECOND one is the reported number: the steady state of a 32-block run, where the
@@ -35,10 +36,12 @@ def one_block_llama(dev, seed=0, n_blocks=2):
     return m
 
 
-def run(method, dev, samples, seq, special, quant_out=False):
+def run(method, dev, samples, seq, special, quant_out=False, bs=1):
+    """bs: rows per calibration batch (the recipe's `calib.bs`; -1 = all samples in ONE batch, awq_w_only.yml:13)."""
     model = one_block_llama(dev)
     g = torch.Generator().manual_seed(1)
-    data = [{'input_ids': torch.randint(0, 1024, (1, seq), generator=g).to(dev)} for _ in range(samples)]
+    bs = samples if bs == -1 else bs
+    data = [{'input_ids': torch.randint(0, 1024, (bs, seq), generator=g).to(dev)} for _ in range(samples // bs)]
     ad = algo.adapters.LlamaAdapter(model)
     inp = ad.collect_first_block_input(data)
     a = algo.ALGO_REGISTRY[method](ad, {'weight': dict(W4), 'special': special, 'quant_out': quant_out}, inp, None,
@@ -81,11 +84,11 @@ def main(argv=None, emit=True):
         res['gptq_config'] = f'{samples} x 2048 tokens, w4a16 g128, actorder, true_sequential, quant_out (gptq_w_only.yml)'
     if 'awq' in which:
         sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
-        run('Awq', dev, 2, 512, sp)
-        t = run('Awq', dev, samples, 512, sp)
+        run('Awq', dev, 2, 512, sp, bs=-1)
+        t = run('Awq', dev, samples, 512, sp, bs=-1)
         res['awq_s_per_block'], res['awq_s_first_block'] = t[-1], t[0]
         res['awq_memory'] = MEM.get('Awq')
-        res['awq_config'] = f'{samples} x 512 tokens, w4a16 g128, trans v2 + AutoClip'
+        res['awq_config'] = f'{samples} x 512 tokens (one batch, bs -1), w4a16 g128, trans v2 + AutoClip'
     if emit:
         print(json.dumps(res), flush=True)
     return res

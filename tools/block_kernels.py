@@ -25,7 +25,8 @@ else:
     sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
 model = bb.one_block_llama(dev, n_blocks=2)
 g = torch.Generator().manual_seed(1)
-data = [{'input_ids': torch.randint(0, 1024, (1, seq), generator=g).to(dev)} for _ in range(samples)]
+bs = samples if method == 'awq' else 1   # awq_w_only.yml: bs -1 (one batch); gptq_w_only.yml: bs 1
+data = [{'input_ids': torch.randint(0, 1024, (bs, seq), generator=g).to(dev)} for _ in range(samples // bs)]
 ad = algo.adapters.LlamaAdapter(model)
 inp = ad.collect_first_block_input(data)
 a = algo.ALGO_REGISTRY[name](ad, {'weight': dict(bb.W4), 'special': sp, 'quant_out': qo}, inp, None, {'calib': {'seq_len': seq}})

@@ -45,8 +45,8 @@ if method == 'gptq':
     t = bb.run('GPTQ', dev, 128, 2048, sp, True)
 else:
     sp = {'trans': True, 'trans_version': 'v2', 'weight_clip': True, 'clip_sym': False}
-    bb.run('Awq', dev, 2, 512, sp)
+    bb.run('Awq', dev, 2, 512, sp, bs=-1)
     acc.clear()
-    t = bb.run('Awq', dev, 128, 512, sp)
+    t = bb.run('Awq', dev, 128, 512, sp, bs=-1)
 print('wall per block', [round(v, 4) for v in t], '(phase sums cover BOTH blocks)', {k: round(v, 4) for k, v in acc.items()})
 # nested: block_forward is inside rehook_next_subset / _forward_fake_quant; factor / finalize / w_qdq inside the others
