@@ -212,6 +212,23 @@ def extras(torch, dev, tf_peak, tf_burst, hbm_peak):
     return res
 
 
+def nested_block_bench(world):
+    """tools/block_bench.py under its own torchrun on `world` GPUs of this node; returns its JSON record."""
+    env = {k: v for k, v in os.environ.items()
+           if not (k.startswith('TORCHELASTIC') or k in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'LOCAL_WORLD_SIZE', 'GROUP_RANK',
+                                                         'GROUP_WORLD_SIZE', 'ROLE_RANK', 'ROLE_WORLD_SIZE', 'ROLE_NAME',
+                                                         'MASTER_ADDR', 'MASTER_PORT', 'TORCH_NCCL_ASYNC_ERROR_HANDLING'))}
+    port = int(os.environ.get('MASTER_PORT', '29500')) + 37
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', f'--nproc-per-node={world}', '--master-addr', '127.0.0.1',
+           '--master-port', str(port), os.path.join(ROOT, 'tools', 'block_bench.py'), 'gptq', 'awq']
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    except subprocess.TimeoutExpired:
+        return {'error': 'timeout'}
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith('{')]
+    return json.loads(lines[-1]) if r.returncode == 0 and lines else {'error': (r.stderr or r.stdout)[-400:]}
+
+
 def hbm_extras(torch, dev, hbm_peak):
     """The other HBM-bound call sites of the path at the reference's own call sizes, through the reference API, one call
     per tensor. Inputs rotate through a pool larger than the 126 MB L2 and every output stays alive until the clock
@@ -587,11 +604,17 @@ def main():
         out['sharded'] = sharded_extras(torch, dist, dev, world, rank)
     if rank == 0 and world == 1 and not args.no_cpu_baseline and not args.sharded_only:
         out['cpu_baseline'] = cpu_baseline()[0]
-    if rank == 0:
-        print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+        if rank == 0 and not args.no_extras:
+            # END-TO-END s / block at N ranks (GPTQ: calibration samples sharded, one all-reduce of the packed Hessian per
+            # distinct input; AWQ: candidate x row-tile units and AutoClip channels sharded), as a job of its own on the
+            # same N GPUs: this rank launches it after the group is gone, the other ranks have left
+            torch.cuda.empty_cache()
+            out['sharded']['calib_e2e'] = nested_block_bench(world)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
 
 
 if __name__ == '__main__':

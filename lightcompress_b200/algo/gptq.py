@@ -135,6 +135,15 @@ class GPTQLayer(object):
         tmp, losses, scales, zeros = ops.gptq_weight_transform(
             W, Hinv, self.blocksize, gs, qmin, qmax, wq.sym, wq.round_zp, static_scales=static_scales,
             static_zeros=static_zeros, col_group=col_group)
+        rank, world = lcdist.world()
+        if world > 1:
+            # every rank factorises the same all-reduced H, but split-K partial sums land in L2 in a different order on
+            # every GPU (fp32 reduce-adds, ~1e-7 apart), and GPTQ's error feedback turns that into other grid points:
+            # rank 0's solution is the one every rank keeps (the reference's ranks agree because cuSOLVER is deterministic)
+            import torch.distributed as dist
+            for t in (tmp, scales, zeros):          # `losses` is per-rank bookkeeping
+                if t is not None:
+                    dist.broadcast(t, src=0)
         self.losses = losses
         self.scales, self.zeros = scales, zeros
         if self.actorder:

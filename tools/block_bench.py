@@ -2,6 +2,12 @@
 Llama-3-8B dimensions (hidden 4096, inter 14336, 32 heads / 8 KV heads) — BASELINE.json's "GPTQ/AWQ calib s/block".
 
     python tools/block_bench.py [gptq] [awq] [--samples N]
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/block_bench.py [gptq] [awq]
+
+Under torchrun (SURVEY 8e): GPTQ shards the calibration samples `rank::world` like the reference's loader
+(base_dataset.py:169-172) — every rank forwards its own samples, ONE all-reduce of the packed Hessian per distinct input,
+the factorisation and the column update are replicated; AWQ gives every rank the same batch and shards the (candidate, row
+tile) units and AutoClip's output channels. Reported time = max over ranks; every rank ends with identical weights (checked).
 
 GPTQ: 128 samples x 2048 tokens, w4a16 g128, actorder + true_sequential + quant_out — the shipped recipe verbatim
       (configs/quantization/methods/GPTQ/gptq_w_only.yml:25-38).
@@ -42,6 +48,8 @@ def run(method, dev, samples, seq, special, quant_out=False, bs=1):
     g = torch.Generator().manual_seed(1)
     bs = samples if bs == -1 else bs
     data = [{'input_ids': torch.randint(0, 1024, (bs, seq), generator=g).to(dev)} for _ in range(samples // bs)]
+    if WORLD > 1 and len(data) >= WORLD:
+        data = data[RANK::WORLD]         # token-sharded calibration (GPTQ); a single batch (AWQ) stays whole on every rank
     ad = algo.adapters.LlamaAdapter(model)
     inp = ad.collect_first_block_input(data)
     a = algo.ALGO_REGISTRY[method](ad, {'weight': dict(W4), 'special': special, 'quant_out': quant_out}, inp, None,
@@ -51,10 +59,15 @@ def run(method, dev, samples, seq, special, quant_out=False, bs=1):
 
     def timed_block_opt(block):
         torch.cuda.synchronize()
+        if WORLD > 1:
+            torch.distributed.barrier()
         t0 = time.perf_counter()
         opt(block)
         torch.cuda.synchronize()
-        times.append(time.perf_counter() - t0)
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if WORLD > 1:
+            torch.distributed.all_reduce(dt, op=torch.distributed.ReduceOp.MAX)
+        times.append(float(dt.item()))
     a.block_opt = timed_block_opt
     torch.cuda.reset_peak_memory_stats()
     a.run_block_loop()
@@ -64,14 +77,30 @@ def run(method, dev, samples, seq, special, quant_out=False, bs=1):
                    'cudaMalloc_calls': int(st.get('num_device_alloc', 0)), 'alloc_retries': int(st.get('num_alloc_retries', 0))}
     w = model.model.layers[-1].mlp.down_proj.weight
     assert torch.isfinite(w.float()).all()
+    if WORLD > 1:                        # every rank must hold the same calibrated weights
+        chk = torch.stack([p.float().abs().sum() for p in model.model.layers[-1].parameters()])
+        lo, hi = chk.clone(), chk.clone()
+        torch.distributed.all_reduce(lo, op=torch.distributed.ReduceOp.MIN)
+        torch.distributed.all_reduce(hi, op=torch.distributed.ReduceOp.MAX)
+        assert torch.equal(lo, hi), 'ranks ended with different weights'
     del a, ad, model, data, inp
     torch.cuda.empty_cache()
     return times
 
 
+RANK, WORLD = 0, 1
+
+
 def main(argv=None, emit=True):
+    global RANK, WORLD
     argv = sys.argv[1:] if argv is None else argv
-    dev = torch.device('cuda:0')
+    WORLD = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    dev = torch.device(f'cuda:{local}')
+    torch.cuda.set_device(dev)
+    if WORLD > 1 and not torch.distributed.is_initialized():
+        torch.distributed.init_process_group('nccl', device_id=dev)
+    RANK = torch.distributed.get_rank() if WORLD > 1 else 0
     samples = int(argv[argv.index('--samples') + 1]) if '--samples' in argv else 128
     which = [a for a in argv if a in ('gptq', 'awq')] or ['gptq', 'awq']
     res = {}
@@ -89,8 +118,12 @@ def main(argv=None, emit=True):
         res['awq_s_per_block'], res['awq_s_first_block'] = t[-1], t[0]
         res['awq_memory'] = MEM.get('Awq')
         res['awq_config'] = f'{samples} x 512 tokens (one batch, bs -1), w4a16 g128, trans v2 + AutoClip'
-    if emit:
+    res['n_gpus'] = WORLD
+    if emit and RANK == 0:
         print(json.dumps(res), flush=True)
+    if WORLD > 1 and emit:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
     return res
 
 
