@@ -167,6 +167,25 @@ int lcb_fakequant_block_fp8_multi(const void* const* ins, void* const* outs, voi
                                   const int64_t* cols, int32_t n, const lcb_quant_spec* spec, void* stream);
 
 /*
+ * FloatQuantizer WITHOUT qtorch (`use_qtorch` unset: configs/quantization/methods/FP_Quant/rtn_we4m3ae4m3.yml and
+ * friends): per-ELEMENT scales. Replaces FloatQuantizer.get_float_qparams (quant.py:1005-1027) + quant / dequant
+ * (quant.py:1061-1076) for the 1-D granularities (per_channel / per_token / per_group / per_head):
+ *   maxval = max(max, -min) of the unit;  bias = 2^e - log2(maxval) + log2(2 - 2^-m) - 1;
+ *   xc = clamp(x, -maxval, maxval);  s = 2 ** (clamp(floor(log2|xc| + bias), min = 1) - m - bias);  s[s == 0] = 1;
+ *   y = (round(xc / s + 0) - 0) * s
+ * with one rounding to the tensor dtype after every op (e_bits < 5) or an fp32 chain and one final cast (e_bits >= 5,
+ * quant.py:1016-1017; f32 tensors). in: [n_units, unit_size] contiguous in `dtype`. out (fake-quantized, `dtype`),
+ * xc_out and scales_out (what get_tensor_qparams returns: `dtype` when e_bits < 5, f32 otherwise) may each be NULL.
+ * An all-zero unit yields NaN like the reference (log2(0) + inf).
+ * lcb_floatquant_elem_static: y = (round(x / s + 0) - 0) * s with caller-provided per-element scales
+ * (fake_quant_*_static with the scales of get_tensor_qparams, quant.py:1083-1140); scales_dtype = dtype or LCB_F32.
+ */
+int lcb_floatquant_elem(const void* in, void* out, void* xc_out, void* scales_out, int64_t n_units, int64_t unit_size,
+                        int32_t e_bits, int32_t m_bits, int32_t dtype, void* stream);
+int lcb_floatquant_elem_static(const void* in, const void* scales, void* out, int64_t n, int32_t dtype, int32_t scales_dtype,
+                               void* stream);
+
+/*
  * Block-wise FP8 dequantisation y = x_fp8 * s[block] -> bf16/f16/f32
  * Replaces weight_cast_to_bf16 (quant.py:18-31, kernel.py:86-138).
  */

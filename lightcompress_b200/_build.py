@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, 'csrc')
 LIBDIR = os.path.join(HERE, '_lib')
 LIB = os.path.join(LIBDIR, 'liblcb200.so')
 SOURCES = ['abi.cu', 'fakequant.cu', 'misc.cu', 'tc_gemm.cu', 'hessian.cu', 'gptq.cu', 'awq.cu', 'cholinv.cu', 'autoclip.cu', 'pack.cu',
-           'mse_range.cu', 'fp8_infer.cu']
+           'mse_range.cu', 'fp8_infer.cu', 'floatq.cu']
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
     '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr',

@@ -850,12 +850,17 @@ class IntegerQuantizer(BaseQuantizer):
 
 
 class FloatQuantizer(BaseQuantizer):
-    """Mirror of quant.py:963-1229 for the scale-based (`use_qtorch: True`) FP8 formats.
+    """Mirror of quant.py:963-1229.
 
-    Rounding is fp32 -> fp8 round-to-nearest-even (the rounding of `Tensor.to(torch.float8_*)`, which ends
-    every reference real-quant call, quant.py:1183/1211, and of the reference's own Triton path,
-    kernel.py:8-83). qtorch itself is an un-vendored dependency: parity unpinned for its tie rule, see
+    `use_qtorch: True` (scale-based FP8, e4m3 / e5m2): rounding is fp32 -> fp8 round-to-nearest-even (the rounding of
+    `Tensor.to(torch.float8_*)`, which ends every reference real-quant call, quant.py:1183/1211, and of the reference's
+    own Triton path, kernel.py:8-83). qtorch itself is an un-vendored dependency: parity unpinned for its tie rule, see
     DESIGN.md.
+
+    `use_qtorch` unset (configs/quantization/methods/FP_Quant/rtn_we4m3ae4m3.yml ...): per-ELEMENT scales from
+    get_float_qparams (quant.py:1005-1027), any eXmY format, 1-D granularities — csrc/floatq.cu, pinned bit-exactly to the
+    unmodified reference on the GPU box (tests/test_floatq_gpu.py). Real quant has no meaning there (one scale per
+    element) and raises.
     """
 
     def __init__(self, bit, symmetric, granularity, **kwargs):
@@ -869,11 +874,11 @@ class FloatQuantizer(BaseQuantizer):
         self.default_bias = 2 ** (self.e_bits - 1)
         self.dst_nbins = 2 ** self.num_bits
         self.use_qtorch = kwargs.get('use_qtorch')
-        if self.bit not in ('e4m3', 'e5m2'):
-            raise NotImplementedError('Only FP8 E4M3 / E5M2 are on the CUDA hot path')
         if not self.use_qtorch:
-            raise NotImplementedError('per-element power-of-two float scales (use_qtorch unset, '
-                                      'quant.py:1005-1027) are not on the CUDA hot path')
+            self.qmin = self.qmax = None      # the reference never sets them on this path
+            return
+        if self.bit not in ('e4m3', 'e5m2'):
+            raise NotImplementedError('use_qtorch: only FP8 E4M3 / E5M2 are on the CUDA hot path')
         if 'float_range' in kwargs:
             self.qmin, self.qmax = kwargs['float_range']
         else:
@@ -882,18 +887,111 @@ class FloatQuantizer(BaseQuantizer):
         self.qmax = torch.tensor(self.qmax)
         self.qmin = torch.tensor(self.qmin)
 
+    # ---- use_qtorch unset: per-element scales (quant.py:1005-1027, 1061-1076) -------------------------------------------
+    def _elem_units(self, tensor):
+        """(n_units, unit_size) of the 1-D granularities; what the reference cannot run raises the same way."""
+        if self.calib_algo not in ('minmax',):
+            raise NotImplementedError(f'FloatQuantizer without qtorch: calib_algo={self.calib_algo!r} is not on the CUDA hot path')
+        if self.granularity == 'per_tensor':
+            raise IndexError('tuple index out of range')     # quant.py:1013: maxval.shape[0] of a 0-dim tensor
+        if self.granularity == 'per_block':
+            raise NotImplementedError('FloatQuantizer without qtorch: per_block is not on the CUDA hot path')
+        u = self._units(tensor)
+        return u.n_units, u.uc
+
+    def _elem_dynamic(self, tensor, want_out, want_qparams):
+        _require_cuda(tensor, 'FloatQuantizer (per-element scales)')
+        if tensor.dtype not in _DT:
+            raise NotImplementedError(f'dtype {tensor.dtype}')
+        x = tensor.contiguous()
+        n_units, unit = self._elem_units(x)
+        qdt = torch.float32 if (self.e_bits >= 5 or x.dtype == torch.float32) else x.dtype
+        out = torch.empty_like(x) if want_out else None
+        xc = torch.empty(x.shape, dtype=qdt, device=x.device) if want_qparams else None
+        sc = torch.empty(x.shape, dtype=qdt, device=x.device) if want_qparams else None
+        lib = _cabi._lib or _cabi.load()
+        with _on_device(x.device):
+            st = lib.lcb_floatquant_elem(x.data_ptr(), out.data_ptr() if want_out else None,
+                                         xc.data_ptr() if want_qparams else None, sc.data_ptr() if want_qparams else None,
+                                         n_units, unit, self.e_bits, self.m_bits, _DT[x.dtype], _stream(x.device.index))
+        _cabi.check(st, 'lcb_floatquant_elem')
+        return out, xc, sc
+
+    def _elem_static(self, tensor, scales):
+        """(round(x / s + 0) - 0) * s with per-element scales (the `scales[scales == 0] = 1` of quant.py:1062 is applied
+        to the caller's tensor too, as the reference does)."""
+        _require_cuda(tensor, 'FloatQuantizer (per-element scales)')
+        x = tensor.contiguous()
+        if not torch.is_tensor(scales) or scales.numel() != x.numel():
+            raise ValueError(f'per-element scales hold {getattr(scales, "numel", lambda: 1)()} values, tensor has {x.numel()}')
+        scales[scales == 0] = 1
+        sc = scales.contiguous()
+        if sc.dtype != x.dtype and sc.dtype != torch.float32:
+            sc = sc.float()
+        out = torch.empty_like(x)
+        lib = _cabi._lib or _cabi.load()
+        with _on_device(x.device):
+            st = lib.lcb_floatquant_elem_static(x.data_ptr(), sc.data_ptr(), out.data_ptr(), x.numel(), _DT[x.dtype],
+                                                _DT[sc.dtype], _stream(x.device.index))
+        _cabi.check(st, 'lcb_floatquant_elem_static')
+        return out
+
+    def get_float_qparams(self, tensor, tensor_range=None, device=None):
+        """quant.py:1005-1027 -> (xc, scales) for a tensor in its reshape_tensor() layout (the range is recomputed: it
+        is the min / max of that layout's rows)."""
+        _, xc, sc = self._elem_dynamic(tensor, False, True)
+        return xc, sc
+
+    def get_tensor_qparams(self, tensor, args={}):
+        if self.use_qtorch:
+            return super().get_tensor_qparams(tensor, args)
+        t = self.reshape_tensor(tensor)
+        xc, sc = self.get_float_qparams(t)
+        return xc, sc, torch.tensor(0), None, None
+
+    def quant_dequant(self, tensor, scales, zeros, qmax, qmin):
+        if self.use_qtorch:
+            return super().quant_dequant(tensor, scales, zeros, qmax, qmin)
+        out = self._elem_static(tensor.to(scales.dtype) if scales.dtype == torch.float32 and tensor.dtype != torch.float32
+                                else tensor, scales)
+        return out
+
+    def _fake_dynamic(self, tensor, args, is_weight):
+        if self.use_qtorch:
+            return super()._fake_dynamic(tensor, args, is_weight)
+        t = tensor.T if (is_weight and 'dim' in args and 'ic' in args['dim']) else tensor
+        q, _, _ = self._elem_dynamic(t, True, False)
+        return q.T if t is not tensor else q
+
+    def _fake_static(self, tensor, args, is_weight):
+        if self.use_qtorch:
+            return super()._fake_static(tensor, args, is_weight)
+        if 'rounding' in args:
+            raise NotImplementedError("args['rounding'] (AdaRound-style floor+offset) is not on the CUDA hot path")
+        t = tensor.T if (is_weight and 'dim' in args and 'ic' in args['dim']) else tensor
+        q = self._elem_static(t, args['scales'])
+        return q.T if t is not tensor else q
+
     def _kind(self):
         return _cabi.KIND_FP8_E4M3 if self.e_bits == 4 else _cabi.KIND_FP8_E5M2
 
     def _fp8_dtype(self):
         return torch.float8_e4m3fn if self.e_bits == 4 else torch.float8_e5m2
 
-    def quant_dequant(self, tensor, scales, zeros, qmax, qmin):
-        return super().quant_dequant(tensor, scales, zeros, qmax, qmin)
+    def _no_real_quant(self):
+        if not self.use_qtorch:
+            raise NotImplementedError('FloatQuantizer without qtorch has one scale per ELEMENT (quant.py:1005-1027): '
+                                      'real quant is not defined on the CUDA hot path')
+
+    def fake_quant_weights_dynamic(self, weights):
+        if not self.use_qtorch:
+            return [self.fake_quant_weight_dynamic(w) for w in weights]
+        return super().fake_quant_weights_dynamic(weights)
 
     def real_quant_weight_dynamic(self, weight, args={}):
         """quant.py:1195-1221 → (fp8 codes, scales, None)."""
         assert self.bit in ['e4m3', 'e5m2'], 'Only FP8 E4M3 and E5M2 support real quant'
+        self._no_real_quant()
         osf = 1
         if 'output_scale_factor' in args:
             osf = args['output_scale_factor']
@@ -906,6 +1004,7 @@ class FloatQuantizer(BaseQuantizer):
         """Extension (not in the reference API): real_quant_weight_dynamic of a list of weights — FP8 per_block weights go
         64 per launch (the expert matrices of a MoE block); anything else loops. Same results as the per-tensor calls."""
         ws = list(weights)
+        self._no_real_quant()
         if self.bit in ['e4m3', 'e5m2'] and self._block_fp8_multi_ok(ws):
             res = self._block_fp8_multi(ws, _cabi.OUT_FP8)
             if res is not None:
@@ -915,6 +1014,7 @@ class FloatQuantizer(BaseQuantizer):
     def real_quant_weight_static(self, weight, args):
         """quant.py:1161-1193."""
         assert self.bit in ['e4m3', 'e5m2'], 'Only FP8 E4M3 and E5M2 support real quant'
+        self._no_real_quant()
         osf = 1
         if 'output_scale_factor' in args:
             osf = args['output_scale_factor']

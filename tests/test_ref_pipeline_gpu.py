@@ -183,6 +183,21 @@ def test_rtn_bit_exact_vs_reference_pipeline(wcfg):
     assert lp['ref'] == lp['got']
 
 
+@pytest.mark.parametrize('bit', ['e4m3', 'e5m2'])
+def test_rtn_float_quant_without_qtorch_vs_reference_pipeline(bit):
+    """configs/quantization/methods/FP_Quant/rtn_we4m3ae4m3.yml / rtn_we5m2ae5m2.yml verbatim: FloatQuantizer without
+    qtorch (per-element scales, quant.py:1005-1027) for per_channel weights and per_token activations — csrc/floatq.cu."""
+    model = tiny_llama(seed=4)
+    q = {'method': 'RTN',
+         'weight': {'quant_type': 'float-quant', 'bit': bit, 'symmetric': True, 'granularity': 'per_channel'},
+         'act': {'quant_type': 'float-quant', 'bit': bit, 'symmetric': True, 'granularity': 'per_token'}}
+    ref, _ = run_reference(model, 'Llama', q, tokens(2, 64, 5))
+    got, _ = run_product(model, 'Llama', q, tokens(2, 64, 5))
+    same, rel, lp = compare(ref, got, model, tokens(8, 128, 6), f'RTN float-quant {bit} w+a')
+    assert min(same.values()) == 1.0
+    assert lp['ref'] == lp['got']
+
+
 # ---- GPTQ: the shipped recipe and its variants ----------------------------------------------------------------------
 GPTQ_SP = {'actorder': True, 'static_groups': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}
 
