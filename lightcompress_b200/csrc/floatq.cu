@@ -22,6 +22,8 @@
 // division, a log2f and a powf per element (~150 instructions): the kernel is bound by the FP32 / SFU pipes, not by HBM
 // (measured number in DESIGN.md), which is what the arithmetic of the reference dictates.
 #include <algorithm>
+#include <cstdlib>
+#include <type_traits>
 #include "common.cuh"
 
 namespace lcb {
@@ -152,9 +154,210 @@ __global__ void __launch_bounds__(256) floatq_static_kernel(const T* __restrict_
     TI<T>::store1(out + i, C::qdq(TI<T>::load1(in + i), TI<TS>::load1(scales + i)));
 }
 
+// ---- fast kernel: 16-bit tensors, 16-byte aligned units of <= 16384 elements, fake-quant output only ----------------------
+// Same arithmetic, fewer instructions. The element scale is a function of the unit's bias and of the INTEGER
+// ls = clamp(floor(log2|xc| + bias), 1) only, and ls <= K := ls(maxval) <= 2^e + 1: the threads of a unit build a table
+// (s_k, RN(1 / s_k)) for k = 1 .. K once per unit (K powf calls per unit instead of one per element) and the element
+// divides by Markstein's correction on the tabulated reciprocal (q0 = x r; e = fma(-s, q0, x); q = fma(e, r, q0) == RN(x / s)
+// for s in [1e-20, 1e20] and |x| in [2^-40, 1e8): tests/test_fq_math_identity.py). Whatever falls outside — a table index
+// that is not in 1 .. K (NaN, or log2f not monotone in its last bit), a scale or an element outside the window — takes the
+// literal chain for that element. The unit lives in registers between the range pass and the element pass.
+constexpr int kTabMax = 48;
+
+// floor(t) for |t| < 2^22 without the conversion pipe: rint by the 1.5 * 2^23 magic add, minus one where it rounded up
+__device__ __forceinline__ float floor_small(float t) {
+  const float r = __fsub_rn(__fadd_rn(t, 12582912.0f), 12582912.0f);
+  return r > t ? __fsub_rn(r, 1.0f) : r;
+}
+
+// One element on the fast path. Returns the fake-quantized value and sets `ok` when it is certified to be the value of the
+// literal chain; otherwise the caller recomputes the element with elem_slow. Branch-free: eight of these interleave.
+//
+// ls = clamp(floor(rd(rd(log2f(ax)) + bias)), 1) comes from MUFU.LG2 when the answer cannot depend on the last bits of the
+// logarithm: lg2.approx is within 2^-22 (absolute for results in (-1, 1), relative otherwise) of log2 and libdevice's log2f
+// within one ulp; both ends of an interval four times that wide must round to the same number (16-bit chain: the first
+// rounding is the only place the logarithm's low bits can matter; fp32 chain: the floor). Not certified: zero, subnormal,
+// inf, NaN, |x| outside [2^-40, 1e8) (the window of the division identity), an index outside the unit's table.
+template <typename T, bool F32CHAIN>
+__device__ __forceinline__ float elem_fast(float x, float maxval, float bias, float Kf, const float2* tab, bool& ok) {
+  using C = Chain<T, F32CHAIN>;
+  const float xc = C::clamp_unit(x, maxval);
+  const float ax = fabsf(xc);
+  float lp;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lp) : "f"(ax));
+  const float mg = __fmaf_rn(fabsf(lp), 9.5367431640625e-07f, 9.5367431640625e-07f);   // 2^-20 (|lp| + 1)
+  float t;
+  bool sure;
+  if (F32CHAIN) {
+    const float f_lo = floor_small(__fadd_rn(__fsub_rn(lp, mg), bias));
+    t = floor_small(__fadd_rn(__fadd_rn(lp, mg), bias));
+    sure = f_lo == t;
+  } else {
+    const float r_lo = C::rd(__fsub_rn(lp, mg)), r_hi = C::rd(__fadd_rn(lp, mg));
+    t = floor_small(C::rd(__fadd_rn(r_lo, bias)));      // |bias| <= 512 and ax normal: |t| < 2^22
+    sure = r_lo == r_hi;
+  }
+  t = fmaxf(t, 1.0f);                                   // NaN -> 1
+  const float ti = fminf(t, Kf);                        // Kf = 0 (no table for this unit): entry 0, never certified
+  // 2^-40 <= ax < 1e8 in one unsigned compare on the bit patterns (also rejects inf / NaN / zero / subnormals)
+  const bool in_window = (__float_as_uint(ax) - 0x2b800000u) < (0x4cbebc20u - 0x2b800000u);
+  ok = in_window && sure && ti == t;
+  const float2 sr = tab[(int)ti];
+  const float q0 = __fmul_rn(xc, sr.y);
+  const float er = __fmaf_rn(-sr.x, q0, xc);
+  float q = __fadd_rn(C::rd(__fmaf_rn(er, sr.y, q0)), 0.0f);          // rd(x / s) + 0  (a T-valued sum: no second rounding)
+  // |q| < 2^(m + 9): ls is the element's own exponent (or larger, when clamped to 1) and the roundings of the chain move
+  // log2(s) by a few units at most for |bias| <= 512. torch.round = magic add (half to even), the sign survives
+  // (-0.3 -> -0.0); "- 0" is the identity
+  q = copysignf(__fsub_rn(__fadd_rn(q, 12582912.0f), 12582912.0f), q);
+  return __fmul_rn(C::rd(q), sr.x);                     // the caller's pack rounds to T (the chain's last rd)
+}
+
+// what elem_fast does not certify
+template <typename T, bool F32CHAIN>
+__device__ __noinline__ float elem_slow(float x, float maxval, float bias, float m_bits, float Kf, const float2* tab) {
+  using C = Chain<T, F32CHAIN>;
+  const float xc = C::clamp_unit(x, maxval);
+  // a zero element: ls = 1, 0 / s_1 = 0, "+ 0" makes it +0 whatever its sign, 0 * s_1 = +0 for a finite scale
+  if (xc == 0.0f && Kf >= 1.0f) return 0.0f;
+  return C::qdq(xc, C::scale_of(xc, bias, m_bits));
+}
+
+template <typename T, bool F32CHAIN, int TPU, int NV>   // TPU threads per unit (8 | 32 | 256), NV 16-byte vectors per thread
+__global__ void __launch_bounds__(256) floatq_fast_kernel(FParams p) {
+  using C = Chain<T, F32CHAIN>;
+  constexpr int VEC = 8;
+  constexpr int UPB = 256 / TPU;
+  __shared__ float2 tab[UPB][kTabMax];
+  __shared__ float red_mx[8], red_mn[8];
+  const int sub = threadIdx.x / TPU, lane = threadIdx.x % TPU;
+  const float two_e = powf(2.0f, p.e_bits);
+  const float c_log = C::rd(log2f(__fsub_rn(2.0f, powf(2.0f, -p.m_bits))));
+  const int nvec = (int)(p.unit / VEC);
+  const T* in = reinterpret_cast<const T*>(p.in);
+  T* out = reinterpret_cast<T*>(p.out);
+  for (int64_t u0 = (int64_t)blockIdx.x * UPB; u0 < p.n_units; u0 += (int64_t)gridDim.x * UPB) {
+    const int64_t u = u0 + sub;
+    const bool live = u < p.n_units;
+    const uint4* row = reinterpret_cast<const uint4*>(in + u * p.unit);
+    uint4 v[NV];
+    float mx = -INFINITY, mn = INFINITY;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int j = lane + i * TPU;
+      if (live && j < nvec) {
+        v[i] = ld_stream(row + j);
+        float f[VEC];
+        TI<T>::unpack(v[i], f);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+          mx = max_nan(mx, f[k]);
+          mn = min_nan(mn, f[k]);
+        }
+      }
+    }
+#pragma unroll
+    for (int o = (TPU < 32 ? TPU : 32) / 2; o > 0; o >>= 1) {
+      mx = max_nan(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      mn = min_nan(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    }
+    if (TPU == 256) {
+      __syncthreads();   // the previous unit's table readers are done
+      if ((threadIdx.x & 31) == 0) {
+        red_mx[threadIdx.x >> 5] = mx;
+        red_mn[threadIdx.x >> 5] = mn;
+      }
+      __syncthreads();
+      mx = red_mx[0];
+      mn = red_mn[0];
+#pragma unroll
+      for (int w = 1; w < 8; ++w) {
+        mx = max_nan(mx, red_mx[w]);
+        mn = min_nan(mn, red_mn[w]);
+      }
+    } else {
+      __syncwarp();      // the previous unit's table readers are done
+    }
+    const float maxval = max_nan(mx, -mn);
+    const float bias = C::bias_of(maxval, two_e, c_log);
+    // K = ls(maxval): the largest table index an element of this unit can ask for
+    float tk = floorf(C::rd(__fadd_rn(C::rd(log2f(maxval)), bias)));
+    tk = (tk != tk) ? tk : fmaxf(tk, 1.0f);
+    // 0: no table (NaN / inf / implausible bias): literal chain
+    int K = (live && tk >= 1.0f && tk < (float)kTabMax && fabsf(bias) <= 512.0f) ? (int)tk : 0;
+    bool all_ok = true;
+    for (int k = lane; k <= K; k += TPU) {                 // entry 0: a harmless stand-in for units without a table
+      const float e2 = C::rd(__fsub_rn(C::rd(__fsub_rn((float)k, p.m_bits)), bias));
+      float sk = k == 0 ? 1.0f : C::rd(powf(2.0f, e2));
+      if (sk == 0.0f) sk = 1.0f;
+      all_ok = all_ok && sk >= 1e-20f && sk <= 1e20f;      // the window of the division identity
+      tab[sub][k] = make_float2(sk, __frcp_rn(sk));
+    }
+    // one scale outside the window: the whole unit takes the literal chain (K = 0)
+    if (TPU == 256) {
+      if (!__syncthreads_and(all_ok)) K = 0;
+    } else {
+      unsigned bad = __ballot_sync(0xffffffffu, !all_ok);
+      if (TPU < 32) bad &= ((1u << TPU) - 1u) << ((threadIdx.x & 31) / TPU * TPU);
+      if (bad) K = 0;
+      __syncwarp();
+    }
+    if (!live) continue;
+    const float Kf = (float)K;
+    uint4* orow = reinterpret_cast<uint4*>(out + u * p.unit);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int j = lane + i * TPU;
+      if (j < nvec) {
+        float f[VEC];
+        TI<T>::unpack(v[i], f);
+        float y[VEC];
+        unsigned redo = 0;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+          bool ok;
+          y[k] = elem_fast<T, F32CHAIN>(f[k], maxval, bias, Kf, tab[sub], ok);
+          redo |= ok ? 0u : (1u << k);
+        }
+        if (redo) {
+#pragma unroll
+          for (int k = 0; k < VEC; ++k)
+            if (redo & (1u << k)) y[k] = elem_slow<T, F32CHAIN>(f[k], maxval, bias, p.m_bits, Kf, tab[sub]);
+        }
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) f[k] = y[k];
+        st_stream(orow + j, TI<T>::pack(f));
+      }
+    }
+  }
+}
+
+template <typename T, bool F32CHAIN>
+bool launch_fast(const FParams& p, cudaStream_t st) {
+  if (p.xc_out || p.s_out || !p.out || p.unit % 8 || p.unit > 16384) return false;
+  if ((reinterpret_cast<uintptr_t>(p.in) | reinterpret_cast<uintptr_t>(p.out)) & 15) return false;
+  const int nvec = (int)(p.unit / 8);
+  auto grid = [&](int upb) { return (int)std::min<int64_t>((p.n_units + upb - 1) / upb, (int64_t)kNumSMs * 16); };
+  if (nvec <= 8) floatq_fast_kernel<T, F32CHAIN, 8, 1><<<grid(32), 256, 0, st>>>(p);
+  else if (nvec <= 32) floatq_fast_kernel<T, F32CHAIN, 32, 1><<<grid(8), 256, 0, st>>>(p);
+  else if (nvec <= 64) floatq_fast_kernel<T, F32CHAIN, 32, 2><<<grid(8), 256, 0, st>>>(p);
+  else if (nvec <= 128) floatq_fast_kernel<T, F32CHAIN, 32, 4><<<grid(8), 256, 0, st>>>(p);
+  else if (nvec <= 512) floatq_fast_kernel<T, F32CHAIN, 256, 2><<<grid(1), 256, 0, st>>>(p);
+  else if (nvec <= 1024) floatq_fast_kernel<T, F32CHAIN, 256, 4><<<grid(1), 256, 0, st>>>(p);
+  else floatq_fast_kernel<T, F32CHAIN, 256, 8><<<grid(1), 256, 0, st>>>(p);
+  return true;
+}
+
 template <typename T>
 int launch_dynamic(const FParams& p, bool f32chain, cudaStream_t st) {
   const int64_t unit = p.unit;
+  if (sizeof(T) == 2 && !getenv("LCB_FLOATQ_LITERAL")) {
+    using T16 = typename std::conditional<sizeof(T) == 2, T, __nv_bfloat16>::type;
+    if (f32chain ? launch_fast<T16, true>(p, st) : launch_fast<T16, false>(p, st)) {
+      LCB_CUDA_CHECK_LAUNCH("floatq_fast");
+      return LCB_OK;
+    }
+  }
   auto grid = [&](int upb) { return (int)std::min<int64_t>((p.n_units + upb - 1) / upb, (int64_t)kNumSMs * 8); };
 #define LCB_FQ_LAUNCH(F32, L, UPB) floatq_dynamic_kernel<T, F32, L><<<grid(UPB), 256, 0, st>>>(p)
   if (f32chain) {
