@@ -212,6 +212,20 @@ int lcb_act_quant_fp8(const void* x, void* y, float* scales, int64_t n_groups, i
  */
 int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias, int64_t M,
                  int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* stream);
+/*
+ * The same GEMM with a caller workspace of lcb_fp8_gemm_workspace_bytes(M, N, K) bytes (0: no workspace needed, NULL is
+ * fine), 16-byte aligned, which MUST BE ZERO-FILLED before its first use and is LEFT ZERO-FILLED by every call (so one
+ * zeroed buffer serves any number of calls that are ordered on a stream; calls that overlap on the GPU need their own).
+ * With few output tiles (decode shapes: M <= 128 rows leave N / 256 CTAs for 148 SMs, and the call is bound by streaming
+ * the weight) the K blocks of a tile are split over the idle SMs; every slice adds its fp32 partial tile into the
+ * workspace (16-byte L2 reductions), the slice that arrives last reads the sums back, rounds to out_dtype, adds the bias,
+ * stores the tile and clears sums and counter: ONE launch. Same contraction and promotion per K block; the fp32 sum over
+ * K blocks runs in slice order instead of block order (differences at fp32 rounding level, not deterministic between
+ * runs). No counterpart in the reference (its Triton kernel has no split-K).
+ */
+int64_t lcb_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K);
+int lcb_fp8_gemm_ws(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias, int64_t M,
+                    int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* workspace, void* stream);
 
 /*
  * GPTQ Hessian accumulation  S += X^T X   (upper 128x128 blocks of S only; SYRK)

@@ -42,6 +42,8 @@ SIGNATURES = {
     'lcb_fp8_block_dequant': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
     'lcb_act_quant_fp8': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp]),
     'lcb_fp8_gemm': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp]),
+    'lcb_fp8_gemm_ws': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_i32, _c_i32, _c_vp, _c_vp]),
+    'lcb_fp8_gemm_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i64]),
     'lcb_hessian_accum': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_vp, _c_vp]),
     'lcb_hessian_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i32]),
     'lcb_floatquant_elem': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp]),

@@ -11,6 +11,8 @@
 //   warp 1    : MMA issuer (one thread): 4 x (M = 128, N = 256, K = 32) per K block, accumulate flag cleared on the first
 //   warps 4-11: promotion + epilogue: thread = output row (TMEM lane) x 128-column half, 128 fp32 accumulators in
 //               registers (setmaxnreg: 232 for these two warpgroups, 40 for the producer / issuer warpgroup)
+#include <algorithm>
+#include <cstdlib>
 #include "tc.cuh"
 
 namespace lcb {
@@ -177,6 +179,12 @@ struct Params {
   const void* bias;   // NULL or [N]
   int bias_dtype;
   uint32_t idesc;
+  // split-K (few output tiles: M <= 128 decode shapes): tile t -> (output tile t / ksplit, K slice t % ksplit of kbs blocks);
+  // slices add their fp32 partial sums into `ws` [M, N]; the slice that arrives last reads the sums back, rounds, adds the
+  // bias, stores the tile and leaves sums and counter zero for the next call (the workspace is zero between calls)
+  int ksplit, kbs;
+  float* ws;
+  int* cnt;           // arrivals per output tile (behind the sums in the workspace); zero between calls
 };
 struct Maps {
   CUtensorMap a, b;
@@ -205,6 +213,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + NACC;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + NACC);
+  volatile int* last_flag = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
@@ -236,8 +245,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
         // consecutive CTAs share the B (weight) column block: tile index runs over row blocks fastest
-        const int ti = t % p.nblk_i, tj = t / p.nblk_i;
-        for (int kb = 0; kb < nkb; ++kb) {
+        const int to = t / p.ksplit, ks = t % p.ksplit;
+        const int ti = to % p.nblk_i, tj = to / p.nblk_i;
+        const int kb0 = ks * p.kbs, kb1 = min(nkb, kb0 + p.kbs);
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           tc::mbar_expect_tx(&full[stage], STAGE_BYTES);
@@ -256,7 +267,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
     uint32_t phase = 0, acc_phase = 0;
     const uint64_t desc_k = tc::smem_desc_sw128(0, 1024);   // K-major SWIZZLE_128B: 8-row groups 1024 B apart
     for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
-      for (int kb = 0; kb < nkb; ++kb) {
+      const int kb0 = (t % p.ksplit) * p.kbs, kb1 = min(nkb, kb0 + p.kbs);
+      for (int kb = kb0; kb < kb1; ++kb) {
         tc::mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc::mbar_wait(&full[stage], phase);
         tc::tc_fence_after();
@@ -291,16 +303,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
     uint32_t acc_phase = 0;
     float accv[EPI_COLS];
     for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
-      const int ti = t % p.nblk_i, tj = t / p.nblk_i;
+      const int to = t / p.ksplit, ks = t % p.ksplit;
+      const int ti = to % p.nblk_i, tj = to / p.nblk_i;
+      const int kb0 = ks * p.kbs, kb1 = min(nkb, kb0 + p.kbs);
       const int row = ti * BM + q * 32 + lane;
       const float* asp = p.a_s + (int64_t)min(row, p.M - 1) * nkb;
       // weight scale block of this warp's 128 columns (clamped for the half tile past the ragged edge: nothing is stored)
       const float* bsp = p.b_s + (int64_t)min((tj * BN + ch) >> 7, p.nsb - 1) * nkb;
 #pragma unroll
       for (int j = 0; j < EPI_COLS; ++j) accv[j] = 0.f;
-      float sc = __fmul_rn(asp[0], bsp[0]);
+      float sc = __fmul_rn(asp[kb0], bsp[kb0]);
 #pragma unroll 1
-      for (int kb = 0; kb < nkb; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         const int kn = min(kb + 1, nkb - 1);
         const float sc_next = __fmul_rn(__ldg(asp + kn), __ldg(bsp + kn));
         tc::mbar_wait(&tfull[acc], acc_phase);
@@ -329,6 +343,90 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
           acc_phase ^= 1;
         }
         sc = sc_next;
+      }
+      if (p.ksplit > 1) {
+        // ---- split-K: fp32 partial sums of this K slice into the workspace (L2 reductions, 16 bytes each) ----
+        const int col0 = tj * BN + ch;
+        float* wrow = p.ws + (int64_t)row * p.N + col0;
+        const bool vec_ok = (p.N % 4 == 0);
+        if (row < p.M) {
+#pragma unroll
+          for (int c = 0; c < EPI_COLS; c += 4) {
+            if (vec_ok && col0 + c + 4 <= p.N) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(wrow + c), "f"(accv[c]), "f"(accv[c + 1]),
+                           "f"(accv[c + 2]), "f"(accv[c + 3])
+                           : "memory");
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                if (col0 + c + i < p.N) atomicAdd(wrow + c + i, accv[c + i]);
+            }
+          }
+        }
+        // the slice that arrives last owns the tile (threadFenceReduction pattern: reductions, fence, barrier, one counter
+        // increment; the owner fences again and reads the sums from L2)
+        __threadfence();
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+        if (threadIdx.x == FIRST_EPI_WARP * 32) *last_flag = (atomicAdd(p.cnt + to, 1) == p.ksplit - 1) ? 1 : 0;
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+        if (*last_flag == 0) continue;
+        __threadfence();
+        // the owner's tail is a ROLLED loop over the live part of the tile, coalesced along the rows of the workspace
+        // (a second unrolled 128-accumulator block would be cold code: its instruction fetches cost more than the data):
+        // read the sums, put the zeros back, round, add the bias, store
+        {
+          const int et = threadIdx.x - FIRST_EPI_WARP * 32;
+          const int r0 = ti * BM, c0 = tj * BN;
+          const int rows = min(BM, p.M - r0), cols = min(BN, p.N - c0);
+          TO* cb = reinterpret_cast<TO*>(p.c);
+          if (vec_ok && (reinterpret_cast<uintptr_t>(p.c) & 15) == 0) {
+            const int nq = cols >> 2, total = rows * nq;
+            constexpr int U = 8, NT = EPI_WARPS * 32;       // U loads in flight per thread: the loop is L2-latency bound
+#pragma unroll 1
+            for (int base = et; base < total; base += U * NT) {
+              float4 v[U];
+              int64_t off[U];
+#pragma unroll
+              for (int u = 0; u < U; ++u) {
+                const int idx = base + u * NT;
+                const int r = idx / nq, c = (idx - r * nq) << 2;
+                off[u] = (int64_t)(r0 + r) * p.N + c0 + c;
+                if (idx < total) v[u] = __ldcg(reinterpret_cast<const float4*>(p.ws + off[u]));
+              }
+#pragma unroll
+              for (int u = 0; u < U; ++u) {
+                if (base + u * NT >= total) break;
+                __stcg(reinterpret_cast<float4*>(p.ws + off[u]), make_float4(0.f, 0.f, 0.f, 0.f));
+                float o[4] = {TI<TO>::rd(v[u].x), TI<TO>::rd(v[u].y), TI<TO>::rd(v[u].z), TI<TO>::rd(v[u].w)};
+                if (p.bias) {
+                  const int c = (int)(off[u] - (off[u] / p.N) * p.N);
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) o[i] = TI<TO>::rd(__fadd_rn(o[i], load_rt(p.bias, c + i, p.bias_dtype)));
+                }
+                if (sizeof(TO) == 4) {
+                  *reinterpret_cast<float4*>(cb + off[u]) = make_float4(o[0], o[1], o[2], o[3]);
+                } else {
+                  TO t4[4];
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) TI<TO>::store1(t4 + i, o[i]);
+                  *reinterpret_cast<uint2*>(cb + off[u]) = *reinterpret_cast<const uint2*>(t4);
+                }
+              }
+            }
+          } else {
+#pragma unroll 1
+            for (int idx = et; idx < rows * cols; idx += EPI_WARPS * 32) {
+              const int r = idx / cols, c = idx - r * cols;
+              const int64_t off = (int64_t)(r0 + r) * p.N + c0 + c;
+              float o = TI<TO>::rd(__ldcg(p.ws + off));
+              __stcg(p.ws + off, 0.f);
+              if (p.bias) o = TI<TO>::rd(__fadd_rn(o, load_rt(p.bias, c0 + c, p.bias_dtype)));
+              TI<TO>::store1(cb + off, o);
+            }
+          }
+        }
+        if (threadIdx.x == FIRST_EPI_WARP * 32) p.cnt[to] = 0;
+        continue;
       }
       // ---- store: round to the output dtype, then the bias add of block_wise_fp8_forward_func (y += bias) ----
       if (row < p.M) {
@@ -397,8 +495,52 @@ extern "C" int lcb_act_quant_fp8(const void* x, void* y, float* scales, int64_t 
   return LCB_E_UNSUPPORTED;
 }
 
+namespace lcb {
+namespace f8 {
+// K slices per output tile when the tiles alone leave most SMs idle. Model fitted on the B200 (tools/fp8_decode_bench.py,
+// profiles/r2_fp8_ksplit_sweep.txt): a call costs ~6.3 us + 0.5 us per K block of its longest CTA; a split tile adds
+// ~2.7 us + 0.065 us per live row (16-byte L2 reductions of every slice, the owner's read-back and store). One wave only:
+// slices x tiles <= SMs. LCB_FP8_KSPLIT=<n> forces n slices (experiments).
+static int pick_ksplit(int n_out_tiles, int nkb, int64_t M) {
+  if (n_out_tiles * 2 > kNumSMs || nkb < 4) return 1;
+  static const int forced = [] { const char* e = getenv("LCB_FP8_KSPLIT"); return e ? atoi(e) : 0; }();
+  int ks = forced > 0 ? forced : kNumSMs / n_out_tiles;
+  ks = std::max(1, std::min(ks, nkb / 2));
+  if (forced > 0 || ks == 1) return ks;
+  const int kbs = (nkb + ks - 1) / ks;
+  const float saving = 0.5f * (float)(nkb - kbs);
+  const float tail = 2.7f + 0.065f * (float)std::min<int64_t>(M, BM);
+  return saving > 1.2f * tail ? ks : 1;
+}
+}  // namespace f8
+}  // namespace lcb
+
+extern "C" int64_t lcb_fp8_gemm_workspace_bytes(int64_t M, int64_t N, int64_t K) {
+  using namespace lcb::f8;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  const int n_out = (int)((M + BM - 1) / BM) * (int)((N + BN - 1) / BN);
+  if (pick_ksplit(n_out, (int)((K + BKB - 1) / BKB), M) <= 1) return 0;
+  return ((M * N + 3) / 4 * 4 + (n_out + 3) / 4 * 4) * (int64_t)sizeof(float);   // fp32 sums [M, N] + one counter per tile
+}
+
+static int fp8_gemm_impl(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias,
+                         int64_t M, int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* workspace,
+                         void* stream);
+
 extern "C" int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias,
                             int64_t M, int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* stream) {
+  return fp8_gemm_impl(a, a_s, b, b_s, c, bias, M, N, K, out_dtype, bias_dtype, nullptr, stream);
+}
+
+extern "C" int lcb_fp8_gemm_ws(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias,
+                               int64_t M, int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* workspace,
+                               void* stream) {
+  return fp8_gemm_impl(a, a_s, b, b_s, c, bias, M, N, K, out_dtype, bias_dtype, workspace, stream);
+}
+
+static int fp8_gemm_impl(const void* a, const float* a_s, const void* b, const float* b_s, void* c, const void* bias,
+                         int64_t M, int64_t N, int64_t K, int32_t out_dtype, int32_t bias_dtype, void* workspace,
+                         void* stream) {
   using namespace lcb;
   using namespace lcb::f8;
   if (M == 0 || N == 0) return LCB_OK;
@@ -413,8 +555,17 @@ extern "C" int lcb_fp8_gemm(const void* a, const float* a_s, const void* b, cons
   p.K = (int)K;
   p.nblk_i = (int)((M + BM - 1) / BM);
   p.nblk_j = (int)((N + BN - 1) / BN);
-  p.n_tiles = p.nblk_i * p.nblk_j;
   p.nkb = (int)((K + BKB - 1) / BKB);
+  p.ksplit = 1;
+  if (workspace) {
+    if (reinterpret_cast<uintptr_t>(workspace) & 15) return LCB_E_ALIGN;
+    p.ksplit = pick_ksplit(p.nblk_i * p.nblk_j, p.nkb, M);
+  }
+  p.kbs = (p.nkb + p.ksplit - 1) / p.ksplit;
+  p.ksplit = (p.nkb + p.kbs - 1) / p.kbs;          // no empty slice
+  p.ws = reinterpret_cast<float*>(workspace);
+  p.cnt = workspace ? reinterpret_cast<int*>(p.ws + (M * N + 3) / 4 * 4) : nullptr;
+  p.n_tiles = p.nblk_i * p.nblk_j * p.ksplit;
   p.nsb = (int)((N + 127) / 128);
   p.a_s = a_s;
   p.b_s = b_s;

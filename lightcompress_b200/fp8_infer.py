@@ -29,6 +29,21 @@ def act_quant(x, block_size=128):
     return y.view(_F8), s
 
 
+_WS = {}
+
+
+def _zero_workspace(device, nbytes):
+    """The split-K workspace of lcb_fp8_gemm_ws: zero on entry, left zero by the call — one buffer per (device, stream)
+    serves every call ordered on that stream (calls on different streams may overlap on the GPU and get their own)."""
+    if torch.cuda.is_current_stream_capturing():     # a graph owns its buffers: zeroed by a captured memset, not cached
+        return torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = _WS[key] = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+    return ws
+
+
 def fp8_gemm(a, a_s, b, b_s, bias=None, out_dtype=None):
     """kernel.py:218-242: c[..., N] = (a * a_s) @ (b * b_s)^T with 128-deep K blocks, in torch.get_default_dtype()
     (or `out_dtype`). `bias` (not a reference argument) fuses the `y += bias` of block_wise_fp8_forward_func."""
@@ -57,10 +72,14 @@ def fp8_gemm(a, a_s, b, b_s, bias=None, out_dtype=None):
         bias = bias.contiguous()
         if bias.dtype not in _DT or bias.numel() != N:
             raise TypeError('fp8_gemm: bias must be a float tensor of N elements')
+    # few output tiles (decode shapes): split-K over the idle SMs through an fp32 workspace (lcb_fp8_gemm_ws)
+    nws = int(lib.lcb_fp8_gemm_workspace_bytes(M, N, K)) if M <= 256 else 0
+    ws = _zero_workspace(a.device, nws) if nws else None
     with _on_device(a.device):
-        st = lib.lcb_fp8_gemm(a.data_ptr(), a_s.data_ptr(), b.data_ptr(), b_s.data_ptr(), c.data_ptr(),
-                              bias.data_ptr() if bias is not None else None, M, N, K, _DT[dt],
-                              _DT[bias.dtype] if bias is not None else 0, _stream(a.device.index))
+        st = lib.lcb_fp8_gemm_ws(a.data_ptr(), a_s.data_ptr(), b.data_ptr(), b_s.data_ptr(), c.data_ptr(),
+                                 bias.data_ptr() if bias is not None else None, M, N, K, _DT[dt],
+                                 _DT[bias.dtype] if bias is not None else 0, ws.data_ptr() if ws is not None else None,
+                                 _stream(a.device.index))
     _cabi.check(st, 'lcb_fp8_gemm')
     return c
 

@@ -212,3 +212,31 @@ def test_c_abi_status_codes_surface_as_exceptions():
         fi.fp8_gemm(a, torch.ones(4, 2, device=DEV), b, torch.ones(1, 2, device=DEV), out_dtype=torch.bfloat16)
     with pytest.raises(Exception, match='lcb_act_quant_fp8'):
         fi.act_quant(torch.zeros(4, 96, device=DEV, dtype=torch.bfloat16), 48)
+
+
+@pytest.mark.parametrize('out_dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K', [(1, 2048, 7168), (16, 7168, 2048), (100, 520, 4096), (128, 4096, 4096), (7, 136, 4096)])
+def test_fp8_gemm_split_k_decode_shapes(out_dtype, M, N, K):
+    """Few output tiles: lcb_fp8_gemm_ws splits the K blocks of a tile over the idle SMs (fp32 reductions into a
+    workspace + a finishing launch). Same bar as the one-pass kernel, with and without bias, and against it."""
+    from lightcompress_b200 import _cabi
+    lib = _cabi.load()
+    assert lib.lcb_fp8_gemm_workspace_bytes(M, N, K) >= M * N * 4, 'this shape is expected to take the split-K path'
+    assert lib.lcb_fp8_gemm_workspace_bytes(4096, 4096, 4096) == 0 and lib.lcb_fp8_gemm_workspace_bytes(128, 7168, 2048) == 0
+    a, a_s, b, b_s = _gemm_case(M, N, K, M + K)
+    _check_gemm(a, a_s, b, b_s, out_dtype)
+    g = torch.Generator().manual_seed(3)
+    _check_gemm(a, a_s, b, b_s, out_dtype, bias=torch.randn(N, generator=g).to(torch.bfloat16 if out_dtype != torch.float32
+                                                                                 else torch.float32))
+    # against the one-pass entry (no workspace) on the same operands: fp32 sums in another order
+    ad, asd, bd, bsd = a.to(DEV), a_s.to(DEV), b.to(DEV), b_s.to(DEV)
+    one = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    st = lib.lcb_fp8_gemm(ad.data_ptr(), asd.data_ptr(), bd.data_ptr(), bsd.data_ptr(), one.data_ptr(), None, M, N, K, 0, 0,
+                          torch.cuda.current_stream().cuda_stream)
+    assert st == 0
+    scale = float(one.abs().max())
+    for _ in range(3):      # the workspace is left zero: back-to-back calls on one buffer agree
+        two = fi.fp8_gemm(ad, asd, bd, bsd, out_dtype=torch.float32)
+        assert float((one - two).abs().max()) <= 2e-6 * scale
+    ws = fi._zero_workspace(torch.device(DEV), 16)
+    assert int(ws.count_nonzero()) == 0, 'split-K calls must leave their workspace zero-filled'
