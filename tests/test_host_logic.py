@@ -105,3 +105,40 @@ def test_patch_fp8_inference_rebinds_only_what_a_module_defines():
     assert kernel.weight_cast_to_fp8 is fi.weight_cast_to_fp8 and kernel.fp8_gemm_configs == [1, 2]
     assert not hasattr(kernel, 'block_wise_fp8_forward_func') and not hasattr(mu, 'weight_cast_to_fp8')
     assert sorted(done['ref_module_utils']) == ['act_quant', 'block_wise_fp8_forward_func', 'fp8_gemm']
+
+
+def test_float_quantizer_without_qtorch_host_side():
+    """use_qtorch unset: any eXmY format constructs (quant.py:963-1003 sets no qmin / qmax on that path), the 1-D
+    granularities are accepted, per_tensor raises like the reference (maxval.shape[0] of a 0-dim tensor), real quant and
+    CPU tensors are refused loudly."""
+    for bit in ('e4m3', 'e5m2', 'e2m1', 'e3m2', 'e4m7'):
+        q = Q.FloatQuantizer(bit, True, 'per_channel')
+        assert q.qmin is None and q.qmax is None and q.e_bits == int(bit[1]) and q.m_bits == int(bit[-1])
+    with pytest.raises(NotImplementedError):
+        Q.FloatQuantizer('e2m1', True, 'per_channel', use_qtorch=True)        # qtorch grid formats are not on the hot path
+    q = Q.FloatQuantizer('e4m3', True, 'per_group', group_size=128)
+    assert q._elem_units(torch.zeros(4, 256)) == (8, 128)
+    assert Q.FloatQuantizer('e4m3', True, 'per_token')._elem_units(torch.zeros(2, 3, 64)) == (6, 64)
+    with pytest.raises(IndexError):
+        Q.FloatQuantizer('e4m3', True, 'per_tensor')._elem_units(torch.zeros(4, 8))
+    with pytest.raises(NotImplementedError):
+        Q.FloatQuantizer('e4m3', True, 'per_block', block_size=128)._elem_units(torch.zeros(128, 128))
+    with pytest.raises(NotImplementedError):
+        Q.FloatQuantizer('e4m3', True, 'per_channel', calib_algo='mse')._elem_units(torch.zeros(4, 8))
+    with pytest.raises(RuntimeError, match='no CPU path'):
+        Q.FloatQuantizer('e4m3', True, 'per_channel').fake_quant_weight_dynamic(torch.zeros(4, 8, dtype=torch.bfloat16))
+    with pytest.raises(NotImplementedError):
+        Q.FloatQuantizer('e4m3', True, 'per_channel').real_quant_weight_dynamic(torch.zeros(4, 8, dtype=torch.bfloat16))
+
+
+def test_fp8_gemm_split_k_plan_is_a_host_function():
+    """lcb_fp8_gemm_workspace_bytes is the split-K decision (a fitted cost model, no device call): decode shapes with a long
+    K get a workspace (fp32 sums + one counter per tile, 16-byte multiples), prefill shapes and short K do not."""
+    from lightcompress_b200 import _cabi
+    lib = _cabi.load()
+    f = lib.lcb_fp8_gemm_workspace_bytes
+    assert f(16, 2048, 7168) == (16 * 2048 + 8) * 4          # 8 output tiles
+    assert f(1, 1536, 7168) == (1536 + 8) * 4                # 6 tiles: counters padded to 8
+    assert f(128, 7168, 2048) == 0 and f(64, 24576, 1536) == 0 and f(4096, 4096, 4096) == 0 and f(16, 2048, 256) == 0
+    assert f(0, 128, 128) == 0
+    assert f(128, 2048, 7168) > 0 and f(128, 4096, 4096) > 0
