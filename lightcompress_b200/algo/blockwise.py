@@ -81,6 +81,14 @@ class _ChildCache(object):
         return sum(v for k, v in self.bytes.items() if '.' in k) > self.budget
 
 
+class _ChunkedList(list):
+    """The per-sample tensors of a calibration pass (what `self.input['data']` holds) together with the chunk tensors they
+    are views of: a later pass over the same data feeds the chunks to the block directly instead of concatenating
+    `forward_batch` samples again (32 `torch.cat` of 268 MB per Llama-3-8B block: 14 ms of device time)."""
+    chunks = None     # list of [B, T, C] tensors; sample i is chunks[i // B][i % B : i % B + 1]
+    B = 0
+
+
 class _StopForward(Exception):
     """Raised by the re-hook pre-hooks once every layer of the next subset has seen its input: the rest of the block
     forward (whose output nobody reads, base_bq.py:505-526) is not computed."""
@@ -167,6 +175,17 @@ class BaseBlockwiseQuantization(object):
                     kw[k] = tuple(t.to(dev) if torch.is_tensor(t) else t for t in v)
         if self.graph_safe_hooks and dev.type == 'cuda' and len(data) >= 2 and self._uniform_samples(data, dev):
             if self.forward_batch > 1:
+                if input_data is None and not isinstance(data, _ChunkedList):
+                    # the first block's inputs arrive as separate samples: concatenate the chunks ONCE for all its passes
+                    B = self.forward_batch
+                    cl = _ChunkedList()
+                    cl.chunks, cl.B = [], B
+                    for i in range(0, len(data), B):
+                        part = data[i:i + B]
+                        x = part[0] if len(part) == 1 else torch.cat(part, 0)
+                        cl.chunks.append(x)
+                        cl.extend(x.split([p.shape[0] for p in part], 0))
+                    data = self.input['data'] = cl
                 return self._block_forward_batched(block, data, may_stop)
             if self.use_graph and len(data) >= 4:
                 return self._block_forward_graph(block, data, may_stop)
@@ -272,10 +291,15 @@ class BaseBlockwiseQuantization(object):
                     continue
                 handles.append(mod.register_forward_pre_hook(functools.partial(pre, name=name)))
                 handles.append(mod.register_forward_hook(functools.partial(post, name=name)))
+        chunks = data.chunks if isinstance(data, _ChunkedList) and data.B == B and data.chunks is not None else None
+        y_chunks = []
         try:
             for ci, i in enumerate(range(0, len(data), B)):
                 part = data[i:i + B]
-                x = part[0] if len(part) == 1 else torch.cat(part, 0)
+                if chunks is not None:
+                    x = chunks[ci]
+                else:
+                    x = part[0] if len(part) == 1 else torch.cat(part, 0)
                 state['chunk'] = ci
                 if cache is not None:
                     cache.calls = {}
@@ -287,6 +311,7 @@ class BaseBlockwiseQuantization(object):
                     continue
                 y = y[0] if isinstance(y, tuple) else y
                 out.extend(y.split([p.shape[0] for p in part], 0))
+                y_chunks.append(y)
         finally:
             for h in handles:
                 h.remove()
@@ -296,6 +321,10 @@ class BaseBlockwiseQuantization(object):
                 cache.deep = False             # too much memory kept alive: keep only the block's direct children
                 for name in [k for k in cache.out if '.' in k]:
                     cache.drop(name)
+        if len(y_chunks) == n_chunks and len(out) == len(data):   # a complete pass: its outputs remember their chunks
+            res = _ChunkedList(out)
+            res.chunks, res.B = y_chunks, B
+            return res
         return out
 
     def _block_forward_graph(self, block, data, may_stop):
