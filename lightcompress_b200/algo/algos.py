@@ -66,6 +66,9 @@ class GPTQ(BaseBlockwiseQuantization):
 
     graph_safe_hooks = True   # the hook launches one kernel into a persistent buffer and keeps no tensor
 
+    def needs_input(self, name):   # only the owner of a shared Hessian accumulates (cache_input_hook below)
+        return name in self.layers_cache and self.hessian_owner.get(name, True)
+
     def cache_input_hook(self, m, x, y, name, feat_dict):   # gptq.py:247-251: accumulate, do not keep the input
         if name in self.layers_cache and self.hessian_owner.get(name, True):
             if self._capturing:   # block_forward is recording a CUDA graph: the batch is counted once per replay
