@@ -89,6 +89,56 @@ class _ChunkedList(list):
     B = 0
 
 
+class _BlockPrefetcher(object):
+    """Copies the next block's parameters and buffers to the device on a side stream from a worker thread while the
+    current block is calibrated (base_bq.py:397 does the same copy synchronously at the block's turn)."""
+
+    def __init__(self, dev):
+        import threading
+        self.dev = dev
+        self.stream = torch.cuda.Stream(device=dev)
+        self.thread = None
+        self.block = None
+        self.error = None
+        self._threading = threading
+
+    @staticmethod
+    def on_device(block, dev):
+        return all(t.device.type == dev.type for t in list(block.parameters()) + list(block.buffers()))
+
+    def start(self, block):
+        if self.on_device(block, self.dev):
+            return
+        self.block, self.error = block, None
+
+        def work():
+            try:
+                with torch.cuda.device(self.stream.device), torch.cuda.stream(self.stream):
+                    block.to(self.dev)
+            except BaseException as e:     # noqa: BLE001  (re-raised on the calling thread by wait())
+                self.error = e
+        self.thread = self._threading.Thread(target=work, name='lcb-block-prefetch', daemon=True)
+        self.thread.start()
+
+    def wait(self, block):
+        if self.thread is None or self.block is not block:
+            return
+        self.thread.join()
+        self.thread = self.block = None
+        if self.error is not None:
+            raise self.error
+        main = torch.cuda.current_stream(self.stream.device)
+        main.wait_stream(self.stream)
+        for t in list(block.parameters()) + list(block.buffers()):
+            if t.is_cuda:
+                t.data.record_stream(main)    # allocated on the side stream, used (and one day freed) under the main one
+
+    def close(self):
+        if self.thread is not None:
+            self.thread.join()
+            self.thread = self.block = None
+
+
 class _StopForward(Exception):
     """Raised by the re-hook pre-hooks once every layer of the next subset has seen its input: the rest of the block
     forward (whose output nobody reads, base_bq.py:505-526) is not computed."""
@@ -159,9 +209,24 @@ class BaseBlockwiseQuantization(object):
 
     # ---- block loop (blockwise_optimization.py:31-51, base_bq.py:367-452) ----------------------------------------------
     def run_block_loop(self):
-        for i, block in enumerate(self.blocks):
-            self.block_idx = i
-            self.block_opt(block)
+        """blockwise_optimization.py:31-51. The reference moves a block to the GPU when its turn comes (base_bq.py:397) and
+        back afterwards (:418); here the weights stay on the device once they are there (180 GB of HBM3e), and while block i
+        is calibrated block i + 1 is copied in by a worker thread on a side stream (`special.prefetch_blocks`, default on; a
+        host-to-device copy from pageable memory blocks its calling thread, hence the thread). A block that already lives on
+        the device costs nothing."""
+        blocks = list(self.blocks)
+        pre = _BlockPrefetcher(self.dev) if self.special.get('prefetch_blocks', True) and self.dev.type == 'cuda' else None
+        try:
+            for i, block in enumerate(blocks):
+                self.block_idx = i
+                if pre is not None:
+                    pre.wait(block)                       # no-op unless a copy of this block is in flight
+                    if i + 1 < len(blocks):
+                        pre.start(blocks[i + 1])
+                self.block_opt(block)
+        finally:
+            if pre is not None:
+                pre.close()
 
     @torch.no_grad()
     def block_forward(self, block, input_data=None, may_stop=False):

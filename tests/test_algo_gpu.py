@@ -281,3 +281,40 @@ def test_child_output_reuse_changes_nothing():
     for mode in (True, 'direct', 'budget0'):     # every level / the block's direct children only / memory budget exceeded
         assert torch.equal(outs[mode][0], outs[False][0]), mode
         assert torch.equal(outs[mode][1], outs[False][1]), mode
+
+
+def test_block_loop_prefetches_blocks_that_start_on_the_host():
+    """SURVEY §8f N4 (base_bq.py:397): a model whose blocks still live in host memory is calibrated block by block while
+    the next block is copied in on a side stream by a worker thread — same weights as the model that starts on the GPU,
+    with and without the prefetch, and every block ends on the device."""
+    import copy
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(3)
+    cfg = LlamaConfig(vocab_size=256, hidden_size=256, intermediate_size=512, num_hidden_layers=4, num_attention_heads=4,
+                      num_key_value_heads=2, max_position_embeddings=256)
+    base = LlamaForCausalLM(cfg).to(torch.bfloat16).eval()
+    g = torch.Generator().manual_seed(1)
+    calib = [torch.randint(0, 256, (1, 64), generator=g) for _ in range(8)]
+    q = {'weight': {'bit': 4, 'symmetric': False, 'granularity': 'per_group', 'group_size': 128},
+         'special': {'actorder': False, 'percdamp': 0.01, 'blocksize': 128, 'true_sequential': True}, 'quant_out': True}
+
+    def run(host_blocks, prefetch):
+        m = copy.deepcopy(base).to(DEV)
+        ad = algo.adapters.LlamaAdapter(m)
+        inp = ad.collect_first_block_input([{'input_ids': ids.to(DEV)} for ids in calib])
+        if host_blocks:
+            for b in m.model.layers:
+                b.to('cpu')
+        cfgq = copy.deepcopy(q)
+        cfgq['special']['prefetch_blocks'] = prefetch
+        a = algo.ALGO_REGISTRY['GPTQ'](ad, cfgq, inp, None, {'calib': {'seq_len': 64}})
+        a.run_block_loop()
+        assert all(p.is_cuda for b in m.model.layers for p in b.parameters())
+        return [p.detach().float().cpu() for b in m.model.layers for p in b.parameters()]
+
+    ref = run(False, True)
+    for host_blocks, prefetch in ((True, True), (True, False)):
+        got = run(host_blocks, prefetch)
+        # the Hessian's split-K reductions are not run-to-run deterministic: equal up to GPTQ's own reproducibility
+        same = sum(float((a == b).float().mean()) for a, b in zip(ref, got)) / len(ref)
+        assert same > 0.99, same

@@ -1,7 +1,7 @@
 """End-to-end calibration seconds per block through the ALGO_REGISTRY plug-ins, on ONE random-init decoder block with
 Llama-3-8B dimensions (hidden 4096, inter 14336, 32 heads / 8 KV heads) — BASELINE.json's "GPTQ/AWQ calib s/block".
 
-    python tools/block_bench.py [gptq] [awq] [--samples N]
+    python tools/block_bench.py [gptq] [awq] [--samples N] [--host-blocks prefetch|sync]
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/block_bench.py [gptq] [awq]
 
 Under torchrun: GPTQ shards the calibration samples `rank::world` like the reference's loader
@@ -52,6 +52,10 @@ def run(method, dev, samples, seq, special, quant_out=False, bs=1):
         data = data[RANK::WORLD]         # token-sharded calibration (GPTQ); a single batch (AWQ) stays whole on every rank
     ad = algo.adapters.LlamaAdapter(model)
     inp = ad.collect_first_block_input(data)
+    if HOST_BLOCKS:                       # the blocks start in (pageable) host memory, like a freshly loaded checkpoint
+        for b in model.model.layers:
+            b.to('cpu')
+        special = dict(special, prefetch_blocks=HOST_BLOCKS == 'prefetch')
     a = algo.ALGO_REGISTRY[method](ad, {'weight': dict(W4), 'special': special, 'quant_out': quant_out}, inp, None,
                                    {'calib': {'seq_len': seq}})
     times = []
@@ -89,10 +93,11 @@ def run(method, dev, samples, seq, special, quant_out=False, bs=1):
 
 
 RANK, WORLD = 0, 1
+HOST_BLOCKS = None    # --host-blocks prefetch|sync: blocks start on the host; copied in ahead of time or at their turn
 
 
 def main(argv=None, emit=True):
-    global RANK, WORLD
+    global RANK, WORLD, HOST_BLOCKS
     argv = sys.argv[1:] if argv is None else argv
     WORLD = int(os.environ.get('WORLD_SIZE', '1'))
     local = int(os.environ.get('LOCAL_RANK', '0'))
@@ -102,6 +107,7 @@ def main(argv=None, emit=True):
         torch.distributed.init_process_group('nccl', device_id=dev)
     RANK = torch.distributed.get_rank() if WORLD > 1 else 0
     samples = int(argv[argv.index('--samples') + 1]) if '--samples' in argv else 128
+    HOST_BLOCKS = argv[argv.index('--host-blocks') + 1] if '--host-blocks' in argv else None
     which = [a for a in argv if a in ('gptq', 'awq')] or ['gptq', 'awq']
     res = {}
     if 'gptq' in which:
@@ -119,6 +125,8 @@ def main(argv=None, emit=True):
         res['awq_memory'] = MEM.get('Awq')
         res['awq_config'] = f'{samples} x 512 tokens (one batch, bs -1), w4a16 g128, trans v2 + AutoClip'
     res['n_gpus'] = WORLD
+    if HOST_BLOCKS:
+        res['host_blocks'] = HOST_BLOCKS
     if emit and RANK == 0:
         print(json.dumps(res), flush=True)
     if WORLD > 1 and emit:
