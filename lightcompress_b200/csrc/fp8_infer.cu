@@ -185,6 +185,7 @@ struct Params {
   int ksplit, kbs;
   float* ws;
   int* cnt;           // arrivals per output tile (behind the sums in the workspace); zero between calls
+  int col_fast;       // tile order: column blocks fastest (a wave covers few row blocks x all column blocks)
 };
 struct Maps {
   CUtensorMap a, b;
@@ -244,9 +245,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
-        // consecutive CTAs share the B (weight) column block: tile index runs over row blocks fastest
+        // tile index runs over column blocks fastest (p.col_fast): consecutive CTAs share the A row block
         const int to = t / p.ksplit, ks = t % p.ksplit;
-        const int ti = to % p.nblk_i, tj = to / p.nblk_i;
+        const int ti = p.col_fast ? to / p.nblk_j : to % p.nblk_i, tj = p.col_fast ? to % p.nblk_j : to / p.nblk_i;
         const int kb0 = ks * p.kbs, kb1 = min(nkb, kb0 + p.kbs);
         for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(&empty[stage], phase ^ 1);
@@ -304,7 +305,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) fp8_gemm_kernel(const __grid_cons
     float accv[EPI_COLS];
     for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
       const int to = t / p.ksplit, ks = t % p.ksplit;
-      const int ti = to % p.nblk_i, tj = to / p.nblk_i;
+      const int ti = p.col_fast ? to / p.nblk_j : to % p.nblk_i, tj = p.col_fast ? to % p.nblk_j : to / p.nblk_i;
       const int kb0 = ks * p.kbs, kb1 = min(nkb, kb0 + p.kbs);
       const int row = ti * BM + q * 32 + lane;
       const float* asp = p.a_s + (int64_t)min(row, p.M - 1) * nkb;
@@ -564,6 +565,10 @@ static int fp8_gemm_impl(const void* a, const float* a_s, const void* b, const f
   p.kbs = (p.nkb + p.ksplit - 1) / p.ksplit;
   p.ksplit = (p.nkb + p.kbs - 1) / p.kbs;          // no empty slice
   p.ws = reinterpret_cast<float*>(workspace);
+  // a wave of 148 tiles covers a few row blocks x all column blocks: an A row block is read from HBM once (shared by the
+  // CTAs of its row through the L2) and the weight stays L2-resident across waves. ncu, 8192 x 2048 x 7168: dram read
+  // 132 -> 75 MB (= the operands), L2 hit 80 -> 87 %, +2-13 % TFLOP/s. LCB_FP8_COL_FAST=0 restores row blocks fastest.
+  p.col_fast = getenv("LCB_FP8_COL_FAST") ? atoi(getenv("LCB_FP8_COL_FAST")) : 1;
   p.cnt = workspace ? reinterpret_cast<int*>(p.ws + (M * N + 3) / 4 * 4) : nullptr;
   p.n_tiles = p.nblk_i * p.nblk_j * p.ksplit;
   p.nsb = (int)((N + 127) / 128);
