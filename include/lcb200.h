@@ -398,6 +398,14 @@ int lcb_pack_rows(const void* codes, int32_t* out, int64_t rows, int64_t cols, i
 int lcb_awq_gemm_pack(const void* W, const void* scales, const int32_t* zeros, int32_t* qweight, int32_t* qzeros, int64_t R,
                       int64_t C, int32_t group_size, int32_t dtype, void* stream);
 
+/*
+ * out[0] += sum_i (T(a[i] - b[i]))^2: the difference rounded to the tensor dtype, the square and the sum in fp32 / fp64 —
+ * the arithmetic of `(org_out - out).float().pow(2).mean()` (calculate_loss, awq.py:134-145; the caller divides by n) in
+ * one pass over the two tensors instead of four torch kernels. a, b: n contiguous elements of `dtype`; out: one double,
+ * accumulated into (zero it first).
+ */
+int lcb_sqdiff_sum(const void* a, const void* b, double* out, int64_t n, int32_t dtype, void* stream);
+
 /* column absmax of a [rows, cols] matrix -> fp32 [cols] (running max: out = max(out, colmax)).
  * Replaces SmoothQuant.get_act_scale / get_weight_scale (smoothquant.py:27-51) and the |x| reductions
  * of Awq.get_act_scale (awq.py:74-85) when mean != 0 (then it is a column |x| sum). */

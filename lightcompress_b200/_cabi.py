@@ -48,6 +48,7 @@ SIGNATURES = {
     'lcb_hessian_workspace_bytes': (_c_i64, [_c_i64, _c_i64, _c_i32]),
     'lcb_floatquant_elem': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i32, _c_i32, _c_i32, _c_vp]),
     'lcb_floatquant_elem_static': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i32, _c_i32, _c_vp]),
+    'lcb_sqdiff_sum': (ctypes.c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i32, _c_vp]),
     'lcb_hessian_accum_f32_noalloc': (ctypes.c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_vp]),
     'lcb_hessian_finalize': (ctypes.c_int, [_c_vp, _c_i64, ctypes.c_double, _c_vp]),
     'lcb_hessian_packed_elems': (_c_i64, [_c_i64]),

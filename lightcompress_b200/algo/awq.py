@@ -140,7 +140,10 @@ def awq_search_scale_module(x, layers, inspect_module, wquantizer, kwargs=None, 
         if aquantizer is not None:
             x_tmp = aquantizer.fake_quant_act_dynamic(x_tmp)
         out = fwd(x_tmp)
-        losses.append((org_out - out).float().pow(2).mean())   # stays on the device: one sync after the loop
+        if out.is_cuda and out.dtype == org_out.dtype and out.dtype in (torch.bfloat16, torch.float16, torch.float32):
+            losses.append(ops.sqdiff_mean(org_out, out))            # one pass, same roundings; stays on the device
+        else:
+            losses.append((org_out - out).float().pow(2).mean())   # stays on the device: one sync after the loop
         for m, w0 in zip(layers, saved):
             m.weight.data = w0
     losses = torch.stack(losses).tolist() if losses else []

@@ -190,6 +190,21 @@ def linear_mse(x, w, org_out, loss=None):
     return loss
 
 
+def sqdiff_mean(a, b):
+    """`(a - b).float().pow(2).mean()` (calculate_loss, awq.py:134-145) in one pass (lcb_sqdiff_sum): the difference in
+    the tensor dtype, squares and sum in fp32 / fp64. Returns a 0-dim float64 device tensor (no host sync)."""
+    _need_cuda(a, b)
+    assert a.shape == b.shape and a.dtype == b.dtype
+    a2 = a if a.is_contiguous() else a.contiguous()
+    b2 = b if b.is_contiguous() else b.contiguous()
+    out = torch.zeros(1, dtype=torch.float64, device=a.device)
+    lib = _cabi.load()
+    with _on_device(a.device):
+        st = lib.lcb_sqdiff_sum(a2.data_ptr(), b2.data_ptr(), out.data_ptr(), a2.numel(), _DT[a2.dtype], _stream(a.device.index))
+    _cabi.check(st, 'lcb_sqdiff_sum')
+    return out[0] / float(max(a2.numel(), 1))
+
+
 def linear(x, w, bias=None):
     """torch.nn.functional.linear(x, w, bias) for 16-bit tensors on the tcgen05 contraction (lcb_linear): fp32
     accumulation, one rounding. x [..., C], w [R, C] of the same dtype; bias None or [R]."""

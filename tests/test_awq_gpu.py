@@ -118,3 +118,20 @@ def test_own_linears_swaps_and_restores():
         got = mlp(x)
     assert all('forward' not in m.__dict__ for m in mlp.modules())
     assert float((got.float() - ref.float()).abs().max()) <= 2e-2 * float(ref.float().abs().max())
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize('shape', [(64, 512, 1024), (7, 33), (1000, 4099)])
+def test_sqdiff_mean_is_the_reference_loss_in_one_pass(dtype, shape):
+    """ops.sqdiff_mean == (a - b).float().pow(2).mean() (calculate_loss, awq.py:134-145): same element roundings (difference
+    in the tensor dtype, fp32 squares); only the summation order differs, bounded here against an fp64 sum of the same terms."""
+    g = torch.Generator(device=DEV).manual_seed(shape[0])
+    a = torch.randn(*shape, device=DEV, generator=g).to(dtype)
+    b = (a.float() + 0.05 * torch.randn(*shape, device=DEV, generator=g)).to(dtype)
+    got = float(ops.sqdiff_mean(a, b))
+    terms = (a - b).float().pow(2)
+    exact = float(terms.double().sum() / terms.numel())
+    ref = float(terms.mean())
+    assert abs(got - exact) <= 2e-6 * exact
+    assert abs(got - ref) <= 1e-5 * exact
+    assert float(ops.sqdiff_mean(a, a)) == 0.0
