@@ -219,8 +219,9 @@ def _restore(cls):
 
 
 def patch_autoclipper(cls):
-    """cls: llmc.compression.quantization.auto_clip.AutoClipper. Routes auto_clip_layer (v1, w_only) to
-    lcb_autoclip_search; anything else keeps the reference path. Returns True when newly patched."""
+    """cls: llmc.compression.quantization.auto_clip.AutoClipper. Routes auto_clip_layer to lcb_autoclip_search (v1, w_only)
+    or to the split lcb_autoclip_init / _step search (v2 per_channel, w+a); anything else keeps the reference path.
+    Returns True when newly patched."""
     if cls.__dict__.get('_lcb_patched', False):
         return False
     _rebind(cls, 'auto_clip_layer', _autoclip_layer)
