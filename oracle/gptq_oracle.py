@@ -5,9 +5,9 @@ Each function follows /root/reference/llmc/compression/quantization/gptq.py line
   add_batch                     gptq.py:254-295   (world_size 1: the all-reduce is the identity)
   process_hessian               gptq.py:128-176   (dead columns, damping, Cholesky inverse factor)
   weight_transform              gptq.py:199-244   (+ search_column_qparams :359-366)
-Parity pinning: tests/golden/make_gptq_golden.py drives the UNMODIFIED reference class methods
-(object.__new__(GPTQ), SURVEY.md §8c recipe 2) on seeded inputs and stores their outputs under tests/golden/;
-tests/test_gptq_oracle.py checks this restatement against them.
+Parity pinning: tests/golden/make_algo_golden.py drives the UNMODIFIED reference class methods
+(object.__new__(GPTQ), SURVEY.md §8c recipe 2) on seeded inputs and stores their outputs in tests/golden/algo_golden.pt.gz;
+tests/test_algo_oracle_golden.py checks this restatement against them.
 """
 import math
 
