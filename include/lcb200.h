@@ -258,7 +258,8 @@ int64_t lcb_hessian_workspace_bytes(int64_t tokens, int64_t C, int32_t x_dtype);
  */
 #define LCB_HESSIAN_NOALLOC_MAX_ELEMS (4ll << 20)
 int lcb_hessian_accum_f32_noalloc(float* S, const float* X, int64_t tokens, int64_t C, void* stream);
-/* H = scale * sym(S) in place: scales the upper blocks and mirrors them into the lower ones. scale = 2 / nsamples. */
+/* H = scale * sym(S) in place: scales the upper blocks and mirrors them into the lower ones. scale = 2 / nsamples: the
+ * normalisation gptq.py:283-290 applies per batch (H *= n / (n + b); H += (2 / n) X^T X), applied once. */
 int lcb_hessian_finalize(float* S, int64_t C, double scale, void* stream);
 /*
  * Token-sharded Hessians (replaces the all-reduce per batch of gptq.py:292-295 by ONE per linear):
@@ -412,9 +413,10 @@ int lcb_sqdiff_sum(const void* a, const void* b, double* out, int64_t n, int32_t
 int lcb_col_absstat(const void* x, float* out, int64_t rows, int64_t cols, int32_t dtype, int32_t mean,
                     void* stream);
 
-/* version / capability probe; returns LCB_ABI_VERSION */
+/* version / capability probe; returns LCB_ABI_VERSION (no counterpart in the reference: it has no FFI) */
 int lcb_abi_version(void);
-/* name of the last failing CUDA call of this thread ("" if none) */
+/* name of the last failing CUDA call of this thread ("" if none); no counterpart in the reference: the text the Python
+ * mirror puts into the RuntimeError it raises for LCB_E_CUDA */
 const char* lcb_last_error(void);
 
 #ifdef __cplusplus

@@ -37,3 +37,18 @@ def test_sass_is_sm100a_only():
     out = subprocess.run(['cuobjdump', '-lelf', _build.LIB], capture_output=True, text=True).stdout
     archs = set(re.findall(r'sm_(\d+a?)', out))
     assert archs == {'100a'}, archs
+
+
+def test_every_entry_point_cites_the_reference_interface_it_replaces():
+    """The boundary rule: each declaration in include/lcb200.h sits under a comment that cites the reference file:line it
+    replaces, or says that it has no counterpart in the reference."""
+    src = open(os.path.join(ROOT, 'include', 'lcb200.h')).read()
+    comments = [(m.end(), m.group(1)) for m in re.finditer(r'/\*(.*?)\*/', src, flags=re.S)]
+    blank = re.sub(r'/\*.*?\*/', lambda m: ' ' * len(m.group(0)), src, flags=re.S)
+    missing = []
+    for m in re.finditer(r'\b(lcb_[a-z0-9_]+)\s*\(', blank):
+        before = [c for end, c in comments if end <= m.start()]
+        text = before[-1] if before else ''
+        if not (re.search(r'\.py:\d+', text) or 'no counterpart in the reference' in text.lower()):
+            missing.append(m.group(1))
+    assert not missing, missing
