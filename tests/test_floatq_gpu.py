@@ -104,3 +104,4 @@ def test_llama_sized_rows_and_error_behaviour(ref):
         Q.FloatQuantizer('e4m3', True, 'per_tensor').fake_quant_weight_dynamic(w)
     with pytest.raises(NotImplementedError):
         Q.FloatQuantizer('e4m3', True, 'per_channel').real_quant_weight_dynamic(w)
+
