@@ -1,11 +1,12 @@
 """TEST INFRASTRUCTURE — CPU restatement of the reference's block-wise FP8 inference kernels
 (llmc/compression/quantization/kernel.py). Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import it.
 
-The reference functions are Triton kernels and cannot run without a GPU, so there is no reference-generated golden
-vector for them: PARITY UNPINNED against Triton's own code generation (its fp32 `/`, the accumulation order inside
-`tl.dot`). The restatement follows the kernel source statement by statement with IEEE fp32 arithmetic; the pieces that
-the reference ALSO states in torch (weight_cast_to_fp8 / weight_cast_to_bf16, quant.py:18-43) are pinned elsewhere
-(tests/golden/quant_golden.pt.gz).
+The reference functions are Triton kernels and cannot run without a GPU. Pinned by tests/golden/fp8_infer_golden.pt.gz:
+outputs of the reference's own kernels produced on the B200 box (tests/golden/make_fp8_infer_golden.py) — against this
+restatement's IEEE divisions the Triton scales (div.full.f32) sit at most one fp32 ulp apart and < 0.1 % of the codes
+(exact e4m3 rounding ties) one code step apart; fp8_gemm on identical operands agrees to 7e-8; weight_cast_to_bf16 is
+bit-exact (tests/test_fp8_infer_golden.py). The pieces that the reference ALSO states in torch (weight_cast_to_fp8 /
+weight_cast_to_bf16, quant.py:18-43) are pinned by tests/golden/quant_golden.pt.gz as well.
 """
 import torch
 
